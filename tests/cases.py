@@ -1,0 +1,64 @@
+"""Shared synthetic inputs for tests / bench (SURVEY 8 'Synthetic inputs').  Pure numpy."""
+import numpy as np
+
+MASK = (1 << 64) - 1
+
+
+def splitmix64(seed, n):
+    """n uniform doubles in [0,1) from splitmix64(seed)."""
+    out = np.empty(n)
+    s = seed & MASK
+    for i in range(n):
+        s = (s + 0x9E3779B97F4A7C15) & MASK
+        z = s
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & MASK
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & MASK
+        z ^= z >> 31
+        out[i] = (z >> 11) * (1.0 / (1 << 53))
+    return out
+
+
+def gaussian_source(x, y):
+    """main.cpp:29-32"""
+    return np.exp(-25 * ((x - 0.5) ** 2 + (y - 0.5) ** 2))
+
+
+def tilted_source(x, y):
+    """anchor source of SURVEY 8(c): e^{-25 rho^2} (1 + x + 2y)"""
+    return gaussian_source(x, y) * (1 + x + 2 * y)
+
+
+def random_source(n, seed=1):
+    return 2 * splitmix64(seed, n) - 1
+
+
+def sigma_fields(kind, x, y, sz, deg):
+    """returns (sigma_s, sigma_t) per node."""
+    if kind == "main":  # main.cpp:34-40
+        ss = 16 * 0.5 * (1 - np.cos(2 * np.pi * x))
+        return ss, ss + 0.2
+    if kind == "const":  # demo.m:15-16
+        ss = np.full_like(x, 20.0)
+        return ss, ss + 0.2
+    if kind == "hetero":  # C3: sigma_s = 4 + 12 u(cell), sigma_a = 0.2
+        u = splitmix64(0xA715020, sz * sz)
+        ss = np.repeat(4 + 12 * u, deg * deg)
+        return ss, ss + 0.2
+    if kind == "layers":  # C5: 4 bands in y
+        band = np.minimum((y * 4).astype(int), 3)
+        ss = np.array([2.0, 16.0, 6.0, 12.0])[band]
+        sa = np.array([0.1, 0.5, 0.2, 0.3])[band]
+        return ss, ss + sa
+    raise ValueError(kind)
+
+
+# name -> (sz, deg, K, g, sr, np, maxLevel, sigma kind)
+CASES = {
+    "a16": (16, 1, 2, 0.5, 10, 4, 20, "main"),      # SURVEY 8(c) anchor
+    "b8d3": (8, 3, 2, 0.5, 8, 4, 20, "main"),       # SURVEY 8(c) anchor, deg 3
+    "h32": (32, 1, 2, 0.9, 10, 6, 20, "hetero"),    # C3-like, np 6
+    "nu6d5": (6, 5, 1, 0.5, 6, 2, 20, "layers"),    # non-uniform tree (W/X lists)
+    "ml12d2": (12, 2, 1, 0.5, 4, 3, 2, "main"),     # maxLevel cap, non power-of-two sz
+    "c2": (128, 1, 5, 0.5, 10, 4, 20, "const"),     # BASELINE config 2
+    "c1": (64, 3, 1, 0.95, 8, 4, 20, "main"),       # BASELINE config 1 (data.cfg)
+}
