@@ -1,0 +1,95 @@
+// Device-side view of one aniso handle and the launch wrappers of kernels.cu.  sm_100a only.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+namespace an {
+
+enum PartMask { PART_REAL = 1, PART_IMAG = 2, PART_BOTH = 3 };  // realParts / imagParts of KernelFactory.h:22-23
+
+// sigma_t interpolant (KernelFactory.cpp:174-207): per-cell Legendre coefficients already divided by the
+// legendreNorms, evaluated at GLOBAL coordinates (quirk Q1).
+struct SigmaGrid {
+    int sz, deg, c2;
+    double h;              // cell width 1/sz
+    const double* chat;    // [ncell][c2]
+    const double* glx;     // [deg] table order
+    const double* glw;     // [deg]
+};
+
+// block-CSR operator (see plan.hpp BlockCSR); all pointers are device memory
+struct DevCSR {
+    int groups = 0, entries = 0, nrows_total = 0, uniform_nrow = 0;
+    int64_t nnz = 0;
+    int *row_off = nullptr, *nrow = nullptr, *ent_ptr = nullptr, *col_off = nullptr, *ncol = nullptr;
+    int64_t* blk_off = nullptr;
+    int *tgt_node = nullptr, *src_node = nullptr, *grow_ptr = nullptr, *row_group = nullptr;
+};
+
+struct DevTree {
+    int nnodes = 0, np = 0, r = 0, nlevels = 0;
+    double *cx = nullptr, *cy = nullptr, *rx = nullptr, *ry = nullptr;
+    int *parent = nullptr, *index = nullptr, *child = nullptr;  // child: [nnodes][4]
+    int *pt_off = nullptr, *npts = nullptr;
+    unsigned char* flags = nullptr;                             // bit0 leaf, bit1 empty
+    double *cheb = nullptr, *tnode = nullptr, *R = nullptr;     // R: [4][r][r]
+    int* leaves = nullptr;                                      // owned non-empty leaves
+    int nleaves = 0;
+};
+
+// cell-based correction tables (Geometry / singPrecompute data, uploaded once)
+struct DevGeom {
+    int sz, deg, c2, rq, nsing, N;
+    double dx;
+    const double *px, *py, *pw;          // slot order
+    const int *perm, *inv_perm;          // slot <-> reference node index
+    const double *sqrtw, *interp, *lnorm, *nearMap, *rqx, *rqy, *rqw, *singX, *singY, *singW;
+};
+
+// ---- launch wrappers (kernels.cu) -------------------------------------------------------------
+// K1/K2 evaluator: fills A for every entry of `m`.  cheb != 0: Chebyshev nodes of the two boxes (M2L),
+// else the points of the two nodes (P2P).  A[blk_off[e] + s*nrow + t] = eval(source s, target t).
+void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const SigmaGrid& S, int id, int part, int cheb,
+                 double* A, cudaStream_t st);
+// y[row] (=) sum over entries: the HBM-streaming cached apply (K3 / K4)
+void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, cudaStream_t st);
+void launch_scale(int n, const double* x, const double* sig_s, const double* w, double* f, double* q, cudaStream_t st);
+void launch_p2m(const DevTree& T, const DevGeom& G, const double* q, double* mcharge, cudaStream_t st);
+void launch_m2m(const DevTree& T, int first, int count, double* mcharge, cudaStream_t st);
+void launch_l2l(const DevTree& T, int first, int count, double* mpot, cudaStream_t st);
+// out[p] = pot[p] + L2P(p) for slots [slot0, slot0+n)
+void launch_l2p(const DevTree& T, const DevGeom& G, const int* leaf_of_slot, int slot0, int n, const double* mpot,
+                const double* pot, double* out, cudaStream_t st);
+// correction stencils: C[(slotcell*c2+q)*nown + (p-slot0)], slotcell in 0..8 ((dr+1)*3+(dc+1))
+void launch_build_stencils(const DevGeom& G, int id, int slot0, int nown, double* c7, double* c8, double* c9, cudaStream_t st);
+// acc[p-slot0] (+)= sign * sum stencil * f ; mode 0: overwrite, 1: accumulate
+void launch_stencil_apply(const DevGeom& G, int slot0, int nown, const double* C, const double* f, double* acc, int accumulate,
+                          cudaStream_t st);
+// out = (fmm + corr) / 2pi, optionally y = x - that (GMRES operator of main.cpp:123-136)
+void launch_finalize(int n, const double* fmm, const double* corr, const double* x, double* out, int subtract_from_x,
+                     cudaStream_t st);
+void launch_gather(int n, const double* src, const int* idx, double* dst, cudaStream_t st);  // dst[i] = src[idx[i]]
+void launch_add3(int n, const double* a, const double* b, const double* c, double* out, cudaStream_t st);
+// sigma interpolation on device: chat[c][r] = (sum_j interp[r][j] sqrtw[j] h[c*c2+j]) / (lnorm ? lnorm[r] : 1), h in REFERENCE order
+void launch_interpolate(const DevGeom& G, const double* h_ref, const double* lnorm_or_null, double* coeff, cudaStream_t st);
+// probes for parity tests
+void launch_probe_line_integral(const SigmaGrid& S, int n, const double* pts4, double* out, cudaStream_t st);
+void launch_probe_kernel(const SigmaGrid& S, int id, int part, int n, const double* pts4, double* out, cudaStream_t st);
+
+// ---- GMRES vector ops (gmres.cu) ----------------------------------------------------------------
+struct DotWork {
+    double* partial = nullptr;  // [blocks]
+    unsigned int* counter = nullptr;
+    int blocks = 0;
+};
+void launch_dot(int n, const double* a, const double* b, double* result, DotWork& wk, cudaStream_t st);
+// w -= h[0] * v  (h read from device memory)
+void launch_axpy_neg_dev(int n, const double* h, const double* v, double* w, cudaStream_t st);
+void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t st);
+// out = in * (1/ *norm)
+void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, cudaStream_t st);
+void launch_sqrt1(double* v, cudaStream_t st);
+void launch_sub(int n, const double* a, const double* b, double* out, cudaStream_t st);  // out = a - b
+
+}  // namespace an

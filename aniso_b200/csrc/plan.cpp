@@ -1,0 +1,594 @@
+// Host set-up for the aniso hot path (see plan.hpp).  Plain C++17, no CUDA, usable on a CPU-only box.
+#include "plan.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <functional>
+#include <stdexcept>
+
+namespace an {
+
+static constexpr double kEps = 1e-12;  // bbfmm/utils.h:46 (EPS)
+
+// ---------------------------------------------------------------------------------------------
+// Gauss-Legendre tables.  The reference ships 58-digit decimal tables (Quadrature.cpp:5418-22191);
+// correctly rounded doubles are reproduced here by Newton iteration carried to binary128, and the
+// rows are emitted in the table's (non-monotone) order: centre outwards in (-x,+x) pairs, with the
+// three irregular degrees 6, 7 and 9 listed explicitly (quirk Q9).
+// ---------------------------------------------------------------------------------------------
+typedef __float128 quad_t;
+
+static void legendre_pair(int n, quad_t z, quad_t& pn, quad_t& pnm1) {
+    quad_t a = 1, b = 0;
+    for (int j = 1; j <= n; ++j) {
+        quad_t c = b;
+        b = a;
+        a = ((2 * j - 1) * z * b - (j - 1) * c) / j;
+    }
+    pn = a;
+    pnm1 = b;
+}
+
+static void gl_sorted(int n, std::vector<quad_t>& x, std::vector<quad_t>& w) {
+    x.resize(n);
+    w.resize(n);
+    const long double pi = 3.14159265358979323846264338327950288L;
+    for (int i = 0; i < n; ++i) {
+        long double zl = -cosl(pi * (i + 0.75L) / (n + 0.5L));
+        for (int it = 0; it < 100; ++it) {
+            long double a = 1, b = 0;
+            for (int j = 1; j <= n; ++j) {
+                long double c = b;
+                b = a;
+                a = ((2 * j - 1) * zl * b - (j - 1) * c) / j;
+            }
+            long double step = a / (n * (zl * a - b) / (zl * zl - 1));
+            zl -= step;
+            if (fabsl(step) < 1e-19L) break;
+        }
+        quad_t z = zl, pn, pm, dp = 0;
+        for (int it = 0; it < 3; ++it) {
+            legendre_pair(n, z, pn, pm);
+            dp = n * (z * pn - pm) / (z * z - 1);
+            if (it < 2) z -= pn / dp;
+        }
+        x[i] = z;
+        w[i] = 2 / ((1 - z * z) * dp * dp);
+    }
+    if (n & 1) x[n / 2] = 0;
+}
+
+static void table_order(int n, std::vector<int>& ord) {
+    ord.resize(n);
+    static const int o6[6] = {4, 1, 2, 3, 0, 5};
+    static const int o7[7] = {3, 4, 2, 1, 5, 0, 6};
+    static const int o9[9] = {4, 1, 7, 0, 8, 3, 5, 2, 6};
+    const int* irregular = n == 6 ? o6 : n == 7 ? o7 : n == 9 ? o9 : nullptr;
+    if (irregular) {
+        std::copy(irregular, irregular + n, ord.begin());
+        return;
+    }
+    int k = 0;
+    int lo = (n & 1) ? n / 2 - 1 : n / 2 - 1, hi = (n & 1) ? n / 2 + 1 : n / 2;
+    if (n & 1) ord[k++] = n / 2;
+    while (lo >= 0) {
+        ord[k++] = lo--;
+        ord[k++] = hi++;
+    }
+}
+
+bool gl_table(int n, double* x, double* w) {
+    if (n < 1 || n > 128) return false;
+    std::vector<quad_t> xs, ws;
+    std::vector<int> ord;
+    gl_sorted(n, xs, ws);
+    table_order(n, ord);
+    for (int s = 0; s < n; ++s) {
+        x[s] = (double)xs[ord[s]];
+        w[s] = (double)ws[ord[s]];
+    }
+    return true;
+}
+
+// libstdc++ std::tr1::legendre (tr1/legendre_function.tcc:82-114), used via bbfmm/utils.h:81
+static double legendre_tr1(int l, double x) {
+    if (x == 1.0) return 1.0;
+    if (x == -1.0) return (l & 1) ? -1.0 : 1.0;
+    if (l == 0) return 1.0;
+    if (l == 1) return x;
+    double pm2 = 1.0, pm1 = x, p = 0;
+    for (int ll = 2; ll <= l; ++ll) {
+        p = 2.0 * x * pm1 - pm2 - (x * pm1 - pm2) / (double)ll;
+        pm2 = pm1;
+        pm1 = p;
+    }
+    return p;
+}
+
+// Geometry::makeLegendreMatrix (Geometry.cpp:129-154): rows (n,k), normalised; norms go to p.lnorm
+static void legendre_matrix(HostPlan& p, std::vector<double>& M, int npts, const double* x, const double* y,
+                            const double* w) {
+    const int deg = p.deg, c2 = p.c2;
+    M.assign((size_t)c2 * npts, 0.0);
+    for (int n = 0; n < deg; ++n)
+        for (int k = 0; k < deg; ++k) {
+            double* row = &M[(size_t)(n * deg + k) * npts];
+            double ss = 0;
+            for (int I = 0; I < npts; ++I) {
+                row[I] = legendre_tr1(n, x[I]) * legendre_tr1(k, y[I]) * std::sqrt(w[I]);
+                ss += row[I] * row[I];
+            }
+            const double nrm = std::sqrt(ss);
+            p.lnorm[n * deg + k] = nrm;  // the second call (refined rule) overwrites the first: Q3
+            for (int I = 0; I < npts; ++I) row[I] /= nrm;
+        }
+}
+
+static void build_geometry(HostPlan& p) {
+    const int sz = p.sz, deg = p.deg, c2 = p.c2, rq = p.rq, sr = p.sr;
+    p.glx.resize(deg);
+    p.glw.resize(deg);
+    gl_table(deg, p.glx.data(), p.glw.data());
+    p.sgx.resize(sr);
+    p.sgw.resize(sr);
+    gl_table(sr, p.sgx.data(), p.sgw.data());
+    for (int k = 0; k < sr; ++k) {  // affine(), Quadrature.cpp:22194-22199
+        p.sgw[k] /= 2.0;
+        p.sgx[k] += 1.0;
+        p.sgx[k] /= 2.0;
+    }
+    std::vector<double> qx(c2), qy(c2), qw(c2);
+    p.sqrtw.resize(c2);
+    for (int a = 0; a < deg; ++a)
+        for (int b = 0; b < deg; ++b) {
+            qx[a * deg + b] = p.glx[a];
+            qy[a * deg + b] = p.glx[b];
+            qw[a * deg + b] = p.glw[a] * p.glw[b];
+            p.sqrtw[a * deg + b] = std::sqrt(qw[a * deg + b]);
+        }
+    p.nx.resize(p.N);
+    p.ny.resize(p.N);
+    p.w.resize(p.N);
+    const double dx = p.dx;
+    for (int i = 0; i < sz; ++i)
+        for (int j = 0; j < sz; ++j)
+            for (int k = 0; k < c2; ++k) {
+                const int id = (i * sz + j) * c2 + k;
+                p.nx[id] = (0.5 + i) * dx + 0.5 * (qx[k]) * dx;
+                p.ny[id] = (0.5 + j) * dx + 0.5 * qy[k] * dx;
+                p.w[id] = qw[k] * 0.25 * (dx * dx);
+            }
+    p.lnorm.assign(c2, 0.0);
+    legendre_matrix(p, p.interp, c2, qx.data(), qy.data(), qw.data());
+    // two rounds of 4-way refinement in the reference's push order (Geometry.cpp:79-107)
+    std::vector<double> rx = qx, ry = qy, rw = qw;
+    for (int round = 0; round < 2; ++round) {
+        std::vector<double> tx, ty, tw;
+        tx.reserve(rx.size() * 4);
+        ty.reserve(rx.size() * 4);
+        tw.reserve(rx.size() * 4);
+        static const int sx[4] = {+1, +1, -1, -1}, sy[4] = {+1, -1, +1, -1};
+        for (size_t id = 0; id < rx.size(); ++id)
+            for (int q = 0; q < 4; ++q) {
+                tx.push_back((rx[id] + sx[q]) / 2.0);
+                ty.push_back((ry[id] + sy[q]) / 2.0);
+                tw.push_back(rw[id] / 4.0);
+            }
+        rx.swap(tx);
+        ry.swap(ty);
+        rw.swap(tw);
+    }
+    p.rqx = rx;
+    p.rqy = ry;
+    p.rqw = rw;
+    std::vector<double> refinements;
+    legendre_matrix(p, refinements, rq, rx.data(), ry.data(), rw.data());
+    // nearMapping = refinements^T * interpolate (Geometry.cpp:109-113), stored [a][q]
+    p.nearMap.assign((size_t)rq * c2, 0.0);
+    for (int a = 0; a < rq; ++a)
+        for (int q = 0; q < c2; ++q) {
+            double s = 0;
+            for (int r = 0; r < c2; ++r) s += refinements[(size_t)r * rq + a] * p.interp[(size_t)r * c2 + q];
+            p.nearMap[(size_t)a * c2 + q] = s;
+        }
+    // singPrecompute (KernelFactory.cpp:929-986): 8 Duffy triangles around each in-cell node
+    const int ns = p.nsing;
+    p.singX.assign((size_t)c2 * ns, 0.0);
+    p.singY.assign((size_t)c2 * ns, 0.0);
+    p.singW.assign((size_t)c2 * ns, 0.0);
+    for (int a = 0; a < deg; ++a)
+        for (int b = 0; b < deg; ++b) {
+            const int t = a * deg + b;
+            const double x = p.glx[a], y = p.glx[b];
+            const double tri[8][6] = {{x, y, 1., y, 1., 1.},   {x, y, 1., 1, x, 1.},    {x, y, x, 1., -1., 1.},
+                                      {x, y, -1., 1., -1., y}, {x, y, -1., y, -1., -1.}, {x, y, -1., -1, x, -1.},
+                                      {x, y, x, -1., 1., -1.}, {x, y, 1., -1, 1., y}};
+            for (int k = 0; k < 8; ++k) {  // duffy_transform, KernelFactory.cpp:863-927
+                const double* v = tri[k];
+                const double a11 = v[2] - v[0], a12 = v[4] - v[2], a21 = v[3] - v[1], a22 = v[5] - v[3];
+                const double det = a11 * a22 - a12 * a21;
+                size_t o = (size_t)t * ns + (size_t)k * sr * sr;
+                for (int ri = 0; ri < sr; ++ri)
+                    for (int ci = 0; ci < sr; ++ci, ++o) {
+                        const double u = p.sgx[ri], vv = p.sgx[ci], ww = p.sgw[ri] * p.sgw[ci];
+                        const double zx = u, zy = u * vv, zw = ww * u;
+                        p.singX[o] = a11 * zx + a12 * zy + v[0];
+                        p.singY[o] = a21 * zx + a22 * zy + v[1];
+                        p.singW[o] = det * zw;
+                    }
+            }
+        }
+}
+
+void interpolate_field(const HostPlan& p, const double* h, double* coeff) {
+    const int c2 = p.c2;
+    for (int c = 0; c < p.ncell; ++c)
+        for (int r = 0; r < c2; ++r) {
+            double s = 0;
+            for (int j = 0; j < c2; ++j) s += p.interp[(size_t)r * c2 + j] * (p.sqrtw[j] * h[(size_t)c * c2 + j]);
+            coeff[(size_t)c * c2 + r] = s;
+        }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Quadtree and interaction lists (bbfmm.h:176-447).  Built in creation order, then renumbered
+// level-major (Morton order inside a level) so that every level is one contiguous index range.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct TreeBuilder {
+    HostPlan& p;
+    std::vector<TreeNode> t;
+    int rank, maxLevel, deepest = 0;
+    explicit TreeBuilder(HostPlan& plan) : p(plan), rank(plan.rank), maxLevel(plan.maxLevelArg) {}
+
+    void split(int id) {  // assignChildren, bbfmm.h:250-317
+        if (t[id].npts == 0) {
+            t[id].leaf = t[id].empty = true;
+            return;
+        }
+        if (t[id].npts <= rank || t[id].level == maxLevel) {
+            t[id].leaf = true;
+            deepest = std::max(deepest, t[id].level);
+            return;
+        }
+        int kids[4];
+        for (int c = 0; c < 4; ++c) {
+            TreeNode n;
+            const TreeNode& par = t[id];
+            n.parent = id;
+            n.level = par.level + 1;
+            n.index = c;
+            n.cx = par.cx + ((c & 1) - 0.5) * par.rx;
+            n.cy = par.cy + (((c >> 1) & 1) - 0.5) * par.ry;
+            n.rx = par.rx * 0.5;
+            n.ry = par.ry * 0.5;
+            kids[c] = (int)t.size();
+            t.push_back(n);
+            t[id].child[c] = kids[c];
+        }
+        for (int idx : t[id].pts) {
+            const int xbit = p.nx[idx] < t[id].cx ? 0 : 1, ybit = p.ny[idx] < t[id].cy ? 0 : 1;
+            TreeNode& q = t[kids[2 * ybit + xbit]];
+            q.pts.push_back(idx);
+            q.npts++;
+        }
+        for (int c = 0; c < 4; ++c) split(kids[c]);
+    }
+
+    int locate(double px, double py) const {  // findNode, bbfmm.h:416-429
+        int id = 0;
+        for (;;) {
+            const TreeNode& n = t[id];
+            if (std::fabs(n.cx - px) < kEps && std::fabs(n.cy - py) < kEps) return id;
+            if (n.leaf) return id;
+            const int xbit = n.cx > px ? 0 : 1, ybit = n.cy > py ? 0 : 1;
+            id = n.child[2 * ybit + xbit];
+        }
+    }
+
+    bool adjacent(int a, int b) const {  // isAdjacent, bbfmm.h:431-447
+        const TreeNode &A = t[a], &B = t[b];
+        const double dx = std::fabs(A.cx - B.cx), dy = std::fabs(A.cy - B.cy);
+        const double rx = std::fabs(A.rx + B.rx), ry = std::fabs(A.ry + B.ry);
+        const bool rdx = rx >= dx - kEps, rdy = ry >= dy - kEps;
+        return ((std::fabs(dx - rx) < kEps) && rdy) || ((std::fabs(dy - ry) < kEps) && rdx);
+    }
+
+    static void add_unique(std::vector<int>& v, int x) {
+        if (std::find(v.begin(), v.end(), x) == v.end()) v.push_back(x);
+    }
+
+    void lists(int id, double minx, double miny, double maxx, double maxy) {  // buildNode, bbfmm.h:334-413
+        TreeNode& n = t[id];
+        if (n.parent >= 0) {
+            const TreeNode& par = t[n.parent];
+            const double hx = n.rx, hy = n.ry, x0 = par.cx - hx, y0 = par.cy - hy;
+            for (int xi = -2; xi < 4; ++xi)
+                for (int yi = -2; yi < 4; ++yi) {
+                    const double cx = x0 + 2 * xi * hx, cy = y0 + 2 * yi * hy;
+                    const bool inside = cx <= maxx + kEps && cy <= maxy + kEps && cx >= minx - kEps && cy >= miny - kEps;
+                    const bool self = std::fabs(cx - n.cx) < kEps && std::fabs(cy - n.cy) < kEps;
+                    if (!inside || self) continue;
+                    const int cur = locate(cx, cy);
+                    const bool adj = adjacent(id, cur);
+                    if (t[cur].level < n.level) {
+                        if (adj) {
+                            if (t[cur].leaf) add_unique(n.U, cur);
+                        } else
+                            add_unique(n.X, cur);
+                    }
+                    if (t[cur].level == n.level) {
+                        if (!adj)
+                            add_unique(n.V, cur);
+                        else if (n.leaf) {
+                            std::vector<int> queue{cur};
+                            for (size_t h = 0; h < queue.size(); ++h) {
+                                const int f = queue[h];
+                                if (!adjacent(f, id))
+                                    add_unique(n.W, f);
+                                else if (t[f].leaf)
+                                    add_unique(n.U, f);
+                                else
+                                    for (int c = 0; c < 4; ++c) queue.push_back(t[f].child[c]);
+                            }
+                        }
+                    }
+                }
+        }
+        if (n.leaf) add_unique(n.U, id);  // bbfmm.h:405-407
+    }
+};
+
+}  // namespace
+
+static void build_tree(HostPlan& p) {
+    TreeBuilder B(p);
+    TreeNode root;
+    double xmax = p.nx[0], xmin = p.nx[0], ymax = p.ny[0], ymin = p.ny[0];
+    for (int i = 0; i < p.N; ++i) {  // getCenterRadius, bbfmm.h:231-248 (bounding box of the nodes, Q4)
+        xmax = std::max(xmax, p.nx[i]);
+        xmin = std::min(xmin, p.nx[i]);
+        ymax = std::max(ymax, p.ny[i]);
+        ymin = std::min(ymin, p.ny[i]);
+    }
+    root.cx = (xmax + xmin) / 2.0;
+    root.cy = (ymax + ymin) / 2.0;
+    root.rx = (xmax - xmin) / 2.0;
+    root.ry = (ymax - ymin) / 2.0;
+    root.npts = p.N;
+    root.pts.resize(p.N);
+    for (int i = 0; i < p.N; ++i) root.pts[i] = i;
+    B.t.reserve((size_t)p.N / 2 + 16);
+    B.t.push_back(root);
+    B.split(0);
+    const double minx = B.t[0].cx - B.t[0].rx, miny = B.t[0].cy - B.t[0].ry;
+    const double maxx = B.t[0].cx + B.t[0].rx, maxy = B.t[0].cy + B.t[0].ry;
+    const int nn = (int)B.t.size();
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int i = 0; i < nn; ++i) B.lists(i, minx, miny, maxx, maxy);
+    p.treeMaxLevel = B.deepest;
+
+    // statistics (same order as tests/golden tree_stats)
+    long leaves = 0, su = 0, sv = 0, sw = 0, sx = 0, pairs = 0, mx = 0;
+    for (const TreeNode& n : B.t) {
+        if (n.leaf) {
+            ++leaves;
+            mx = std::max<long>(mx, n.npts);
+            for (int e : n.U) pairs += (long)B.t[e].npts * n.npts;
+            for (int e : n.W) pairs += (long)B.t[e].npts * n.npts;
+        }
+        su += n.U.size();
+        sv += n.V.size();
+        sw += n.W.size();
+        sx += n.X.size();
+    }
+    long st[9] = {nn, leaves, B.deepest, su, sv, sw, sx, pairs, mx};
+    std::copy(st, st + 9, p.stats);
+
+    // renumber: breadth-first with children visited 0..3 => Morton order per level
+    std::vector<int> order, newid(nn, -1);
+    order.reserve(nn);
+    p.level_ptr.assign(1, 0);
+    std::vector<int> cur{0};
+    while (!cur.empty()) {
+        std::vector<int> next;
+        for (int id : cur) {
+            newid[id] = (int)order.size();
+            order.push_back(id);
+            if (!B.t[id].leaf)
+                for (int c = 0; c < 4; ++c) next.push_back(B.t[id].child[c]);
+        }
+        p.level_ptr.push_back((int)order.size());
+        cur.swap(next);
+    }
+    p.nodes.resize(nn);
+    for (int k = 0; k < nn; ++k) {
+        TreeNode n = std::move(B.t[order[k]]);
+        if (n.parent >= 0) n.parent = newid[n.parent];
+        for (int c = 0; c < 4; ++c)
+            if (n.child[c] >= 0) n.child[c] = newid[n.child[c]];
+        for (auto* L : {&n.U, &n.V, &n.W, &n.X})
+            for (int& e : *L) e = newid[e];
+        p.nodes[k] = std::move(n);
+    }
+    // point slots: depth-first leaf order, so that every subtree owns one contiguous slot range
+    p.perm.clear();
+    p.perm.reserve(p.N);
+    p.leaves.clear();
+    std::function<void(int)> dfs = [&](int id) {
+        TreeNode& n = p.nodes[id];
+        n.pt_off = (int)p.perm.size();
+        if (n.leaf) {
+            if (!n.empty) p.leaves.push_back(id);
+            for (int idx : n.pts) p.perm.push_back(idx);
+        } else
+            for (int c = 0; c < 4; ++c) dfs(n.child[c]);
+    };
+    dfs(0);
+    p.inv_perm.assign(p.N, -1);
+    p.leaf_of_slot.assign(p.N, -1);
+    for (int s = 0; s < p.N; ++s) p.inv_perm[p.perm[s]] = s;
+    for (int id : p.leaves)
+        for (int k = 0; k < p.nodes[id].npts; ++k) p.leaf_of_slot[p.nodes[id].pt_off + k] = id;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Chebyshev machinery of kernel::initialize (bbfmm.h:476-505, 597-693)
+// ---------------------------------------------------------------------------------------------
+static double cheb_weight(const HostPlan& p, double x, int m) {  // S(x,m) = (2 sum_k T_k(x) T_k(t_m) - 1)/np
+    const int np = p.np;
+    double s = -1.0, t0 = 1.0, t1 = x;
+    for (int k = 0; k < np; ++k) {
+        double tk = k == 0 ? 1.0 : x;
+        if (k >= 2) {
+            tk = 2.0 * x * t1 - t0;
+            t0 = t1;
+            t1 = tk;
+        }
+        s += 2.0 * tk * p.tnode[(size_t)m * np + k];
+    }
+    return s / np;
+}
+
+static void build_chebyshev(HostPlan& p) {
+    const int np = p.np, r = p.rank;
+    p.cheb.resize(np);
+    p.tnode.resize((size_t)np * np);
+    for (int i = 0; i < np; ++i) p.cheb[i] = -std::cos((i + 0.5) * M_PI / np);
+    for (int m = 0; m < np; ++m)
+        for (int k = 0; k < np; ++k)
+            p.tnode[(size_t)m * np + k] =
+                k == 0 ? 1.0 : k == 1 ? p.cheb[m] : 2.0 * p.cheb[m] * p.tnode[(size_t)m * np + k - 1] - p.tnode[(size_t)m * np + k - 2];
+    // R[c][(i*np+j), (k*np+l)] = S(child node i along y, k) * S(child node j along x, l)   (bbfmm.h:661-693)
+    p.R.assign((size_t)4 * r * r, 0.0);
+    for (int c = 0; c < 4; ++c) {
+        const int bx = c & 1, by = (c >> 1) & 1;
+        for (int i = 0; i < np; ++i)
+            for (int j = 0; j < np; ++j) {
+                const double yi = (by ? 0.5 : -0.5) + 0.5 * p.cheb[i];
+                const double xj = (bx ? 0.5 : -0.5) + 0.5 * p.cheb[j];
+                for (int k = 0; k < np; ++k)
+                    for (int l = 0; l < np; ++l)
+                        p.R[((size_t)c * r + (i * np + j)) * r + (k * np + l)] = cheb_weight(p, yi, k) * cheb_weight(p, xj, l);
+            }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Flattening of the V/X (M2L) and U/W (P2P) lists into block-CSR form
+// ---------------------------------------------------------------------------------------------
+static void finish_csr(BlockCSR& b) {
+    const int groups = (int)b.nrow.size();
+    b.grow_ptr.assign(groups + 1, 0);
+    for (int g = 0; g < groups; ++g) b.grow_ptr[g + 1] = b.grow_ptr[g] + b.nrow[g];
+    b.nrows_total = b.grow_ptr[groups];
+    b.row_group.resize(b.nrows_total);
+    for (int g = 0; g < groups; ++g)
+        for (int k = b.grow_ptr[g]; k < b.grow_ptr[g + 1]; ++k) b.row_group[k] = g;
+}
+
+void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
+    const int r = p.rank, nn = (int)p.nodes.size();
+    std::vector<char> need(nn, 0);
+    for (int k = leaf_begin; k < leaf_end; ++k)
+        for (int id = p.leaves[k]; id >= 0 && !need[id]; id = p.nodes[id].parent) need[id] = 1;
+    BlockCSR m, q;
+    m.uniform_nrow = r;
+    m.ent_ptr.push_back(0);
+    q.ent_ptr.push_back(0);
+    for (int id = 0; id < nn; ++id) {  // level-major order: M2L blocks of one level are contiguous
+        const TreeNode& n = p.nodes[id];
+        if (!need[id] || n.empty || n.parent < 0) continue;
+        int cnt = 0;
+        for (const std::vector<int>* L : {&n.V, &n.X})  // X handled as M2L: Q6
+            for (int s : *L) {
+                if (p.nodes[s].empty) continue;
+                m.col_off.push_back(s * r);
+                m.ncol.push_back(r);
+                m.blk_off.push_back(m.nnz);
+                m.tgt_node.push_back(id);
+                m.src_node.push_back(s);
+                m.nnz += (int64_t)r * r;
+                ++cnt;
+            }
+        if (!cnt) continue;
+        m.row_off.push_back(id * r);
+        m.nrow.push_back(r);
+        m.ent_ptr.push_back((int)m.col_off.size());
+    }
+    for (int k = leaf_begin; k < leaf_end; ++k) {
+        const int id = p.leaves[k];
+        const TreeNode& n = p.nodes[id];
+        for (const std::vector<int>* L : {&n.U, &n.W})  // W handled as P2P: Q6
+            for (int s : *L) {
+                if (p.nodes[s].empty) continue;
+                q.col_off.push_back(p.nodes[s].pt_off);
+                q.ncol.push_back(p.nodes[s].npts);
+                q.blk_off.push_back(q.nnz);
+                q.tgt_node.push_back(id);
+                q.src_node.push_back(s);
+                q.nnz += (int64_t)n.npts * p.nodes[s].npts;
+            }
+        q.row_off.push_back(n.pt_off);
+        q.nrow.push_back(n.npts);
+        q.ent_ptr.push_back((int)q.col_off.size());
+    }
+    finish_csr(m);
+    finish_csr(q);
+    p.m2l = std::move(m);
+    p.p2p = std::move(q);
+}
+
+void partition_leaves(const HostPlan& p, int nranks, std::vector<int>& begin, std::vector<int>& end) {
+    // cost of a leaf = operator doubles streamed for it per apply: its P2P tiles plus its own M2L blocks
+    // (ancestors' M2L blocks are shared by the ranks below them and are small in total).
+    const int nl = (int)p.leaves.size(), r = p.rank;
+    std::vector<double> cost(nl);
+    double total = 0;
+    for (int k = 0; k < nl; ++k) {
+        const TreeNode& n = p.nodes[p.leaves[k]];
+        double c = 0;
+        for (int s : n.U) c += (double)n.npts * p.nodes[s].npts;
+        for (int s : n.W) c += (double)n.npts * p.nodes[s].npts;
+        c += (double)(n.V.size() + n.X.size()) * r * r;
+        cost[k] = c;
+        total += c;
+    }
+    begin.assign(nranks, 0);
+    end.assign(nranks, 0);
+    int k = 0;
+    double acc = 0;
+    for (int rk = 0; rk < nranks; ++rk) {
+        begin[rk] = k;
+        const double target = total * (rk + 1) / nranks;
+        while (k < nl && (rk == nranks - 1 || acc + 0.5 * cost[k] <= target)) acc += cost[k++];
+        end[rk] = k;
+    }
+}
+
+void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, int maxLevel) {
+    if (sz < 1) throw std::runtime_error("geometry_size must be >= 1");
+    if (deg < 1 || deg > 128) throw std::runtime_error("The degree is not implemented.");  // Quadrature.cpp:22189-22191
+    if (sr < 1 || sr > 128) throw std::runtime_error("The degree is not implemented.");
+    if (K < 1) throw std::runtime_error("kernel_size must be >= 1");
+    if (np < 1) throw std::runtime_error("np must be >= 1");
+    if ((double)sz * sz * deg * deg > 2.0e9) throw std::runtime_error("number of nodes exceeds index_t (int)");
+    p = HostPlan();
+    p.sz = sz; p.deg = deg; p.K = K; p.kernelSize = 2 * K - 1; p.g = g; p.sr = sr; p.np = np; p.maxLevelArg = maxLevel;
+    p.dx = 1.0 / sz;
+    p.ncell = sz * sz;
+    p.c2 = deg * deg;
+    p.N = p.ncell * p.c2;
+    p.rq = 16 * p.c2;      // DEFAULT_REFINE_LEVEL 2, Geometry.h:27
+    p.nsing = 8 * sr * sr;
+    p.rank = np * np;      // KernelFactory.cpp:284-286 passes np*np as the leaf capacity
+    build_geometry(p);
+    build_tree(p);
+    build_chebyshev(p);
+    flatten_lists(p, 0, (int)p.leaves.size());
+    for (TreeNode& n : p.nodes) std::vector<int>().swap(n.pts);  // build-time only
+}
+
+}  // namespace an
