@@ -1,0 +1,271 @@
+"""Host-side mirror of the reference's plugin interface for the hot path.
+
+  Aniso            class/@Aniso/Aniso.m:1-34 (new / delete / setCoeff / getNodes / cache / mapping) plus the C++
+                   stage methods of KernelFactory.h:65-75 and GMRES (gmres.h:23), all forwarding to the C-ABI.
+  AnisoWrapper     the string-dispatched MEX gateway AnisoWrapper.cpp:10-138 with its integer-handle session table.
+
+Vectors are numpy float64 arrays in the reference node order.  Nothing here computes: every call lands in
+libaniso_b200.so, which fails with ANISO_ENODEVICE when no CUDA device is present.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+
+def _vec(a, n=None, name="vector"):
+    v = np.ascontiguousarray(np.asarray(a, dtype=np.float64).reshape(-1))
+    if n is not None and v.size != n:
+        raise ValueError("%s has %d entries, expected %d" % (name, v.size, n))
+    return v
+
+
+class Aniso:
+    """Aniso(ds, qr, ks, as, sr, fn, fm) == Aniso(geometry_size, geometry_degree, kernel_size, kernel_g,
+    kernel_degree, np, maxLevel) (Aniso.h:14-15)."""
+
+    def __init__(self, ds, qr, ks, g, sr, fn, fm, nranks=1, rank=0, nccl_uid=None, device=-1):
+        self.L = _lib.load()
+        h = C.c_void_p()
+        # MEX passes doubles and truncates with int(*p) (AnisoWrapper.cpp:22-24)
+        args = (int(ds), int(qr), int(ks), float(g), int(sr), int(fn), int(fm))
+        if nranks == 1:
+            _lib.check(self.L.aniso_create(*args, C.byref(h)))
+        else:
+            buf = C.create_string_buffer(bytes(nccl_uid), 128)
+            _lib.check(self.L.aniso_create_sharded(*args, int(nranks), int(rank), buf, int(device), C.byref(h)))
+        self.h = h
+        self.nranks, self.rank = nranks, rank
+        self.numberOfNodes = self.L.aniso_num_nodes(h)
+        self.kernelSize = self.L.aniso_kernel_size(h)
+        self.sz, self.deg, self.sr, self.np, self.maxLevel = int(ds), int(qr), int(sr), int(fn), int(fm)
+        self.sigma_s = self.sigma_t = None
+
+    # -- life cycle --------------------------------------------------------------------------------------
+    def delete(self):
+        if getattr(self, "h", None):
+            self.L.aniso_destroy(self.h)
+            self.h = None
+
+    close = delete
+
+    def __del__(self):
+        try:
+            self.delete()
+        except Exception:
+            pass
+
+    # -- MEX ops -------------------------------------------------------------------------------------------
+    def getNodes(self):
+        """N x 2 array (x column, y column), AnisoWrapper.cpp:33-44."""
+        x, y, _ = self.nodes()
+        return np.stack([x, y], axis=1)
+
+    def nodes(self):
+        n = self.numberOfNodes
+        x, y, w = np.zeros(n), np.zeros(n), np.zeros(n)
+        _lib.check(self.L.aniso_get_nodes(self.h, x, y, w))
+        return x, y, w
+
+    @property
+    def weights(self):
+        return self.nodes()[2]
+
+    def setCoeff(self, sigma_s, sigma_t):
+        n = self.numberOfNodes
+        self.sigma_s, self.sigma_t = _vec(sigma_s, n, "sigma_s"), _vec(sigma_t, n, "sigma_t")
+        _lib.check(self.L.aniso_set_coeff(self.h, self.sigma_s, self.sigma_t))
+
+    def cache(self, kid):
+        _lib.check(self.L.aniso_cache(self.h, int(kid)))
+
+    def mapping(self, charge, kid):
+        out = np.zeros(self.numberOfNodes)
+        _lib.check(self.L.aniso_mapping(self.h, _vec(charge, self.numberOfNodes, "charge"), int(kid), out))
+        return out
+
+    # -- C++ stage methods (KernelFactory.h:65-75) ---------------------------------------------------------
+    def interpolation(self, f):
+        """interpolation(h, coeff): per-cell Legendre coefficients, returned as (cells, deg^2)."""
+        out = np.zeros(self.numberOfNodes)
+        _lib.check(self.L.aniso_interpolation(self.h, _vec(f, self.numberOfNodes), out))
+        return out.reshape(-1, self.deg * self.deg)
+
+    def runKernelsFast(self, kid, f):
+        ret = np.zeros(self.numberOfNodes)
+        _lib.check(self.L.aniso_run_kernels_fast(self.h, int(kid), _vec(f, self.numberOfNodes), ret))
+        return ret
+
+    def runKernelsFastSing(self, kid, f):
+        ret = np.zeros(self.numberOfNodes)
+        _lib.check(self.L.aniso_run_kernels_fast_sing(self.h, int(kid), _vec(f, self.numberOfNodes), ret))
+        return ret
+
+    def nearRemoval(self, kid, f, ret):
+        _lib.check(self.L.aniso_near_removal(self.h, int(kid), _vec(f, self.numberOfNodes), ret))
+        return ret
+
+    def refineAddOnFast(self, kid, f, ret):
+        _lib.check(self.L.aniso_refine_add_on_fast(self.h, int(kid), _vec(f, self.numberOfNodes), ret))
+        return ret
+
+    def singularAddFast(self, kid, fcoeff, ret):
+        _lib.check(self.L.aniso_singular_add_fast(self.h, int(kid), _vec(fcoeff, self.numberOfNodes), ret))
+        return ret
+
+    def mapping_stages(self, charge, kid):
+        """The body of MEX 'mapping' (AnisoWrapper.cpp:111-130) stage by stage, for stage-wise parity tests."""
+        charge = _vec(charge, self.numberOfNodes)
+        scaled = charge * self.weights
+        coeff = self.interpolation(charge)
+        o = {"imag_fmm": self.runKernelsFast(kid, scaled)}
+        t = self.runKernelsFastSing(kid, scaled)
+        o["real_fmm"] = t.copy()
+        o["k7"] = self.nearRemoval(kid, scaled, t).copy()
+        o["k8"] = self.refineAddOnFast(kid, scaled, t).copy()
+        o["k9"] = self.singularAddFast(kid, coeff, t).copy()
+        o["out"] = (t + o["imag_fmm"]) * (1.0 / np.pi / 2.0)
+        return o
+
+    def displayKernelCacheSize(self):
+        """Aniso.cpp:19-47: megabytes held per kernel id."""
+        return {k: self.L.aniso_cache_bytes(self.h, k) / 1e6 for k in range(self.kernelSize)}
+
+    # -- GMRES (gmres.cpp:53-169 with the operator of main.cpp:123-136) ---------------------------------------
+    def gmres(self, b, x0=None, m=80, max_iter=400, tol=1e-12):
+        n = self.numberOfNodes
+        x = np.zeros(n) if x0 is None else _vec(x0, n).copy()
+        it = C.c_int(0)
+        hist = np.zeros(max_iter + 2)
+        rc = _lib.check(self.L.aniso_gmres(self.h, _vec(b, n), x, int(m), int(max_iter), float(tol), C.byref(it), hist,
+                                           hist.size))
+        return x, rc, it.value, hist[: it.value + 1]
+
+    # -- probes / introspection ---------------------------------------------------------------------------------
+    def line_integral(self, pts4):
+        p = np.ascontiguousarray(np.asarray(pts4, np.float64).reshape(-1, 4))
+        out = np.zeros(len(p))
+        _lib.check(self.L.aniso_line_integral(self.h, len(p), p.reshape(-1), out))
+        return out
+
+    def kernel_eval(self, kid, part, pts4):
+        p = np.ascontiguousarray(np.asarray(pts4, np.float64).reshape(-1, 4))
+        out = np.zeros(len(p))
+        _lib.check(self.L.aniso_kernel_eval(self.h, int(kid), int(part), len(p), p.reshape(-1), out))
+        return out
+
+    def sigma_coeff(self):
+        c = self.deg * self.deg
+        ct, cs = np.zeros(self.numberOfNodes), np.zeros(self.numberOfNodes)
+        _lib.check(self.L.aniso_sigma_coeff(self.h, ct, cs))
+        return ct.reshape(-1, c), cs.reshape(-1, c)
+
+    def tree_stats(self):
+        o = np.zeros(9, np.int64)
+        _lib.check(self.L.aniso_tree_stats(self.h, o))
+        return dict(zip(("nodes", "leaves", "max_level", "sumU", "sumV", "sumW", "sumX", "p2p_pairs", "max_leaf"),
+                        (int(v) for v in o)))
+
+    def tree_nodes(self):
+        n = self.L.aniso_tree_nodes(self.h, 0, np.zeros(4), np.zeros(4, np.int32))
+        geom, info = np.zeros(4 * n), np.zeros(4 * n, np.int32)
+        self.L.aniso_tree_nodes(self.h, n, geom, info)
+        return geom.reshape(n, 4), info.reshape(n, 4)
+
+    def node_lists(self, node):
+        ids, kinds = np.zeros(512, np.int32), np.zeros(512, np.int32)
+        c = _lib.check(self.L.aniso_node_lists(self.h, int(node), 512, ids, kinds))
+        return ids[:c].copy(), kinds[:c].copy()
+
+    def geometry_tables(self):
+        c = self.deg * self.deg
+        r = 16 * c
+        o = dict(interpolate=np.zeros(c * c), nearMapping=np.zeros(r * c), legendreNorms=np.zeros(c), rqx=np.zeros(r),
+                 rqy=np.zeros(r), rw=np.zeros(r))
+        _lib.check(self.L.aniso_geometry_tables(self.h, o["interpolate"], o["nearMapping"], o["legendreNorms"],
+                                                o["rqx"], o["rqy"], o["rw"]))
+        o["interpolate"] = o["interpolate"].reshape(c, c)
+        o["nearMapping"] = o["nearMapping"].reshape(r, c)
+        return o
+
+    def sing_tables(self):
+        c, m = self.deg * self.deg, 8 * self.sr * self.sr
+        sx, sy, sw = np.zeros(c * m), np.zeros(c * m), np.zeros(c * m)
+        _lib.check(self.L.aniso_sing_tables(self.h, sx, sy, sw))
+        return sx.reshape(c, m), sy.reshape(c, m), sw.reshape(c, m)
+
+    def slot_permutation(self):
+        p = np.zeros(self.numberOfNodes, np.int32)
+        _lib.check(self.L.aniso_slot_permutation(self.h, p))
+        return p
+
+    def partition(self, nranks, rank):
+        b, e, nl = C.c_int(), C.c_int(), C.c_int()
+        _lib.check(self.L.aniso_partition(self.h, nranks, rank, C.byref(b), C.byref(e), C.byref(nl)))
+        return b.value, e.value, nl.value
+
+    def owned_range(self):
+        b, e = C.c_int(), C.c_int()
+        _lib.check(self.L.aniso_owned_range(self.h, C.byref(b), C.byref(e)))
+        return b.value, e.value
+
+    def launch_count(self):
+        return int(self.L.aniso_launch_count(self.h))
+
+    def apply_bytes(self):
+        o = np.zeros(3, np.int64)
+        _lib.check(self.L.aniso_apply_bytes(self.h, o))
+        return dict(p2p=int(o[0]), m2l=int(o[1]), stencil=int(o[2]))
+
+    def cache_counts(self):
+        o = np.zeros(2, np.int64)
+        _lib.check(self.L.aniso_cache_counts(self.h, o))
+        return dict(p2p=int(o[0]), m2l=int(o[1]))
+
+    def time_kernel(self, kid, which, reps):
+        ms = C.c_double()
+        _lib.check(self.L.aniso_time_kernel(self.h, int(kid), int(which), int(reps), C.byref(ms)))
+        return ms.value
+
+    def synchronize(self):
+        _lib.check(self.L.aniso_synchronize(self.h))
+
+
+def gl_table(deg):
+    x, w = np.zeros(max(deg, 0)), np.zeros(max(deg, 0))
+    _lib.check(_lib.load().aniso_gl_table(int(deg), x, w))
+    return x, w
+
+
+class _Session:
+    """Session<Aniso> of mexplus (dispatch.h:183-275): integer handles into a static table."""
+    table = {}
+    next_id = 1
+
+
+def AnisoWrapper(op, *args):
+    """String-dispatched gateway with the six ops of AnisoWrapper.cpp:10-136."""
+    if op == "new":
+        if len(args) != 7:
+            raise TypeError("AnisoWrapper('new', ds, qr, ks, as, sr, fn, fm)")
+        hid = _Session.next_id
+        _Session.next_id += 1
+        _Session.table[hid] = Aniso(*args)
+        return hid
+    if op not in ("delete", "getNodes", "setCoeff", "cache", "mapping"):
+        raise KeyError("Invalid operation: %s" % op)  # mexplus dispatch.h:302-317
+    if not args or args[0] not in _Session.table:
+        raise KeyError("Invalid id %r" % (args[0] if args else None))  # dispatch.h:207-215
+    a = _Session.table[args[0]]
+    if op == "delete":
+        a.delete()
+        del _Session.table[args[0]]
+        return None
+    if op == "getNodes":
+        return a.getNodes()
+    if op == "setCoeff":
+        return a.setCoeff(args[1], args[2])
+    if op == "cache":
+        return a.cache(int(args[1]))
+    return a.mapping(args[1], int(args[2])).reshape(-1, 1)

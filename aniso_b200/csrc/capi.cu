@@ -1,0 +1,987 @@
+// C-ABI of the B200-native aniso hot path (include/aniso_b200.h): owns all device state of one handle and
+// sequences the kernels of kernels.cu / vecops.cu.  No CPU fallback anywhere on this path.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "../../include/aniso_b200.h"
+#include "device.cuh"
+#include "nccl_dyn.hpp"
+#include "plan.hpp"
+
+using namespace an;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            throw std::runtime_error(std::string(#call) + ": " + cudaGetErrorString(e_));                \
+    } while (0)
+
+struct OperatorCache {  // Cache[node][slot] of bbfmm.h:466, flattened
+    double* p2p = nullptr;
+    double* m2l = nullptr;
+};
+struct StencilCache {
+    double *c7 = nullptr, *c8 = nullptr, *c9 = nullptr, *call = nullptr;
+};
+
+struct aniso_handle {
+    HostPlan plan;
+    int nranks = 1, rank = 0, device = -1;
+    int leaf_begin = 0, leaf_end = 0, slot0 = 0, nown = 0;
+    std::vector<int> all_slot_begin, all_slot_end;  // ownership of every rank
+    bool dev_ready = false, coeff_set = false;
+    cudaStream_t st = nullptr;
+    std::vector<void*> allocs;
+    DevTree T;
+    DevGeom G;
+    DevCSR m2l, p2p;
+    SigmaGrid S;
+    std::vector<double> sigma_s, sigma_t, coeff_t, coeff_s;  // host copies (reference order / cell-major)
+    double *d_sig_s = nullptr, *d_chat = nullptr, *d_lnorm = nullptr;
+    int* d_leaf_of_slot = nullptr;
+    int first_m2l_level = 0;
+    // work vectors
+    double *d_f = nullptr, *d_q = nullptr, *d_mcharge = nullptr, *d_mpot = nullptr, *d_pot = nullptr;
+    double *d_fmm = nullptr, *d_corr = nullptr, *d_a = nullptr, *d_b = nullptr, *d_xfull = nullptr, *d_stage = nullptr;
+    double* pinned = nullptr;  // 2N doubles
+    std::map<std::pair<int, int>, OperatorCache> ops;
+    std::map<int, StencilCache> stencils;
+    int64_t launches = 0;
+    int64_t fill_counts[2] = {0, 0};
+    DotWork dot;
+    double* d_scal = nullptr;  // Hessenberg column / scalars on device
+    NcclApi* nccl = nullptr;
+    ncclComm_t comm = nullptr;
+    unsigned char uid[128];
+};
+
+namespace {
+
+template <class T>
+T* dalloc(aniso_handle* h, size_t n) {
+    T* p = nullptr;
+    CK(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+    h->allocs.push_back(p);
+    return p;
+}
+template <class T>
+T* upload(aniso_handle* h, const std::vector<T>& v) {
+    T* p = dalloc<T>(h, v.size());
+    if (!v.empty()) CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, h->st));
+    return p;
+}
+void dfree(aniso_handle* h, void* p) {
+    if (!p) return;
+    auto it = std::find(h->allocs.begin(), h->allocs.end(), p);
+    if (it != h->allocs.end()) h->allocs.erase(it);
+    cudaFree(p);
+}
+
+DevCSR upload_csr(aniso_handle* h, const BlockCSR& b) {
+    DevCSR d;
+    d.groups = (int)b.nrow.size();
+    d.entries = (int)b.col_off.size();
+    d.nrows_total = b.nrows_total;
+    d.uniform_nrow = b.uniform_nrow;
+    d.nnz = b.nnz;
+    d.row_off = upload(h, b.row_off);
+    d.nrow = upload(h, b.nrow);
+    d.ent_ptr = upload(h, b.ent_ptr);
+    d.col_off = upload(h, b.col_off);
+    d.ncol = upload(h, b.ncol);
+    d.blk_off = upload(h, b.blk_off);
+    d.tgt_node = upload(h, b.tgt_node);
+    d.src_node = upload(h, b.src_node);
+    d.grow_ptr = upload(h, b.grow_ptr);
+    d.row_group = upload(h, b.row_group);
+    return d;
+}
+
+void ensure_device(aniso_handle* h) {
+    if (h->dev_ready) return;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        throw std::domain_error("no CUDA device available (aniso_b200 has no CPU fallback)");
+    }
+    if (h->device < 0) CK(cudaGetDevice(&h->device));
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+    const HostPlan& p = h->plan;
+    const int N = p.N, nn = (int)p.nodes.size(), r = p.rank;
+    // geometry in slot order
+    std::vector<double> sx(N), sy(N), sw(N);
+    for (int s = 0; s < N; ++s) {
+        sx[s] = p.nx[p.perm[s]];
+        sy[s] = p.ny[p.perm[s]];
+        sw[s] = p.w[p.perm[s]];
+    }
+    DevGeom& G = h->G;
+    G.sz = p.sz; G.deg = p.deg; G.c2 = p.c2; G.rq = p.rq; G.nsing = p.nsing; G.N = N; G.dx = p.dx;
+    G.px = upload(h, sx); G.py = upload(h, sy); G.pw = upload(h, sw);
+    G.perm = upload(h, p.perm); G.inv_perm = upload(h, p.inv_perm);
+    G.sqrtw = upload(h, p.sqrtw); G.interp = upload(h, p.interp); G.lnorm = upload(h, p.lnorm);
+    G.nearMap = upload(h, p.nearMap); G.rqx = upload(h, p.rqx); G.rqy = upload(h, p.rqy); G.rqw = upload(h, p.rqw);
+    G.singX = upload(h, p.singX); G.singY = upload(h, p.singY); G.singW = upload(h, p.singW);
+    h->d_lnorm = const_cast<double*>(G.lnorm);
+    // tree
+    std::vector<double> cx(nn), cy(nn), rx(nn), ry(nn);
+    std::vector<int> parent(nn), index(nn), child(4 * nn), pt_off(nn), npts(nn);
+    std::vector<unsigned char> flags(nn);
+    for (int i = 0; i < nn; ++i) {
+        const TreeNode& n = p.nodes[i];
+        cx[i] = n.cx; cy[i] = n.cy; rx[i] = n.rx; ry[i] = n.ry;
+        parent[i] = n.parent; index[i] = n.index; pt_off[i] = n.pt_off; npts[i] = n.npts;
+        for (int c = 0; c < 4; ++c) child[4 * i + c] = n.child[c];
+        flags[i] = (n.leaf ? 1 : 0) | (n.empty ? 2 : 0);
+    }
+    DevTree& T = h->T;
+    T.nnodes = nn; T.np = p.np; T.r = r; T.nlevels = (int)p.level_ptr.size() - 1;
+    T.cx = upload(h, cx); T.cy = upload(h, cy); T.rx = upload(h, rx); T.ry = upload(h, ry);
+    T.parent = upload(h, parent); T.index = upload(h, index); T.child = upload(h, child);
+    T.pt_off = upload(h, pt_off); T.npts = upload(h, npts); T.flags = upload(h, flags);
+    T.cheb = upload(h, p.cheb); T.tnode = upload(h, p.tnode); T.R = upload(h, p.R);
+    T.leaves = upload(h, p.leaves); T.nleaves = (int)p.leaves.size();
+    h->d_leaf_of_slot = upload(h, p.leaf_of_slot);
+    h->m2l = upload_csr(h, p.m2l);
+    h->p2p = upload_csr(h, p.p2p);
+    h->first_m2l_level = T.nlevels;
+    for (int t : p.m2l.tgt_node) h->first_m2l_level = std::min(h->first_m2l_level, p.nodes[t].level);
+    // sigma grid
+    h->d_chat = dalloc<double>(h, N);
+    h->d_sig_s = dalloc<double>(h, N);
+    SigmaGrid& S = h->S;
+    S.sz = p.sz; S.deg = p.deg; S.c2 = p.c2; S.h = p.dx;  // cell edge k sits at k*dx (KernelFactory.cpp:71-72: k / (1/dx))
+    S.chat = h->d_chat; S.glx = upload(h, p.glx); S.glw = upload(h, p.glw);
+    // work space
+    h->d_f = dalloc<double>(h, N); h->d_q = dalloc<double>(h, N); h->d_pot = dalloc<double>(h, N);
+    h->d_fmm = dalloc<double>(h, N); h->d_corr = dalloc<double>(h, N); h->d_a = dalloc<double>(h, N);
+    h->d_b = dalloc<double>(h, N); h->d_xfull = dalloc<double>(h, N); h->d_stage = dalloc<double>(h, N);
+    h->d_mcharge = dalloc<double>(h, (size_t)nn * r);
+    h->d_mpot = dalloc<double>(h, (size_t)nn * r);
+    CK(cudaMemsetAsync(h->d_mcharge, 0, (size_t)nn * r * sizeof(double), h->st));
+    CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)nn * r * sizeof(double), h->st));
+    CK(cudaMemsetAsync(h->d_pot, 0, (size_t)N * sizeof(double), h->st));
+    CK(cudaMallocHost(&h->pinned, (size_t)2 * N * sizeof(double)));
+    h->dot.blocks = 1184;  // 148 SMs x 8
+    h->dot.partial = dalloc<double>(h, h->dot.blocks);
+    h->dot.counter = dalloc<unsigned int>(h, 1);
+    CK(cudaMemsetAsync(h->dot.counter, 0, sizeof(unsigned int), h->st));
+    h->d_scal = dalloc<double>(h, 1024);
+    if (h->nranks > 1) {
+        h->nccl = load_nccl();
+        if (!h->nccl) throw std::runtime_error("libnccl.so.2 could not be loaded");
+        ncclUniqueId id;
+        static_assert(sizeof(id) == 128, "ncclUniqueId size");
+        std::memcpy(&id, h->uid, 128);
+        ncclResult_t rc = h->nccl->CommInitRank(&h->comm, h->nranks, id, h->rank);
+        if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclCommInitRank: ") + h->nccl->GetErrorString(rc));
+    }
+    CK(cudaStreamSynchronize(h->st));
+    h->dev_ready = true;
+}
+
+}  // namespace
+
+#define API_BEGIN try {
+#define API_END                                                    \
+    }                                                              \
+    catch (const std::domain_error& e) {                           \
+        return fail(ANISO_ENODEVICE, e.what());                    \
+    }                                                              \
+    catch (const std::bad_alloc&) {                                \
+        return fail(ANISO_ENOMEM, "out of host memory");           \
+    }                                                              \
+    catch (const std::invalid_argument& e) {                       \
+        return fail(ANISO_EINVAL, e.what());                       \
+    }                                                              \
+    catch (const std::logic_error& e) {                            \
+        return fail(ANISO_ESTATE, e.what());                       \
+    }                                                              \
+    catch (const std::exception& e) {                              \
+        return fail(ANISO_ECUDA, e.what());                        \
+    }
+#define REQUIRE(cond, msg) \
+    if (!(cond)) throw std::invalid_argument(msg)
+#define LAUNCH(h, call) \
+    do {                \
+        call;           \
+        ++(h)->launches; \
+    } while (0)
+
+extern "C" {
+
+const char* aniso_last_error(void) { return g_err.c_str(); }
+const char* aniso_version(void) { return "aniso_b200 0.1 (sm_100a)"; }
+
+int aniso_gl_table(int degree, double* x, double* w) {
+    if (!x || !w) return fail(ANISO_EINVAL, "null pointer");
+    if (!gl_table(degree, x, w)) return fail(ANISO_EINVAL, "The degree is not implemented.");
+    return ANISO_OK;
+}
+
+int aniso_nccl_unique_id(void* out128) {
+    API_BEGIN
+    REQUIRE(out128, "null pointer");
+    NcclApi* api = load_nccl();
+    if (!api) return fail(ANISO_ENCCL, "libnccl.so.2 could not be loaded");
+    ncclUniqueId id;
+    ncclResult_t rc = api->GetUniqueId(&id);
+    if (rc != ncclSuccess) return fail(ANISO_ENCCL, api->GetErrorString(rc));
+    std::memcpy(out128, &id, 128);
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_create_sharded(int sz, int deg, int K, double g, int sr, int np, int maxLevel, int nranks, int rank,
+                         const void* uid, int device, aniso_t** out) {
+    API_BEGIN
+    REQUIRE(out, "null output pointer");
+    REQUIRE(nranks >= 1 && rank >= 0 && rank < nranks, "bad rank / nranks");
+    REQUIRE(nranks == 1 || uid, "nccl_unique_id required for nranks > 1");
+    aniso_handle* h = new aniso_handle();
+    try {
+        build_plan(h->plan, sz, deg, K, g, sr, np, maxLevel);
+    } catch (const std::exception& e) {
+        delete h;
+        throw std::invalid_argument(e.what());
+    }
+    h->nranks = nranks;
+    h->rank = rank;
+    h->device = device;
+    if (uid) std::memcpy(h->uid, uid, 128);
+    std::vector<int> lb, le;
+    partition_leaves(h->plan, nranks, lb, le);
+    h->all_slot_begin.resize(nranks);
+    h->all_slot_end.resize(nranks);
+    const HostPlan& p = h->plan;
+    for (int r = 0; r < nranks; ++r) {
+        h->all_slot_begin[r] = lb[r] < (int)p.leaves.size() ? p.nodes[p.leaves[lb[r]]].pt_off : p.N;
+        h->all_slot_end[r] = le[r] > lb[r] ? p.nodes[p.leaves[le[r] - 1]].pt_off + p.nodes[p.leaves[le[r] - 1]].npts
+                                           : h->all_slot_begin[r];
+    }
+    h->leaf_begin = lb[rank];
+    h->leaf_end = le[rank];
+    h->slot0 = h->all_slot_begin[rank];
+    h->nown = h->all_slot_end[rank] - h->slot0;
+    if (nranks > 1) flatten_lists(h->plan, h->leaf_begin, h->leaf_end);
+    *out = h;
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_create(int sz, int deg, int K, double g, int sr, int np, int maxLevel, aniso_t** out) {
+    return aniso_create_sharded(sz, deg, K, g, sr, np, maxLevel, 1, 0, nullptr, -1, out);
+}
+
+int aniso_destroy(aniso_t* h) {
+    if (!h) return ANISO_OK;
+    if (h->dev_ready) {
+        cudaSetDevice(h->device);
+        cudaStreamSynchronize(h->st);
+        if (h->comm && h->nccl) h->nccl->CommDestroy(h->comm);
+        for (void* p : h->allocs) cudaFree(p);
+        if (h->pinned) cudaFreeHost(h->pinned);
+        cudaStreamDestroy(h->st);
+    }
+    delete h;
+    return ANISO_OK;
+}
+
+int aniso_num_nodes(const aniso_t* h) { return h ? h->plan.N : fail(ANISO_EINVAL, "null handle"); }
+int aniso_kernel_size(const aniso_t* h) { return h ? h->plan.kernelSize : fail(ANISO_EINVAL, "null handle"); }
+
+int aniso_get_nodes(const aniso_t* h, double* x, double* y, double* w) {
+    if (!h) return fail(ANISO_EINVAL, "null handle");
+    const size_t b = sizeof(double) * h->plan.N;
+    if (x) std::memcpy(x, h->plan.nx.data(), b);
+    if (y) std::memcpy(y, h->plan.ny.data(), b);
+    if (w) std::memcpy(w, h->plan.w.data(), b);
+    return ANISO_OK;
+}
+
+int aniso_geometry_tables(const aniso_t* h, double* interp, double* nearMap, double* lnorm, double* rx, double* ry,
+                          double* rw) {
+    if (!h) return fail(ANISO_EINVAL, "null handle");
+    const HostPlan& p = h->plan;
+    auto cp = [](double* d, const std::vector<double>& v) {
+        if (d) std::memcpy(d, v.data(), v.size() * sizeof(double));
+    };
+    cp(interp, p.interp); cp(nearMap, p.nearMap); cp(lnorm, p.lnorm); cp(rx, p.rqx); cp(ry, p.rqy); cp(rw, p.rqw);
+    return ANISO_OK;
+}
+
+int aniso_sing_tables(const aniso_t* h, double* sx, double* sy, double* sw) {
+    if (!h) return fail(ANISO_EINVAL, "null handle");
+    const HostPlan& p = h->plan;
+    if (sx) std::memcpy(sx, p.singX.data(), p.singX.size() * sizeof(double));
+    if (sy) std::memcpy(sy, p.singY.data(), p.singY.size() * sizeof(double));
+    if (sw) std::memcpy(sw, p.singW.data(), p.singW.size() * sizeof(double));
+    return ANISO_OK;
+}
+
+int aniso_tree_stats(const aniso_t* h, int64_t out[9]) {
+    if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
+    for (int i = 0; i < 9; ++i) out[i] = h->plan.stats[i];
+    return ANISO_OK;
+}
+
+int aniso_tree_nodes(const aniso_t* h, int cap, double* geom, int* info) {
+    if (!h) return fail(ANISO_EINVAL, "null handle");
+    const HostPlan& p = h->plan;
+    const int nn = (int)p.nodes.size();
+    for (int i = 0; i < nn && i < cap; ++i) {
+        const TreeNode& n = p.nodes[i];
+        if (geom) { geom[4 * i] = n.cx; geom[4 * i + 1] = n.cy; geom[4 * i + 2] = n.rx; geom[4 * i + 3] = n.ry; }
+        if (info) { info[4 * i] = n.level; info[4 * i + 1] = n.leaf; info[4 * i + 2] = n.npts; info[4 * i + 3] = n.parent; }
+    }
+    return nn;
+}
+
+int aniso_node_lists(const aniso_t* h, int node, int cap, int* ids, int* kinds) {
+    if (!h || node < 0 || node >= (int)h->plan.nodes.size()) return fail(ANISO_EINVAL, "bad node");
+    const TreeNode& n = h->plan.nodes[node];
+    int c = 0;
+    const std::vector<int>* L[4] = {&n.V, &n.X, &n.U, &n.W};
+    for (int kind = 0; kind < 4; ++kind)
+        for (int e : *L[kind]) {
+            if (c < cap) {
+                if (ids) ids[c] = e;
+                if (kinds) kinds[c] = kind;
+            }
+            ++c;
+        }
+    return c;
+}
+
+int aniso_slot_permutation(const aniso_t* h, int* perm) {
+    if (!h || !perm) return fail(ANISO_EINVAL, "null pointer");
+    std::memcpy(perm, h->plan.perm.data(), sizeof(int) * h->plan.N);
+    return ANISO_OK;
+}
+
+int aniso_partition(const aniso_t* h, int nranks, int rank, int* slot_begin, int* slot_end, int* nleaves) {
+    API_BEGIN
+    REQUIRE(h && nranks >= 1 && rank >= 0 && rank < nranks, "bad arguments");
+    std::vector<int> lb, le;
+    partition_leaves(h->plan, nranks, lb, le);
+    const HostPlan& p = h->plan;
+    const int b = lb[rank] < (int)p.leaves.size() ? p.nodes[p.leaves[lb[rank]]].pt_off : p.N;
+    const int e = le[rank] > lb[rank] ? p.nodes[p.leaves[le[rank] - 1]].pt_off + p.nodes[p.leaves[le[rank] - 1]].npts : b;
+    if (slot_begin) *slot_begin = b;
+    if (slot_end) *slot_end = e;
+    if (nleaves) *nleaves = le[rank] - lb[rank];
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_owned_range(const aniso_t* h, int* slot_begin, int* slot_end) {
+    if (!h) return fail(ANISO_EINVAL, "null handle");
+    if (slot_begin) *slot_begin = h->slot0;
+    if (slot_end) *slot_end = h->slot0 + h->nown;
+    return ANISO_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// compute path
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+void free_caches(aniso_handle* h) {
+    for (auto& kv : h->ops) {
+        dfree(h, kv.second.p2p);
+        dfree(h, kv.second.m2l);
+    }
+    h->ops.clear();
+    for (auto& kv : h->stencils) {
+        dfree(h, kv.second.c7); dfree(h, kv.second.c8); dfree(h, kv.second.c9); dfree(h, kv.second.call);
+    }
+    h->stencils.clear();
+}
+
+void check_id(const aniso_handle* h, int id) {
+    if (id < 0 || id >= h->plan.kernelSize) throw std::invalid_argument("kernel id out of range");
+}
+
+// runKernelsCache / runKernelsCacheSing (KernelFactory.cpp:323-334, 279-288): evaluate every operator block
+OperatorCache& ensure_ops(aniso_handle* h, int id, int part) {
+    auto key = std::make_pair(id, part);
+    auto it = h->ops.find(key);
+    if (it != h->ops.end()) return it->second;
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede cache/mapping");
+    OperatorCache c;
+    c.p2p = dalloc<double>(h, (size_t)h->p2p.nnz);
+    c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz);
+    LAUNCH(h, launch_fill(h->p2p, h->T, h->G, h->S, id, part, 0, c.p2p, h->st));
+    LAUNCH(h, launch_fill(h->m2l, h->T, h->G, h->S, id, part, 1, c.m2l, h->st));
+    CK(cudaGetLastError());
+    h->fill_counts[0] = h->p2p.nnz;
+    h->fill_counts[1] = h->m2l.nnz;
+    return h->ops[key] = c;
+}
+
+// refineAddOnCache + singularAddCache (KernelFactory.cpp:550-609, 752-788), plus the K7 table
+StencilCache& ensure_stencils(aniso_handle* h, int id) {
+    auto it = h->stencils.find(id);
+    if (it != h->stencils.end()) return it->second;
+    const size_t n9 = (size_t)9 * h->G.c2 * h->nown;
+    StencilCache s;
+    s.c7 = dalloc<double>(h, n9);
+    s.c8 = dalloc<double>(h, n9);
+    s.call = dalloc<double>(h, n9);
+    s.c9 = dalloc<double>(h, (size_t)h->G.c2 * h->nown);
+    LAUNCH(h, launch_build_stencils(h->G, id, h->slot0, h->nown, s.c7, s.c8, s.c9, h->st));
+    LAUNCH(h, launch_combine_stencils(h->G, h->slot0, h->nown, s.c7, s.c8, s.c9, s.call, h->st));
+    CK(cudaGetLastError());
+    return h->stencils[id] = s;
+}
+
+// kernel::runFast (bbfmm.h:565-592): upPass + downPassFast from the cached operators.
+// q: scaled source, full vector in slot order.  out: owned range.
+void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* out) {
+    const HostPlan& p = h->plan;
+    const DevTree& T = h->T;
+    const int L0 = h->first_m2l_level;
+    LAUNCH(h, launch_p2m(T, h->G, q, h->d_mcharge, h->st));
+    for (int L = T.nlevels - 2; L >= L0; --L)
+        LAUNCH(h, launch_m2m(T, p.level_ptr[L], p.level_ptr[L + 1] - p.level_ptr[L], h->d_mcharge, h->st));
+    CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
+    LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, h->st));
+    for (int L = L0 + 1; L < T.nlevels; ++L)
+        LAUNCH(h, launch_l2l(T, p.level_ptr[L], p.level_ptr[L + 1] - p.level_ptr[L], h->d_mpot, h->st));
+    LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, h->st));
+    LAUNCH(h, launch_l2p(T, h->G, h->d_leaf_of_slot, h->slot0, h->nown, h->d_mpot, h->d_pot, out, h->st));
+}
+
+// all-gather of the owned shards into a full slot-order vector; counts differ per rank, so this is a
+// grouped broadcast per owner
+void allgather_slots(aniso_handle* h, const double* shard, double* full) {
+    if (h->nranks == 1) {
+        if (shard != full) CK(cudaMemcpyAsync(full, shard, sizeof(double) * h->plan.N, cudaMemcpyDeviceToDevice, h->st));
+        return;
+    }
+    NcclApi* a = h->nccl;
+    a->GroupStart();
+    for (int r = 0; r < h->nranks; ++r) {
+        const int b = h->all_slot_begin[r], n = h->all_slot_end[r] - b;
+        if (n == 0) continue;
+        ncclResult_t rc = a->Broadcast(r == h->rank ? shard : full + b, full + b, n, ncclDouble, r, h->comm, h->st);
+        if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclBroadcast: ") + a->GetErrorString(rc));
+    }
+    ncclResult_t rc = a->GroupEnd();
+    if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclGroupEnd: ") + a->GetErrorString(rc));
+}
+
+void allreduce_scalars(aniso_handle* h, double* d, int n) {
+    if (h->nranks == 1) return;
+    ncclResult_t rc = h->nccl->AllReduce(d, d, n, ncclDouble, ncclSum, h->comm, h->st);
+    if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce: ") + h->nccl->GetErrorString(rc));
+}
+
+// mapping in slot order: full source (unscaled) -> owned rows
+void mapping_slots(aniso_handle* h, const double* f_full, int id, const double* sig_s, const double* x_own, double* out,
+                   int subtract) {
+    OperatorCache& c = ensure_ops(h, id, PART_BOTH);
+    StencilCache& s = ensure_stencils(h, id);
+    const double* f = f_full;
+    if (sig_s) {
+        LAUNCH(h, launch_scale(h->plan.N, f_full, sig_s, h->G.pw, h->d_f, h->d_q, h->st));
+        f = h->d_f;
+    } else
+        LAUNCH(h, launch_scale(h->plan.N, f_full, nullptr, h->G.pw, nullptr, h->d_q, h->st));
+    run_fmm(h, c, h->d_q, h->d_fmm);
+    LAUNCH(h, launch_stencil_apply(h->G, h->slot0, h->nown, s.call, f, h->d_corr, 0, h->st));
+    LAUNCH(h, launch_finalize(h->nown, h->d_fmm, h->d_corr, x_own, out, subtract, h->st));
+}
+
+// host vector (N doubles) -> h->d_stage through the pinned buffer; the stream is drained first so the pinned
+// buffer is never rewritten under an in-flight copy
+void stage_h2d(aniso_handle* h, const double* host) {
+    const int N = h->plan.N;
+    CK(cudaStreamSynchronize(h->st));
+    std::memcpy(h->pinned, host, sizeof(double) * N);
+    CK(cudaMemcpyAsync(h->d_stage, h->pinned, sizeof(double) * N, cudaMemcpyHostToDevice, h->st));
+}
+
+// host (reference order) -> device slot order, full vector
+void to_slots(aniso_handle* h, const double* host, double* dev) {
+    const int N = h->plan.N;
+    stage_h2d(h, host);
+    LAUNCH(h, launch_gather(N, h->d_stage, h->G.perm, dev, h->st));
+}
+// device owned rows (slot order) -> host reference order; rows owned by other ranks are left untouched
+void from_slots(aniso_handle* h, const double* dev_own, double* host) {
+    const HostPlan& p = h->plan;
+    double* stage = h->pinned + p.N;
+    CK(cudaMemcpyAsync(stage, dev_own, sizeof(double) * h->nown, cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    for (int k = 0; k < h->nown; ++k) host[p.perm[h->slot0 + k]] = stage[k];
+}
+
+}  // namespace
+
+extern "C" {
+
+int aniso_set_coeff(aniso_t* h, const double* sigma_s, const double* sigma_t) {
+    API_BEGIN
+    REQUIRE(h && sigma_s && sigma_t, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    const HostPlan& p = h->plan;
+    const int N = p.N;
+    CK(cudaStreamSynchronize(h->st));
+    free_caches(h);
+    h->sigma_s.assign(sigma_s, sigma_s + N);
+    h->sigma_t.assign(sigma_t, sigma_t + N);
+    // sigma_s in slot order for the GMRES operator
+    to_slots(h, sigma_s, h->d_sig_s);
+    CK(cudaStreamSynchronize(h->st));
+    // interpolation() KernelFactory.cpp:212-227 on the device; chat = coeff / legendreNorms feeds the ray march
+    stage_h2d(h, sigma_t);
+    LAUNCH(h, launch_interpolate(h->G, h->d_stage, h->d_lnorm, h->d_chat, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    h->coeff_t.clear();
+    h->coeff_s.clear();
+    h->coeff_set = true;
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_interpolation(aniso_t* h, const double* f, double* coeff) {
+    API_BEGIN
+    REQUIRE(h && f && coeff, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    const int N = h->plan.N;
+    stage_h2d(h, f);
+    LAUNCH(h, launch_interpolate(h->G, h->d_stage, nullptr, h->d_a, h->st));
+    CK(cudaMemcpyAsync(h->pinned + N, h->d_a, sizeof(double) * N, cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    std::memcpy(coeff, h->pinned + N, sizeof(double) * N);
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_sigma_coeff(aniso_t* h, double* ct, double* cs) {
+    API_BEGIN
+    REQUIRE(h, "null handle");
+    if (!h->coeff_set) throw std::logic_error("setCoeff has not been called");
+    if (ct) { int rc = aniso_interpolation(h, h->sigma_t.data(), ct); if (rc) return rc; }
+    if (cs) { int rc = aniso_interpolation(h, h->sigma_s.data(), cs); if (rc) return rc; }
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_cache(aniso_t* h, int id) {
+    API_BEGIN
+    REQUIRE(h, "null handle");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    ensure_ops(h, id, PART_BOTH);
+    ensure_stencils(h, id);
+    CK(cudaStreamSynchronize(h->st));
+    return ANISO_OK;
+    API_END
+}
+
+size_t aniso_cache_bytes(const aniso_t* h, int id) {
+    if (!h) return 0;
+    size_t b = 0;
+    for (auto& kv : h->ops)
+        if (kv.first.first == id) b += (size_t)(h->p2p.nnz + h->m2l.nnz) * sizeof(double);
+    if (h->stencils.count(id)) b += ((size_t)3 * 9 + 1) * h->G.c2 * h->nown * sizeof(double);
+    return b;
+}
+
+int aniso_cache_counts(const aniso_t* h, int64_t out[2]) {
+    if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
+    out[0] = h->fill_counts[0];
+    out[1] = h->fill_counts[1];
+    return ANISO_OK;
+}
+
+int aniso_mapping_dev(aniso_t* h, const double* charge_dev, int id, double* out_dev) {
+    API_BEGIN
+    REQUIRE(h && charge_dev && out_dev, "null pointer");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    mapping_slots(h, charge_dev, id, nullptr, nullptr, out_dev, 0);
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_forward_dev(aniso_t* h, const double* x_dev, double* y_dev) {
+    API_BEGIN
+    REQUIRE(h && x_dev && y_dev, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    const double* full = x_dev;
+    if (h->nranks > 1) {
+        allgather_slots(h, x_dev, h->d_xfull);
+        full = h->d_xfull;
+    }
+    mapping_slots(h, full, 0, h->d_sig_s, x_dev, y_dev, 1);
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_mapping(aniso_t* h, const double* charge, int id, double* out) {
+    API_BEGIN
+    REQUIRE(h && charge && out, "null pointer");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    to_slots(h, charge, h->d_a);
+    mapping_slots(h, h->d_a, id, nullptr, nullptr, h->d_b, 0);
+    from_slots(h, h->d_b, out);
+    return ANISO_OK;
+    API_END
+}
+
+static int stage_fmm(aniso_t* h, int id, int part, const double* f, double* ret) {
+    API_BEGIN
+    REQUIRE(h && f && ret, "null pointer");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    OperatorCache& c = ensure_ops(h, id, part);
+    to_slots(h, f, h->d_q);  // the caller passes the scaled function, like the reference
+    run_fmm(h, c, h->d_q, h->d_b);
+    from_slots(h, h->d_b, ret);
+    return ANISO_OK;
+    API_END
+}
+int aniso_run_kernels_fast(aniso_t* h, int id, const double* f, double* ret) { return stage_fmm(h, id, PART_IMAG, f, ret); }
+int aniso_run_kernels_fast_sing(aniso_t* h, int id, const double* f, double* ret) { return stage_fmm(h, id, PART_REAL, f, ret); }
+
+static int stage_stencil(aniso_t* h, int id, int which, const double* f, double* ret) {
+    API_BEGIN
+    REQUIRE(h && f && ret, "null pointer");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    StencilCache& s = ensure_stencils(h, id);
+    to_slots(h, ret, h->d_b);  // corrections accumulate into ret
+    if (which == 9) {
+        stage_h2d(h, f);
+        LAUNCH(h, launch_sing_apply(h->G, h->slot0, h->nown, s.c9, h->d_stage, h->d_b + h->slot0, h->st));
+    } else {
+        to_slots(h, f, h->d_a);
+        LAUNCH(h, launch_stencil_apply(h->G, h->slot0, h->nown, which == 7 ? s.c7 : s.c8, h->d_a, h->d_b + h->slot0, 1, h->st));
+    }
+    from_slots(h, h->d_b + h->slot0, ret);
+    return ANISO_OK;
+    API_END
+}
+int aniso_near_removal(aniso_t* h, int id, const double* f, double* ret) { return stage_stencil(h, id, 7, f, ret); }
+int aniso_refine_add_on_fast(aniso_t* h, int id, const double* f, double* ret) { return stage_stencil(h, id, 8, f, ret); }
+int aniso_singular_add_fast(aniso_t* h, int id, const double* fc, double* ret) { return stage_stencil(h, id, 9, fc, ret); }
+
+int aniso_line_integral(aniso_t* h, int n, const double* pts4, double* out) {
+    API_BEGIN
+    REQUIRE(h && pts4 && out && n >= 0, "bad arguments");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede lineIntegral");
+    double* d = dalloc<double>(h, (size_t)5 * n);
+    CK(cudaMemcpyAsync(d, pts4, sizeof(double) * 4 * n, cudaMemcpyHostToDevice, h->st));
+    LAUNCH(h, launch_probe_line_integral(h->S, n, d, d + 4 * (size_t)n, h->st));
+    CK(cudaMemcpyAsync(out, d + 4 * (size_t)n, sizeof(double) * n, cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    dfree(h, d);
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_kernel_eval(aniso_t* h, int id, int part, int n, const double* pts4, double* out) {
+    API_BEGIN
+    REQUIRE(h && pts4 && out && n >= 0 && part >= 1 && part <= 3, "bad arguments");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede kernel evaluation");
+    double* d = dalloc<double>(h, (size_t)5 * n);
+    CK(cudaMemcpyAsync(d, pts4, sizeof(double) * 4 * n, cudaMemcpyHostToDevice, h->st));
+    LAUNCH(h, launch_probe_kernel(h->S, id, part, n, d, d + 4 * (size_t)n, h->st));
+    CK(cudaMemcpyAsync(out, d + 4 * (size_t)n, sizeof(double) * n, cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    dfree(h, d);
+    return ANISO_OK;
+    API_END
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// GMRES (gmres.cpp:53-169) with A = forwardOperator (main.cpp:123-136).  Vectors live on the device in slot order
+// (owned range); the Hessenberg column is produced on the device and read back once per Arnoldi step for the
+// Givens update, which stays on the host exactly as in the reference.
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+void plane_rotation(double dx, double dy, double& cs, double& sn) {  // GeneratePlaneRotation, gmres.cpp:26-39
+    if (dy == 0.0) {
+        cs = 1.0;
+        sn = 0.0;
+    } else if (std::fabs(dy) > std::fabs(dx)) {
+        const double t = dx / dy;
+        sn = 1.0 / std::sqrt(1.0 + t * t);
+        cs = t * sn;
+    } else {
+        const double t = dy / dx;
+        cs = 1.0 / std::sqrt(1.0 + t * t);
+        sn = t * cs;
+    }
+}
+void apply_rotation(double& dx, double& dy, double cs, double sn) {  // ApplyPlaneRotation, gmres.cpp:42-46
+    const double t = cs * dx + sn * dy;
+    dy = -sn * dx + cs * dy;
+    dx = t;
+}
+
+struct GmresWork {
+    aniso_handle* h;
+    int n, m;
+    double *w, *r, *V;  // V: (m+1) x n
+    double* v(int i) { return V + (size_t)i * n; }
+};
+
+// dot over the owned rows, summed across ranks; result stays on the device (and optionally sqrt'ed)
+void ddot_dev(aniso_handle* h, int n, const double* a, const double* b, double* out, bool take_sqrt) {
+    LAUNCH(h, launch_dot(n, a, b, out, h->dot, h->st));
+    allreduce_scalars(h, out, 1);
+    if (take_sqrt) LAUNCH(h, launch_sqrt1(out, h->st));
+}
+double read_scalar(aniso_handle* h, const double* d) {
+    double v;
+    CK(cudaMemcpyAsync(&v, d, sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return v;
+}
+
+void forward_own(aniso_handle* h, const double* x_own, double* y_own) {
+    const double* full = x_own;
+    if (h->nranks > 1) {
+        allgather_slots(h, x_own, h->d_xfull);
+        full = h->d_xfull;
+    }
+    mapping_slots(h, full, 0, h->d_sig_s, x_own, y_own, 1);
+}
+
+// Update, gmres.cpp:12-24
+void gm_update(GmresWork& g, double* x, int k, const std::vector<double>& H, int ldh, const std::vector<double>& s) {
+    std::vector<double> y(s.begin(), s.begin() + k + 1);
+    for (int i = k; i >= 0; --i) {
+        y[i] /= H[i + (size_t)i * ldh];
+        for (int j = i - 1; j >= 0; --j) y[j] -= H[j + (size_t)i * ldh] * y[i];
+    }
+    for (int j = 0; j <= k; ++j) LAUNCH(g.h, launch_axpy(g.n, y[j], g.v(j), x, g.h->st));
+}
+
+int gmres_core(aniso_handle* h, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
+               int hist_cap) {
+    const int n = h->nown, ldh = m + 1;
+    ensure_ops(h, 0, PART_BOTH);
+    ensure_stencils(h, 0);
+    GmresWork g{h, n, m, nullptr, nullptr, nullptr};
+    g.w = dalloc<double>(h, n);
+    g.r = dalloc<double>(h, n);
+    g.V = dalloc<double>(h, (size_t)(m + 1) * n);
+    double* dh = h->d_scal;  // device Hessenberg column, m+2 entries
+    if (m + 2 > 1024) throw std::invalid_argument("restart length m too large (max 1022)");
+    std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0), col(m + 2);
+    int rc = 1, j = 1, i = 0;
+    bool done = false;
+    double resid = 0;
+    *iters = 0;
+    ddot_dev(h, n, b, b, dh, true);
+    double normb = read_scalar(h, dh);
+    forward_own(h, x, g.w);
+    LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
+    ddot_dev(h, n, g.r, g.r, dh, true);
+    double beta = read_scalar(h, dh);
+    if (normb == 0.0) normb = 1;
+    if ((resid = beta / normb) <= tol) {  // gmres.cpp:90 (<= here, < below: Q11)
+        rc = 0;
+        done = true;
+    }
+    while (!done && j <= max_iter) {
+        LAUNCH(h, launch_scale_inv_dev(n, dh, g.r, g.v(0), h->st));  // dh[0] still holds beta
+        std::fill(s.begin(), s.end(), 0.0);
+        s[0] = beta;
+        for (i = 0; i < m && j <= max_iter; ++i, ++j) {
+            if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
+            *iters = j;
+            forward_own(h, g.v(i), g.w);
+            for (int k = 0; k <= i; ++k) {  // modified Gram-Schmidt, gmres.cpp:115-119
+                ddot_dev(h, n, g.w, g.v(k), dh + k, false);
+                LAUNCH(h, launch_axpy_neg_dev(n, dh + k, g.v(k), g.w, h->st));
+            }
+            ddot_dev(h, n, g.w, g.w, dh + i + 1, true);
+            LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), h->st));
+            CK(cudaMemcpyAsync(col.data(), dh, sizeof(double) * (i + 2), cudaMemcpyDeviceToHost, h->st));
+            CK(cudaStreamSynchronize(h->st));
+            for (int k = 0; k <= i + 1; ++k) H[k + (size_t)i * ldh] = col[k];
+            for (int k = 0; k < i; ++k) apply_rotation(H[k + (size_t)i * ldh], H[k + 1 + (size_t)i * ldh], cs[k], sn[k]);
+            plane_rotation(H[i + (size_t)i * ldh], H[i + 1 + (size_t)i * ldh], cs[i], sn[i]);
+            apply_rotation(H[i + (size_t)i * ldh], H[i + 1 + (size_t)i * ldh], cs[i], sn[i]);
+            apply_rotation(s[i], s[i + 1], cs[i], sn[i]);
+            if ((resid = std::fabs(s[i + 1]) / normb) < tol) {
+                gm_update(g, x, i, H, ldh, s);
+                rc = 0;
+                done = true;
+                break;
+            }
+        }
+        if (done) break;
+        gm_update(g, x, i - 1, H, ldh, s);
+        forward_own(h, x, g.w);
+        LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
+        ddot_dev(h, n, g.r, g.r, dh, true);
+        beta = read_scalar(h, dh);
+        if ((resid = beta / normb) < tol) {
+            rc = 0;
+            done = true;
+        }
+    }
+    if (hist && *iters < hist_cap) hist[*iters] = resid;
+    CK(cudaStreamSynchronize(h->st));
+    dfree(h, g.w);
+    dfree(h, g.r);
+    dfree(h, g.V);
+    return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int aniso_gmres_dev(aniso_t* h, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
+                    int hist_cap) {
+    API_BEGIN
+    REQUIRE(h && b && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede GMRES");
+    return gmres_core(h, b, x, m, max_iter, tol, iters, hist, hist_cap);
+    API_END
+}
+
+int aniso_gmres(aniso_t* h, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
+                int hist_cap) {
+    API_BEGIN
+    REQUIRE(h && b && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede GMRES");
+    double* db = dalloc<double>(h, h->plan.N);
+    double* dx = dalloc<double>(h, h->plan.N);
+    to_slots(h, b, db);
+    to_slots(h, x, dx);
+    const int rc = gmres_core(h, db + h->slot0, dx + h->slot0, m, max_iter, tol, iters, hist, hist_cap);
+    from_slots(h, dx + h->slot0, x);
+    dfree(h, db);
+    dfree(h, dx);
+    return rc;
+    API_END
+}
+
+void* aniso_stream(aniso_t* h) { return h ? (void*)h->st : nullptr; }
+int aniso_device(const aniso_t* h) { return h ? h->device : fail(ANISO_EINVAL, "null handle"); }
+int aniso_synchronize(aniso_t* h) {
+    API_BEGIN
+    REQUIRE(h, "null handle");
+    if (h->dev_ready) CK(cudaStreamSynchronize(h->st));
+    return ANISO_OK;
+    API_END
+}
+int aniso_dev_alloc(aniso_t* h, size_t bytes, void** out) {
+    API_BEGIN
+    REQUIRE(h && out, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    *out = dalloc<char>(h, bytes);
+    return ANISO_OK;
+    API_END
+}
+int aniso_dev_free(aniso_t* h, void* p) {
+    API_BEGIN
+    REQUIRE(h, "null handle");
+    CK(cudaSetDevice(h->device));
+    dfree(h, p);
+    return ANISO_OK;
+    API_END
+}
+int aniso_to_slots(aniso_t* h, const double* host, double* dev) {
+    API_BEGIN
+    REQUIRE(h && host && dev, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    to_slots(h, host, dev);
+    return ANISO_OK;
+    API_END
+}
+int aniso_from_slots(aniso_t* h, const double* dev, double* host) {
+    API_BEGIN
+    REQUIRE(h && host && dev, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    from_slots(h, dev, host);
+    return ANISO_OK;
+    API_END
+}
+int64_t aniso_launch_count(const aniso_t* h) { return h ? h->launches : 0; }
+int aniso_apply_bytes(const aniso_t* h, int64_t out[3]) {
+    if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
+    out[0] = h->plan.p2p.nnz * 8;
+    out[1] = h->plan.m2l.nnz * 8;
+    out[2] = (int64_t)9 * h->plan.c2 * h->nown * 8;
+    return ANISO_OK;
+}
+int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms) {
+    API_BEGIN
+    REQUIRE(h && ms && reps >= 1 && (which == 0 || which == 1), "bad arguments");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    OperatorCache& c = ensure_ops(h, id, PART_BOTH);
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, h->st));
+    for (int i = 0; i < reps; ++i) {
+        if (which == 0) LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, h->st));
+        else LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, h->d_q, h->d_pot, h->st));
+    }
+    CK(cudaEventRecord(e1, h->st));
+    CK(cudaEventSynchronize(e1));
+    float t = 0;
+    CK(cudaEventElapsedTime(&t, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ms = t / reps;
+    return ANISO_OK;
+    API_END
+}
+
+}  // extern "C"

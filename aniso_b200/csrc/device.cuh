@@ -63,14 +63,19 @@ void launch_l2p(const DevTree& T, const DevGeom& G, const int* leaf_of_slot, int
                 const double* pot, double* out, cudaStream_t st);
 // correction stencils: C[(slotcell*c2+q)*nown + (p-slot0)], slotcell in 0..8 ((dr+1)*3+(dc+1))
 void launch_build_stencils(const DevGeom& G, int id, int slot0, int nown, double* c7, double* c8, double* c9, cudaStream_t st);
-// acc[p-slot0] (+)= sign * sum stencil * f ; mode 0: overwrite, 1: accumulate
+// c7/c8 act on the scaled source, c9 ([c2][nown]) on the Legendre coefficients of the unscaled source;
+// call = fused stencil on the unscaled source
+void launch_combine_stencils(const DevGeom& G, int slot0, int nown, const double* c7, const double* c8, const double* c9,
+                             double* call, cudaStream_t st);
+void launch_sing_apply(const DevGeom& G, int slot0, int nown, const double* c9, const double* coeff, double* acc, cudaStream_t st);
+// acc[p-slot0] (+)= sum stencil * f (f: full vector, slot order); accumulate 0: overwrite, 1: add
 void launch_stencil_apply(const DevGeom& G, int slot0, int nown, const double* C, const double* f, double* acc, int accumulate,
                           cudaStream_t st);
 // out = (fmm + corr) / 2pi, optionally y = x - that (GMRES operator of main.cpp:123-136)
 void launch_finalize(int n, const double* fmm, const double* corr, const double* x, double* out, int subtract_from_x,
                      cudaStream_t st);
 void launch_gather(int n, const double* src, const int* idx, double* dst, cudaStream_t st);  // dst[i] = src[idx[i]]
-void launch_add3(int n, const double* a, const double* b, const double* c, double* out, cudaStream_t st);
+void launch_add3(long n, const double* a, const double* b, const double* c, double* out, cudaStream_t st);
 // sigma interpolation on device: chat[c][r] = (sum_j interp[r][j] sqrtw[j] h[c*c2+j]) / (lnorm ? lnorm[r] : 1), h in REFERENCE order
 void launch_interpolate(const DevGeom& G, const double* h_ref, const double* lnorm_or_null, double* coeff, cudaStream_t st);
 // probes for parity tests

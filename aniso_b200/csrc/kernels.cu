@@ -1,0 +1,586 @@
+// Hand-written sm_100a kernels of the aniso matvec.  FP64 throughout (parity gate 1e-10).
+//   fill_blocks      K1/K2 evaluator: optical-depth ray march + kernel family, writes the cached operators
+//   bsr_apply        K3/K4 cached apply: one HBM pass over the operator blocks
+//   p2m/m2m/l2l/l2p  K5/K6 Chebyshev passes
+//   build_stencils   K7+K8+K9 corrections folded into one 9-cell stencil per target (built once per id)
+//   stencil_apply    the per-matvec correction
+#include <cmath>
+#include <cstdio>
+
+#include "device.cuh"
+
+namespace an {
+
+// ------------------------------------------------------------------------------------------------
+// sigma_t interpolant and its line integral
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int cell_index(double v, int sz) {  // getRow/getCol, KernelFactory.cpp:392-401
+    int c = (int)floor(v * sz);
+    return min(max(c, 0), sz - 1);
+}
+
+// sum_{n,k} P_n(x) P_k(y) chat[n*deg+k] with the libstdc++ tr1 Legendre recurrence at GLOBAL coordinates
+// (KernelFactory.cpp:180-187, 198-205; quirk Q1).  chat already holds coeff / legendreNorms.
+__device__ __forceinline__ double sigma_poly(const double* __restrict__ chat, int deg, double x, double y) {
+    if (deg == 1) return __ldg(chat);
+    double acc = 0, pxm2 = 1.0, pxm1 = x;
+    for (int n = 0; n < deg; ++n) {
+        double pxn;
+        if (n == 0) pxn = 1.0;
+        else if (n == 1) pxn = x;
+        else {
+            pxn = 2.0 * x * pxm1 - pxm2 - (x * pxm1 - pxm2) / (double)n;
+            pxm2 = pxm1;
+            pxm1 = pxn;
+        }
+        double pym2 = 1.0, pym1 = y, inner = 0;
+        for (int k = 0; k < deg; ++k) {
+            double pyk;
+            if (k == 0) pyk = 1.0;
+            else if (k == 1) pyk = y;
+            else {
+                pyk = 2.0 * y * pym1 - pym2 - (y * pym1 - pym2) / (double)k;
+                pym2 = pym1;
+                pym1 = pyk;
+            }
+            inner += pyk * __ldg(chat + n * deg + k);
+        }
+        acc += pxn * inner;
+    }
+    return acc;
+}
+
+__device__ __forceinline__ double sigma_eval(const SigmaGrid& S, double x, double y) {  // evaluate, KernelFactory.cpp:193-207
+    const int col = cell_index(x, S.sz), row = cell_index(y, S.sz);
+    return sigma_poly(S.chat + (size_t)(col * S.sz + row) * S.c2, S.deg, x, y);
+}
+
+// Optical depth tau(p0,p1) = exact integral of the piecewise-polynomial interpolant along the segment
+// (lineIntegral + integral_helper, KernelFactory.cpp:67-190).  The reference bisects until the end cells touch and
+// then splits at the cell edges; every piece is integrated with the deg-point Gauss rule, which is exact for the
+// degree-2(deg-1) polynomial along the ray, so the value equals the sum over the cells the ray crosses.  That sum
+// is what this cell walk computes: crossing parameters are evaluated directly (not accumulated) per step.
+__device__ double line_integral(const SigmaGrid& S, double x0, double y0, double x1, double y1) {
+    const int sz = S.sz;
+    const double ddx = x1 - x0, ddy = y1 - y0;
+    const double len = sqrt(ddx * ddx + ddy * ddy);
+    int cx = cell_index(x0, sz), cy = cell_index(y0, sz);
+    const int ex = cell_index(x1, sz), ey = cell_index(y1, sz);
+    const int sx = ex >= cx ? 1 : -1, sy = ey >= cy ? 1 : -1;
+    const double ivx = ddx != 0.0 ? 1.0 / ddx : 0.0, ivy = ddy != 0.0 ? 1.0 / ddy : 0.0;
+    const double inf = 2.0;
+    int bx = cx + (sx > 0), by = cy + (sy > 0);
+    double tx = cx != ex ? ((double)bx * S.h - x0) * ivx : inf;
+    double ty = cy != ey ? ((double)by * S.h - y0) * ivy : inf;
+    const int nsteps = abs(ex - cx) + abs(ey - cy);
+    double tcur = 0.0, acc = 0.0;
+    const int deg = S.deg;
+    for (int step = 0; step <= nsteps; ++step) {
+        const double tn = step == nsteps ? 1.0 : fmin(tx, ty);
+        const double* __restrict__ chat = S.chat + (size_t)(cx * sz + cy) * S.c2;
+        if (deg == 1) {
+            acc += __ldg(chat) * (tn - tcur);
+        } else {
+            // sub-segment end points and its Gauss points (integral_helper, KernelFactory.cpp:174-190)
+            const double xa = x0 + tcur * ddx, ya = y0 + tcur * ddy, xb = x0 + tn * ddx, yb = y0 + tn * ddy;
+            const double mx = (xa + xb) / 2, my = (ya + yb) / 2, hx = (xa - xb) / 2, hy = (ya - yb) / 2;
+            double s = 0;
+            for (int i = 0; i < deg; ++i) {
+                const double g = __ldg(S.glx + i);
+                s += sigma_poly(chat, deg, mx + hx * g, my + hy * g) * __ldg(S.glw + i);
+            }
+            acc += s * (tn - tcur) * 0.5;
+        }
+        if (step < nsteps) {
+            if (tx <= ty) {
+                cx += sx;
+                bx += sx;
+                tx = cx != ex ? ((double)bx * S.h - x0) * ivx : inf;
+            } else {
+                cy += sy;
+                by += sy;
+                ty = cy != ey ? ((double)by * S.h - y0) * ivy : inf;
+            }
+        }
+        tcur = tn;
+    }
+    return acc * len;
+}
+
+// Kernel family of makeKernels (KernelFactory.cpp:240-267): a = source, b = target (Q8).
+//   REAL: cos(k theta)/d        IMAG: (exp(-tau)-1) cos(k theta)/d, diagonal +sigma_t(a) for k = 0 (Q2)
+//   BOTH: their sum exp(-tau) cos(k theta)/d (the physical kernel; what the fused matvec caches)
+__device__ __forceinline__ double cos_k_theta(int k, double c, double s) {  // Re (c + i s)^k
+    double cr = 1.0, ci = 0.0;
+    for (int i = 0; i < k; ++i) {
+        const double nr = cr * c - ci * s;
+        ci = cr * s + ci * c;
+        cr = nr;
+    }
+    return cr;
+}
+
+__device__ double kernel_eval(const SigmaGrid& S, int id, int part, double ax, double ay, double bx, double by) {
+    const double ddx = ax - bx, ddy = ay - by;
+    const double dist = sqrt(ddx * ddx + ddy * ddy);
+    if (dist == 0.0) return ((part & PART_IMAG) && id == 0) ? sigma_eval(S, ax, ay) : 0.0;
+    const double inv = 1.0 / dist;
+    const double ck = id == 0 ? 1.0 : cos_k_theta(id, ddx * inv, ddy * inv);
+    if (part == PART_REAL) return ck / dist;
+    const double tau = line_integral(S, ax, ay, bx, by);
+    const double e = exp(-tau);
+    if (part == PART_IMAG) return (e - 1.0) * ck / dist;
+    return e * ck / dist;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1/K2 evaluator.  One CTA per operator block; threads stride over the block column-major in the target
+// index so the rays of one warp join neighbouring points of the same two boxes (similar step counts).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) fill_blocks_kernel(DevCSR m, DevTree T, DevGeom G, SigmaGrid S, int id, int part,
+                                                          int cheb, double* __restrict__ A) {
+    const int e = blockIdx.x;
+    const int tn = m.tgt_node[e], sn = m.src_node[e];
+    const int np = T.np;
+    int nrow, ncol, toff = 0, soff = 0;
+    double tcx = 0, tcy = 0, trx = 0, try_ = 0, scx = 0, scy = 0, srx = 0, sry = 0;
+    if (cheb) {
+        nrow = ncol = T.r;
+        tcx = T.cx[tn]; tcy = T.cy[tn]; trx = T.rx[tn]; try_ = T.ry[tn];
+        scx = T.cx[sn]; scy = T.cy[sn]; srx = T.rx[sn]; sry = T.ry[sn];
+    } else {
+        nrow = T.npts[tn];
+        ncol = T.npts[sn];
+        toff = T.pt_off[tn];
+        soff = T.pt_off[sn];
+    }
+    double* __restrict__ out = A + m.blk_off[e];
+    const int total = nrow * ncol;
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+        const int t = idx % nrow, s = idx / nrow;
+        double ax, ay, bx, by;
+        if (cheb) {  // flat = j*np + i, y slow (bbfmm.h:787-800)
+            ax = scx + srx * T.cheb[s % np];
+            ay = scy + sry * T.cheb[s / np];
+            bx = tcx + trx * T.cheb[t % np];
+            by = tcy + try_ * T.cheb[t / np];
+        } else {
+            ax = G.px[soff + s];
+            ay = G.py[soff + s];
+            bx = G.px[toff + t];
+            by = G.py[toff + t];
+        }
+        out[idx] = kernel_eval(S, id, part, ax, ay, bx, by);
+    }
+}
+
+void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const SigmaGrid& S, int id, int part, int cheb,
+                 double* A, cudaStream_t st) {
+    if (m.entries == 0) return;
+    int threads = 256;
+    if (cheb && T.r <= 8) threads = 64;
+    else if (cheb && T.r <= 11) threads = 128;
+    fill_blocks_kernel<<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+}
+
+__global__ void probe_line_integral_kernel(SigmaGrid S, int n, const double* __restrict__ p, double* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = line_integral(S, p[4 * i], p[4 * i + 1], p[4 * i + 2], p[4 * i + 3]);
+}
+__global__ void probe_kernel_kernel(SigmaGrid S, int id, int part, int n, const double* __restrict__ p,
+                                    double* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = kernel_eval(S, id, part, p[4 * i], p[4 * i + 1], p[4 * i + 2], p[4 * i + 3]);
+}
+void launch_probe_line_integral(const SigmaGrid& S, int n, const double* pts4, double* out, cudaStream_t st) {
+    if (n > 0) probe_line_integral_kernel<<<(n + 127) / 128, 128, 0, st>>>(S, n, pts4, out);
+}
+void launch_probe_kernel(const SigmaGrid& S, int id, int part, int n, const double* pts4, double* out, cudaStream_t st) {
+    if (n > 0) probe_kernel_kernel<<<(n + 127) / 128, 128, 0, st>>>(S, id, part, n, pts4, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3/K4 cached apply: y[row] = sum_e sum_s A[blk_e + s*nrow + t] x[col_e + s].
+// One thread per output row; the nrow threads of a row group read nrow consecutive doubles per source index
+// (blocks are stored source-major), so a warp's loads are full 128-byte lines.  The operator is read exactly
+// once per apply and never reused: loads bypass L1 allocation (ld.global.nc.L1::no_allocate).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double ld_stream(const double* p) {
+    double v;
+    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+}
+
+__global__ void __launch_bounds__(128) bsr_apply_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
+                                                        double* __restrict__ y) {
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= m.nrows_total) return;
+    int g, t, nrow;
+    if (m.uniform_nrow) {
+        nrow = m.uniform_nrow;
+        g = row / nrow;
+        t = row - g * nrow;
+    } else {
+        g = m.row_group[row];
+        t = row - m.grow_ptr[g];
+        nrow = m.nrow[g];
+    }
+    const int e0 = m.ent_ptr[g], e1 = m.ent_ptr[g + 1];
+    double acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
+    for (int e = e0; e < e1; ++e) {
+        const double* __restrict__ blk = A + m.blk_off[e] + t;
+        const double* __restrict__ xs = x + m.col_off[e];
+        const int nc = m.ncol[e];
+        int s = 0;
+        for (; s + 4 <= nc; s += 4) {
+            const double a0 = ld_stream(blk + (size_t)(s + 0) * nrow);
+            const double a1 = ld_stream(blk + (size_t)(s + 1) * nrow);
+            const double a2 = ld_stream(blk + (size_t)(s + 2) * nrow);
+            const double a3 = ld_stream(blk + (size_t)(s + 3) * nrow);
+            acc0 = fma(a0, __ldg(xs + s + 0), acc0);
+            acc1 = fma(a1, __ldg(xs + s + 1), acc1);
+            acc2 = fma(a2, __ldg(xs + s + 2), acc2);
+            acc3 = fma(a3, __ldg(xs + s + 3), acc3);
+        }
+        for (; s < nc; ++s) acc0 = fma(ld_stream(blk + (size_t)s * nrow), __ldg(xs + s), acc0);
+    }
+    y[m.row_off[g] + t] = (acc0 + acc1) + (acc2 + acc3);
+}
+
+void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, cudaStream_t st) {
+    if (m.nrows_total == 0) return;
+    bsr_apply_kernel<<<(m.nrows_total + 127) / 128, 128, 0, st>>>(m, A, x, y);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5/K6 Chebyshev passes (bbfmm.h:825-861, 1066-1113)
+// ------------------------------------------------------------------------------------------------
+// S(x, m) = (2 sum_k T_k(x) T_k(t_m) - 1)/np   (bbfmm.h:635-656, 742-746)
+__device__ __forceinline__ double cheb_weight(const double* __restrict__ tnode, int np, double x, int m) {
+    double s = -1.0, t0 = 1.0, t1 = x;
+    for (int k = 0; k < np; ++k) {
+        double tk = k == 0 ? 1.0 : x;
+        if (k >= 2) {
+            tk = 2.0 * x * t1 - t0;
+            t0 = t1;
+            t1 = tk;
+        }
+        s += 2.0 * tk * __ldg(tnode + m * np + k);
+    }
+    return s / np;
+}
+
+__global__ void scale_kernel(int n, const double* __restrict__ x, const double* __restrict__ sig_s, const double* __restrict__ w,
+                             double* __restrict__ f, double* __restrict__ q) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double v = sig_s ? x[i] * sig_s[i] : x[i];
+    if (f) f[i] = v;
+    q[i] = v * w[i];
+}
+void launch_scale(int n, const double* x, const double* sig_s, const double* w, double* f, double* q, cudaStream_t st) {
+    scale_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, x, sig_s, w, f, q);
+}
+
+// P2M: nodeCharge[j*np+i] = sum_k Sx(k,i) Sy(k,j) q_k over the leaf's points (bbfmm.h:723-759, 832-844).
+// r threads per leaf; the leaf list covers ALL non-empty leaves (the upward pass is replicated on every rank,
+// SURVEY 8e).
+__global__ void p2m_kernel(DevTree T, DevGeom G, const int* __restrict__ leaves, int nleaves, const double* __restrict__ q,
+                           double* __restrict__ mcharge) {
+    const int r = T.r, np = T.np;
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int li = gid / r, mth = gid - li * r;
+    if (li >= nleaves) return;
+    const int id = leaves[li];
+    const double cx = T.cx[id], cy = T.cy[id], rx = T.rx[id], ry = T.ry[id];
+    const int off = T.pt_off[id], n = T.npts[id];
+    const int i = mth % np, j = mth / np;
+    double acc = 0;
+    for (int k = 0; k < n; ++k) {
+        const double sx = (G.px[off + k] - cx) / rx, sy = (G.py[off + k] - cy) / ry;
+        acc += cheb_weight(T.tnode, np, sx, i) * cheb_weight(T.tnode, np, sy, j) * q[off + k];
+    }
+    mcharge[(size_t)id * r + mth] = acc;
+}
+
+// M2M: parent[b] = sum_{c non-empty} sum_a R[c][a][b] child_c[a]  (bbfmm.h:855-859)
+__global__ void m2m_kernel(DevTree T, int first, int count, double* __restrict__ mcharge) {
+    const int r = T.r;
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ni = gid / r, b = gid - ni * r;
+    if (ni >= count) return;
+    const int id = first + ni;
+    if (T.flags[id] & 1) return;  // leaf: set by P2M (or empty)
+    double acc = 0;
+    for (int c = 0; c < 4; ++c) {
+        const int ch = T.child[id * 4 + c];
+        if (T.flags[ch] & 2) continue;
+        const double* __restrict__ Rc = T.R + (size_t)c * r * r;
+        const double* __restrict__ src = mcharge + (size_t)ch * r;
+        for (int a = 0; a < r; ++a) acc = fma(__ldg(Rc + a * r + b), src[a], acc);
+    }
+    mcharge[(size_t)id * r + b] = acc;
+}
+
+// L2L: child[a] += sum_b R[index][a][b] parent[b]  (bbfmm.h:1070-1071)
+__global__ void l2l_kernel(DevTree T, int first, int count, double* __restrict__ mpot) {
+    const int r = T.r;
+    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int ni = gid / r, a = gid - ni * r;
+    if (ni >= count) return;
+    const int id = first + ni;
+    if (T.flags[id] & 2) return;
+    const int par = T.parent[id];
+    const double* __restrict__ Rc = T.R + (size_t)T.index[id] * r * r + (size_t)a * r;
+    const double* __restrict__ src = mpot + (size_t)par * r;
+    double acc = 0;
+    for (int b = 0; b < r; ++b) acc = fma(__ldg(Rc + b), src[b], acc);
+    mpot[(size_t)id * r + a] += acc;
+}
+
+// L2P + P2P sum: out[p] = pot[p] + sum_{i,j} Sx(p,i) Sy(p,j) nodePotential[leaf][j*np+i]  (bbfmm.h:1104-1113)
+__global__ void l2p_kernel(DevTree T, DevGeom G, const int* __restrict__ leaf_of_slot, int slot0, int n,
+                           const double* __restrict__ mpot, const double* __restrict__ pot, double* __restrict__ out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int p = slot0 + k;
+    const int id = leaf_of_slot[p];
+    const int np = T.np;
+    const double sx = (G.px[p] - T.cx[id]) / T.rx[id], sy = (G.py[p] - T.cy[id]) / T.ry[id];
+    const double* __restrict__ mp = mpot + (size_t)id * T.r;
+    double acc = 0;
+    for (int j = 0; j < np; ++j) {
+        const double wy = cheb_weight(T.tnode, np, sy, j);
+        for (int i = 0; i < np; ++i) acc += cheb_weight(T.tnode, np, sx, i) * wy * mp[j * np + i];
+    }
+    out[k] = pot[p] + acc;
+}
+
+void launch_p2m(const DevTree& T, const DevGeom& G, const double* q, double* mcharge, cudaStream_t st) {
+    const long threads = (long)T.nleaves * T.r;
+    if (threads == 0) return;
+    p2m_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(T, G, T.leaves, T.nleaves, q, mcharge);
+}
+void launch_m2m(const DevTree& T, int first, int count, double* mcharge, cudaStream_t st) {
+    const long threads = (long)count * T.r;
+    if (threads == 0) return;
+    m2m_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(T, first, count, mcharge);
+}
+void launch_l2l(const DevTree& T, int first, int count, double* mpot, cudaStream_t st) {
+    const long threads = (long)count * T.r;
+    if (threads == 0) return;
+    l2l_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(T, first, count, mpot);
+}
+void launch_l2p(const DevTree& T, const DevGeom& G, const int* leaf_of_slot, int slot0, int n, const double* mpot,
+                const double* pot, double* out, cudaStream_t st) {
+    if (n == 0) return;
+    l2p_kernel<<<(n + 127) / 128, 128, 0, st>>>(T, G, leaf_of_slot, slot0, n, mpot, pot, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K7 + K8 + K9 corrections.  All three are linear in the (unscaled) source with support in the 3x3 cell
+// neighbourhood of the target, so each is stored once per kernel id as a stencil
+//     C[(cs*c2 + q)*nown + k],  cs = (dr+1)*3 + (dc+1),  k = target slot - slot0
+// acting on f[(cell + dr*sz + dc)*c2 + q].  The reference instead keeps nearInteractions (N x 9 x 16 deg^2) and
+// singInteractions (N x 8 sr^2) and redoes the small gemv / Legendre sums per target on every apply
+// (KernelFactory.cpp:445-478, 550-609, 662-709, 752-788, 828-860).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double real_kernel(int id, double ax, double ay, double bx, double by) {
+    const double ddx = ax - bx, ddy = ay - by;
+    const double dist = sqrt(ddx * ddx + ddy * ddy);
+    if (dist == 0.0) return 0.0;
+    if (id == 0) return 1 / dist;
+    const double inv = 1.0 / dist;
+    return cos_k_theta(id, ddx * inv, ddy * inv) / dist;
+}
+
+__device__ __forceinline__ double legendre_tr1_dev(int l, double x) {
+    if (l == 0) return 1.0;
+    if (l == 1) return x;
+    double pm2 = 1.0, pm1 = x, p = 0;
+    for (int ll = 2; ll <= l; ++ll) {
+        p = 2.0 * x * pm1 - pm2 - (x * pm1 - pm2) / (double)ll;
+        pm2 = pm1;
+        pm1 = p;
+    }
+    return p;
+}
+
+__global__ void __launch_bounds__(128) build_stencils_kernel(DevGeom G, int id, int slot0, int nown, double* __restrict__ c7,
+                                                             double* __restrict__ c8, double* __restrict__ c9) {
+    const long gid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int c2 = G.c2, sz = G.sz, deg = G.deg;
+    const long total = (long)9 * c2 * nown;
+    if (gid >= total) return;
+    const int k = (int)(gid % nown);
+    const int cq = (int)(gid / nown);
+    const int q = cq % c2, cs = cq / c2;
+    const int dr = cs / 3 - 1, dc = cs % 3 - 1;
+    const int p = slot0 + k;
+    const int t = G.perm[p];
+    const int tc = t / c2, tq = t - tc * c2;
+    const int ti = tc / sz, tj = tc - ti * sz;  // ti <-> x, tj <-> y
+    double v7 = 0, v8 = 0;
+    const int si = ti + dr, sj = tj + dc;
+    if (si >= 0 && si < sz && sj >= 0 && sj < sz) {
+        const double tx = G.px[p], ty = G.py[p], dx = G.dx;
+        const int sslot = G.inv_perm[(si * sz + sj) * c2 + q];
+        // K7 nearRemoval (KernelFactory.cpp:445-478): self cell included, the self pair evaluates to 0 (Q16).
+        // Acts on the SCALED source (f .* weights), like the reference.
+        v7 = -real_kernel(id, G.px[sslot], G.py[sslot], tx, ty);
+        if (cs != 4) {
+            // K8 refineAddOn (KernelFactory.cpp:583-601, 687-700): refined rule of the neighbour cell; acts on the
+            // scaled source: old = scaled / sqrtWeights, new = nearMapping * old, ret += inter . new
+            double acc = 0;
+            for (int a = 0; a < G.rq; ++a) {
+                const double ax = (0.5 + si) * dx + 0.5 * (G.rqx[a]) * dx;
+                const double ay = (0.5 + sj) * dx + 0.5 * (G.rqy[a]) * dx;
+                const double inter = real_kernel(id, ax, ay, tx, ty) * sqrt(G.rqw[a]);
+                acc += inter * G.nearMap[(size_t)a * c2 + q];
+            }
+            v8 = acc / G.sqrtw[q];
+        } else {
+            // K9 singularAdd (KernelFactory.cpp:765-780, 840-856): Duffy points of the self cell; this thread owns the
+            // Legendre mode nk = q.  Acts on the Legendre coefficients of the UNSCALED source, whose interpolant is
+            // evaluated at GLOBAL coordinates (Q1).
+            const double* __restrict__ sX = G.singX + (size_t)tq * G.nsing;
+            const double* __restrict__ sY = G.singY + (size_t)tq * G.nsing;
+            const double* __restrict__ sW = G.singW + (size_t)tq * G.nsing;
+            const int n = q / deg, kk = q - n * deg;
+            const double nrm = G.lnorm[q];
+            double acc = 0;
+            for (int pp = 0; pp < G.nsing; ++pp) {
+                const double x = (0.5 + ti) * dx + 0.5 * (sX[pp]) * dx;
+                const double y = (0.5 + tj) * dx + 0.5 * (sY[pp]) * dx;
+                const double w = sW[pp] * (dx * dx) / 4.0;
+                const double inter = real_kernel(id, x, y, tx, ty) * w;
+                acc += (legendre_tr1_dev(n, x) * legendre_tr1_dev(kk, y) / nrm) * inter;
+            }
+            c9[(size_t)q * nown + k] = acc;
+        }
+    }
+    c7[gid] = v7;
+    c8[gid] = v8;
+}
+
+// fused stencil acting on the UNSCALED source f:  (K7 + K8) .* weight  +  K9 o interpolation
+__global__ void combine_stencils_kernel(DevGeom G, int slot0, int nown, const double* __restrict__ c7, const double* __restrict__ c8,
+                                        const double* __restrict__ c9, double* __restrict__ call) {
+    const long gid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const int c2 = G.c2, sz = G.sz;
+    if (gid >= (long)9 * c2 * nown) return;
+    const int k = (int)(gid % nown);
+    const int cq = (int)(gid / nown);
+    const int q = cq % c2, cs = cq / c2;
+    const int t = G.perm[slot0 + k];
+    const int tc = t / c2;
+    const int ti = tc / sz, tj = tc - ti * sz;
+    const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
+    double v = 0;
+    if (si >= 0 && si < sz && sj >= 0 && sj < sz) {
+        v = (c7[gid] + c8[gid]) * G.pw[G.inv_perm[(si * sz + sj) * c2 + q]];
+        if (cs == 4) {
+            double a = 0;
+            for (int nk = 0; nk < c2; ++nk) a += c9[(size_t)nk * nown + k] * G.interp[(size_t)nk * c2 + q];
+            v += a * G.sqrtw[q];
+        }
+    }
+    call[gid] = v;
+}
+
+void launch_build_stencils(const DevGeom& G, int id, int slot0, int nown, double* c7, double* c8, double* c9, cudaStream_t st) {
+    const long total = (long)9 * G.c2 * nown;
+    if (total == 0) return;
+    build_stencils_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, id, slot0, nown, c7, c8, c9);
+}
+void launch_combine_stencils(const DevGeom& G, int slot0, int nown, const double* c7, const double* c8, const double* c9,
+                             double* call, cudaStream_t st) {
+    const long total = (long)9 * G.c2 * nown;
+    if (total == 0) return;
+    combine_stencils_kernel<<<(unsigned)((total + 127) / 128), 128, 0, st>>>(G, slot0, nown, c7, c8, c9, call);
+}
+
+// K9 stage form: acc[k] += sum_nk c9[nk][k] * coeff[cell(k)][nk]  (singularAddFast, KernelFactory.cpp:828-860)
+__global__ void sing_apply_kernel(DevGeom G, int slot0, int nown, const double* __restrict__ c9, const double* __restrict__ coeff,
+                                  double* __restrict__ acc_out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nown) return;
+    const int c2 = G.c2;
+    const int tc = G.perm[slot0 + k] / c2;
+    double acc = 0;
+    for (int nk = 0; nk < c2; ++nk) acc = fma(c9[(size_t)nk * nown + k], coeff[(size_t)tc * c2 + nk], acc);
+    acc_out[k] += acc;
+}
+void launch_sing_apply(const DevGeom& G, int slot0, int nown, const double* c9, const double* coeff, double* acc, cudaStream_t st) {
+    if (nown) sing_apply_kernel<<<(nown + 127) / 128, 128, 0, st>>>(G, slot0, nown, c9, coeff, acc);
+}
+
+__global__ void stencil_apply_kernel(DevGeom G, int slot0, int nown, const double* __restrict__ C, const double* __restrict__ f,
+                                     double* __restrict__ acc_out, int accumulate) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nown) return;
+    const int c2 = G.c2, sz = G.sz;
+    const int t = G.perm[slot0 + k];
+    const int tc = t / c2;
+    const int ti = tc / sz, tj = tc - ti * sz;
+    double acc = 0;
+    for (int cs = 0; cs < 9; ++cs) {
+        const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
+        if (si < 0 || si >= sz || sj < 0 || sj >= sz) continue;
+        const int base = (si * sz + sj) * c2;
+        for (int q = 0; q < c2; ++q)
+            acc = fma(C[(size_t)(cs * c2 + q) * nown + k], f[G.inv_perm[base + q]], acc);
+    }
+    acc_out[k] = accumulate ? acc_out[k] + acc : acc;
+}
+
+void launch_stencil_apply(const DevGeom& G, int slot0, int nown, const double* C, const double* f, double* acc, int accumulate,
+                          cudaStream_t st) {
+    if (nown == 0) return;
+    stencil_apply_kernel<<<(nown + 127) / 128, 128, 0, st>>>(G, slot0, nown, C, f, acc, accumulate);
+}
+
+__global__ void finalize_kernel(int n, const double* __restrict__ fmm, const double* __restrict__ corr, const double* __restrict__ x,
+                                double* __restrict__ out, int subtract_from_x) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double v = (fmm[i] + (corr ? corr[i] : 0.0)) * (M_1_PI / 2.0);  // AnisoWrapper.cpp:129-130
+    out[i] = subtract_from_x ? x[i] - v : v;                              // main.cpp:129-134
+}
+void launch_finalize(int n, const double* fmm, const double* corr, const double* x, double* out, int subtract_from_x,
+                     cudaStream_t st) {
+    if (n) finalize_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, fmm, corr, x, out, subtract_from_x);
+}
+
+__global__ void gather_kernel(int n, const double* __restrict__ src, const int* __restrict__ idx, double* __restrict__ dst) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
+}
+void launch_gather(int n, const double* src, const int* idx, double* dst, cudaStream_t st) {
+    if (n) gather_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, src, idx, dst);
+}
+
+__global__ void add3_kernel(long n, const double* __restrict__ a, const double* __restrict__ b, const double* __restrict__ c,
+                            double* __restrict__ out) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = a[i] + b[i] + c[i];
+}
+void launch_add3(long n, const double* a, const double* b, const double* c, double* out, cudaStream_t st) {
+    if (n) add3_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, a, b, c, out);
+}
+
+// K10 interpolation (KernelFactory.cpp:212-227, 988-1005): per cell a c2 x c2 gemv; h is in REFERENCE node order
+__global__ void interpolate_kernel(DevGeom G, const double* __restrict__ h, const double* __restrict__ lnorm,
+                                   double* __restrict__ coeff) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= G.N) return;
+    const int c2 = G.c2, c = i / c2, r = i - c * c2;
+    double s = 0;
+    for (int j = 0; j < c2; ++j) s += G.interp[(size_t)r * c2 + j] * (G.sqrtw[j] * h[(size_t)c * c2 + j]);
+    coeff[i] = lnorm ? s / lnorm[r] : s;
+}
+void launch_interpolate(const DevGeom& G, const double* h_ref, const double* lnorm_or_null, double* coeff, cudaStream_t st) {
+    interpolate_kernel<<<(G.N + 255) / 256, 256, 0, st>>>(G, h_ref, lnorm_or_null, coeff);
+}
+
+}  // namespace an

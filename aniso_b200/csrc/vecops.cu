@@ -1,0 +1,90 @@
+// K11: device-resident BLAS-1 pieces of the GMRES Arnoldi step (gmres.cpp:115-122, 12-24).  All scalars that
+// feed the next kernel (Hessenberg entries, norms) stay in device memory, so one Arnoldi step needs a single
+// host synchronisation (to read the new Hessenberg column for the Givens update).
+#include "device.cuh"
+
+namespace an {
+
+static constexpr int kDotThreads = 256;
+
+// Deterministic two-stage dot product: every block writes one partial, the last block to finish adds the
+// partials in index order (fixed summation order => identical bits on every rank and every run).
+__global__ void __launch_bounds__(kDotThreads) dot_kernel(int n, const double* __restrict__ a, const double* __restrict__ b,
+                                                          double* __restrict__ result, double* __restrict__ partial,
+                                                          unsigned int* __restrict__ counter) {
+    __shared__ double warp_sum[kDotThreads / 32];
+    __shared__ bool last;
+    double acc = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) acc = fma(a[i], b[i], acc);
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int w = 0; w < kDotThreads / 32; ++w) s += warp_sum[w];
+        partial[blockIdx.x] = s;
+        __threadfence();
+        last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    // final pass by one block, fixed order: thread t sums partials t, t+256, ... then a tree over the block
+    double s = 0;
+    for (int i = threadIdx.x; i < gridDim.x; i += blockDim.x) s += ((volatile double*)partial)[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0;
+        for (int w = 0; w < kDotThreads / 32; ++w) tot += warp_sum[w];
+        *result = tot;
+        *counter = 0;
+    }
+}
+
+void launch_dot(int n, const double* a, const double* b, double* result, DotWork& wk, cudaStream_t st) {
+    int blocks = (n + kDotThreads * 4 - 1) / (kDotThreads * 4);
+    if (blocks < 1) blocks = 1;
+    if (blocks > wk.blocks) blocks = wk.blocks;
+    dot_kernel<<<blocks, kDotThreads, 0, st>>>(n, a, b, result, wk.partial, wk.counter);
+}
+
+__global__ void axpy_neg_dev_kernel(int n, const double* __restrict__ h, const double* __restrict__ v, double* __restrict__ w) {
+    const double alpha = -*h;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) w[i] = fma(alpha, v[i], w[i]);
+}
+void launch_axpy_neg_dev(int n, const double* h, const double* v, double* w, cudaStream_t st) {
+    if (n) axpy_neg_dev_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, h, v, w);
+}
+
+__global__ void axpy_kernel(int n, double alpha, const double* __restrict__ x, double* __restrict__ y) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) y[i] = fma(alpha, x[i], y[i]);
+}
+void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t st) {
+    if (n) axpy_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, alpha, x, y);
+}
+
+__global__ void scale_inv_dev_kernel(int n, const double* __restrict__ norm, const double* __restrict__ in, double* __restrict__ out) {
+    const double s = 1.0 / *norm;  // gmres.cpp:122 / 100: dscal(1.0 / h, v)
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i] * s;
+}
+void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, cudaStream_t st) {
+    if (n) scale_inv_dev_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, norm, in, out);
+}
+
+__global__ void sqrt1_kernel(double* v) { *v = sqrt(*v); }
+void launch_sqrt1(double* v, cudaStream_t st) { sqrt1_kernel<<<1, 1, 0, st>>>(v); }
+
+__global__ void sub_kernel(int n, const double* __restrict__ a, const double* __restrict__ b, double* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = a[i] - b[i];
+}
+void launch_sub(int n, const double* a, const double* b, double* out, cudaStream_t st) {
+    if (n) sub_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, a, b, out);
+}
+
+}  // namespace an

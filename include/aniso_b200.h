@@ -1,0 +1,159 @@
+/* aniso_b200 - C-ABI of the B200-native aniso hot path (integral-operator matvec `mapping` + GMRES).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  Each entry point names the
+ * reference interface it replaces (file:line into lowrank/aniso).  INTEGRATION.md shows the MEX / C++ / ctypes
+ * bindings a maintainer would put on top.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative ANISO_E* code; aniso_last_error() gives the text
+ *     (thread-local).  No exception crosses this boundary.
+ *   - vectors named `..._host` are caller-owned host buffers of length N = aniso_num_nodes() in the REFERENCE node
+ *     order (Geometry.cpp:28-60); `..._dev` are device pointers on the handle's device in the library's SLOT order
+ *     (depth-first leaf order of the quadtree, see aniso_slot_permutation).
+ *   - all device memory is owned by the handle; calls on one handle must be serialised by the caller (as in the
+ *     reference, which is not re-entrant either).
+ *   - there is NO CPU fallback: every compute entry point fails with ANISO_ENODEVICE when no CUDA device is usable.
+ *     The host-only entry points (geometry, tree, partition introspection) work without a GPU.
+ */
+#ifndef ANISO_B200_H
+#define ANISO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct aniso_handle aniso_t;
+
+enum {
+    ANISO_OK = 0,
+    ANISO_EINVAL = -1,    /* bad argument (null pointer, id out of range, bad size) */
+    ANISO_ENODEVICE = -2, /* no usable CUDA device / driver */
+    ANISO_ECUDA = -3,     /* a CUDA call failed */
+    ANISO_ESTATE = -4,    /* call order violated (setCoeff before cache, cache before mapping) */
+    ANISO_ENOMEM = -5,
+    ANISO_ENCCL = -6
+};
+
+/* kernel parts of KernelFactory.h:22-23: realParts = singular cos(k theta)/r, imagParts = attenuated remainder */
+enum { ANISO_PART_REAL = 1, ANISO_PART_IMAG = 2, ANISO_PART_BOTH = 3 };
+
+const char* aniso_last_error(void);
+const char* aniso_version(void);
+
+/* ---- life cycle ------------------------------------------------------------------------------------------ */
+/* Aniso::Aniso(geometry_size, geometry_degree, kernel_size, kernel_g, kernel_degree, np, maxLevel)  Aniso.h:14-15,
+ * Aniso.cpp:7-13; MEX op 'new' AnisoWrapper.cpp:10-25.  Host set-up only (geometry, quadtree, lists). */
+int aniso_create(int geometry_size, int geometry_degree, int kernel_size, double kernel_g, int kernel_degree, int np,
+                 int maxLevel, aniso_t** out);
+/* Same, as rank `rank` of `nranks` devices on one node: target leaves are partitioned by quadtree ownership
+ * (SURVEY 8e).  nccl_unique_id = the 128 bytes of aniso_nccl_unique_id() from rank 0, identical on all ranks.
+ * device = CUDA device ordinal to use (-1: current device). */
+int aniso_create_sharded(int geometry_size, int geometry_degree, int kernel_size, double kernel_g, int kernel_degree,
+                         int np, int maxLevel, int nranks, int rank, const void* nccl_unique_id, int device,
+                         aniso_t** out);
+int aniso_nccl_unique_id(void* out128);
+/* MEX op 'delete' AnisoWrapper.cpp:27-31 / Aniso::~Aniso */
+int aniso_destroy(aniso_t* h);
+
+/* ---- geometry (host only) -------------------------------------------------------------------------------- */
+int aniso_num_nodes(const aniso_t* h);   /* Geometry::numberOfNodes, Geometry.h:60 */
+int aniso_kernel_size(const aniso_t* h); /* KernelFactory::kernelSize = 2*kernel_size-1, KernelFactory.cpp:10-13 */
+/* MEX op 'getNodes' AnisoWrapper.cpp:33-44 (+ Geometry::weights); any pointer may be NULL */
+int aniso_get_nodes(const aniso_t* h, double* x, double* y, double* w);
+/* get_legendre_data, Quadrature.cpp:5418-22191 (table order) */
+int aniso_gl_table(int degree, double* x, double* w);
+/* Geometry tables: interpolate (c2*c2 row-major), nearMapping (16c2*c2), legendreNorms (c2), refine_quad_x/y,
+ * refine_weight (16c2 each); Geometry.h:49-58.  NULL pointers are skipped. */
+int aniso_geometry_tables(const aniso_t* h, double* interpolate, double* nearMapping, double* legendreNorms,
+                          double* refine_x, double* refine_y, double* refine_w);
+/* singX/singY/singW, KernelFactory.h:36 (c2 * 8*sr*sr each), filled by singPrecompute KernelFactory.cpp:929-986 */
+int aniso_sing_tables(const aniso_t* h, double* sx, double* sy, double* sw);
+/* bbfmm::tree statistics (bbfmm.h:176-447): out[9] = nodes, leaves, maxLevel, sum|U|, sum|V|, sum|W|, sum|X|,
+ * P2P pairs, max points per leaf */
+int aniso_tree_stats(const aniso_t* h, int64_t out[9]);
+/* per tree node (library numbering, level-major): geom[4n] = cx,cy,rx,ry; info[4n] = level, leaf, nSource, parent.
+ * Returns the node count (also when cap is too small). */
+int aniso_tree_nodes(const aniso_t* h, int cap, double* geom, int* info);
+/* interaction lists of one node: kinds 0=V 1=X 2=U 3=W; returns the entry count */
+int aniso_node_lists(const aniso_t* h, int node, int cap, int* ids, int* kinds);
+/* slot order used by the *_dev entry points: perm[slot] = reference node index */
+int aniso_slot_permutation(const aniso_t* h, int* perm);
+/* ownership of rank `rank` out of `nranks`: slots [*slot_begin, *slot_end) and leaf count; host only */
+int aniso_partition(const aniso_t* h, int nranks, int rank, int* slot_begin, int* slot_end, int* nleaves);
+int aniso_owned_range(const aniso_t* h, int* slot_begin, int* slot_end);
+
+/* ---- coefficients and caches ----------------------------------------------------------------------------- */
+/* MEX op 'setCoeff' AnisoWrapper.cpp:46-69: stores sigma_s/sigma_t, runs interpolation() KernelFactory.cpp:212-227
+ * (singPrecompute / makeKernels are part of aniso_create here).  Invalidates every cache. */
+int aniso_set_coeff(aniso_t* h, const double* sigma_s_host, const double* sigma_t_host);
+/* sigma_t_Coeff / sigma_s_Coeff (KernelFactory.h:77-78), N doubles each, cell-major; NULL skipped */
+int aniso_sigma_coeff(aniso_t* h, double* coeff_t_host, double* coeff_s_host);
+/* MEX op 'cache' AnisoWrapper.cpp:72-90 = runKernelsCache + runKernelsCacheSing + refineAddOnCache +
+ * singularAddCache (KernelFactory.cpp:323-334, 279-288, 550-609, 752-788): evaluates every P2P/M2L operator block
+ * of kernel `id` on the device (fused real+imag), and the correction stencils. */
+int aniso_cache(aniso_t* h, int id);
+/* bytes held for kernel id (Aniso::displayKernelCacheSize, Aniso.cpp:19-47) */
+size_t aniso_cache_bytes(const aniso_t* h, int id);
+/* number of kernel evaluations the last aniso_cache(id) performed: out[0] = P2P pairs, out[1] = M2L pairs */
+int aniso_cache_counts(const aniso_t* h, int64_t out[2]);
+
+/* ---- the matvec ------------------------------------------------------------------------------------------- */
+/* MEX op 'mapping' AnisoWrapper.cpp:92-136 == apply_mapping main.cpp:78-119.  Host in, host out (H2D + D2H inside). */
+int aniso_mapping(aniso_t* h, const double* charge_host, int id, double* out_host);
+/* Device-resident form, slot order.  charge_dev: full vector (N); out_dev: the owned range (N on one GPU).
+ * Runs on the handle's stream; returns without synchronising. */
+int aniso_mapping_dev(aniso_t* h, const double* charge_dev, int id, double* out_dev);
+/* y = x - mapping_0(sigma_s .* x): forwardOperator of main.cpp:123-136, device-resident. */
+int aniso_forward_dev(aniso_t* h, const double* x_dev, double* y_dev);
+
+/* stage entry points for stage-wise parity (host vectors, reference order).  The three corrections ACCUMULATE
+ * into ret like the reference; the two FMM calls overwrite it (bbfmm.h:579). */
+int aniso_interpolation(aniso_t* h, const double* f_host, double* coeff_host);            /* KernelFactory.cpp:988-1005 */
+int aniso_run_kernels_fast(aniso_t* h, int id, const double* f_host, double* ret_host);      /* :354-363 (imagParts) */
+int aniso_run_kernels_fast_sing(aniso_t* h, int id, const double* f_host, double* ret_host); /* :379-387 (realParts) */
+int aniso_near_removal(aniso_t* h, int id, const double* f_host, double* ret_host);          /* :445-478 */
+int aniso_refine_add_on_fast(aniso_t* h, int id, const double* f_host, double* ret_host);    /* :662-709 */
+int aniso_singular_add_fast(aniso_t* h, int id, const double* fcoeff_host, double* ret_host);/* :828-860 */
+
+/* ---- GMRES ------------------------------------------------------------------------------------------------ */
+/* GMRES(A, x, b, m, max_iter, tol) gmres.cpp:53-169 with A = forwardOperator (main.cpp:123-136), device-resident
+ * Arnoldi.  x_host: initial guess in, solution out.  Returns 0 converged / 1 not converged (like the reference) or a
+ * negative error.  resid_hist[j-1] = relative residual the reference prints at iteration j, resid_hist[*iters] = the
+ * final one (hist_cap entries available; may be NULL). */
+int aniso_gmres(aniso_t* h, const double* b_host, double* x_host, int m, int max_iter, double tol, int* iters,
+                double* resid_hist, int hist_cap);
+/* Same with device vectors in slot order (owned range), no host copies of vectors. */
+int aniso_gmres_dev(aniso_t* h, const double* b_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
+                    double* resid_hist, int hist_cap);
+
+/* ---- device probes (parity tests of K1/K2 pieces) ---------------------------------------------------------- */
+/* lineIntegral(x0,y0,x1,y1) KernelFactory.cpp:67-166 for n segments, pts4 = n x 4 host doubles */
+int aniso_line_integral(aniso_t* h, int n, const double* pts4_host, double* out_host);
+/* realParts[id].eval / imagParts[id].eval (makeKernels KernelFactory.cpp:240-267): pts4 = (ax,ay,bx,by) */
+int aniso_kernel_eval(aniso_t* h, int id, int part, int n, const double* pts4_host, double* out_host);
+
+/* ---- plumbing ---------------------------------------------------------------------------------------------- */
+void* aniso_stream(aniso_t* h);          /* cudaStream_t all work of the handle is launched on */
+int aniso_device(const aniso_t* h);
+int aniso_synchronize(aniso_t* h);
+/* device buffer helpers for callers without a CUDA runtime of their own */
+int aniso_dev_alloc(aniso_t* h, size_t bytes, void** out);
+int aniso_dev_free(aniso_t* h, void* p);
+int aniso_to_slots(aniso_t* h, const double* ref_order_host, double* slot_order_dev);   /* H2D + permute */
+int aniso_from_slots(aniso_t* h, const double* slot_order_dev, double* ref_order_host); /* permute + D2H (owned rows only
+                                                                                            when sharded: others untouched) */
+/* kernels launched by this handle since creation (bench.py's gpu_launches) */
+int64_t aniso_launch_count(const aniso_t* h);
+/* algorithmic operator bytes one mapping streams: out[0] = P2P, out[1] = M2L, out[2] = stencil */
+int aniso_apply_bytes(const aniso_t* h, int64_t out[3]);
+/* time the streaming apply kernels alone: `reps` back-to-back launches of (0) M2L apply, (1) P2P apply on the cache of `id`,
+ * CUDA events on the handle's stream; returns average milliseconds per launch */
+int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms_per_launch);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ANISO_B200_H */
