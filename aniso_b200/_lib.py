@@ -41,6 +41,7 @@ SIGNATURES = {
     "aniso_cache": (C.c_int, [_H, C.c_int]),
     "aniso_cache_bytes": (C.c_size_t, [_H, C.c_int]),
     "aniso_cache_counts": (C.c_int, [_H, _lp]),
+    "aniso_cache_times": (C.c_int, [_H, _dp]),
     "aniso_mapping": (C.c_int, [_H, _dp, C.c_int, _dp]),
     "aniso_mapping_dev": (C.c_int, [_H, _V, C.c_int, _V]),
     "aniso_forward_dev": (C.c_int, [_H, _V, _V]),

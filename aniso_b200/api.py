@@ -223,6 +223,11 @@ class Aniso:
         _lib.check(self.L.aniso_cache_counts(self.h, o))
         return dict(p2p=int(o[0]), m2l=int(o[1]))
 
+    def cache_times(self):
+        o = np.zeros(3)
+        _lib.check(self.L.aniso_cache_times(self.h, o))
+        return dict(p2p_fill_ms=float(o[0]), m2l_fill_ms=float(o[1]), stencil_ms=float(o[2]))
+
     def time_kernel(self, kid, which, reps):
         ms = C.c_double()
         _lib.check(self.L.aniso_time_kernel(self.h, int(kid), int(which), int(reps), C.byref(ms)))

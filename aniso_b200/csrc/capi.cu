@@ -63,6 +63,7 @@ struct aniso_handle {
     std::map<int, StencilCache> stencils;
     int64_t launches = 0;
     int64_t fill_counts[2] = {0, 0};
+    float fill_ms[3] = {0, 0, 0};  // last P2P fill, M2L fill, stencil build (CUDA events)
     DotWork dot;
     double* d_scal = nullptr;  // Hessenberg column / scalars on device
     NcclApi* nccl = nullptr;
@@ -430,9 +431,18 @@ OperatorCache& ensure_ops(aniso_handle* h, int id, int part) {
     OperatorCache c;
     c.p2p = dalloc<double>(h, (size_t)h->p2p.nnz);
     c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz);
+    cudaEvent_t ev[3];
+    for (auto& e : ev) CK(cudaEventCreate(&e));
+    CK(cudaEventRecord(ev[0], h->st));
     LAUNCH(h, launch_fill(h->p2p, h->T, h->G, h->S, id, part, 0, c.p2p, h->st));
+    CK(cudaEventRecord(ev[1], h->st));
     LAUNCH(h, launch_fill(h->m2l, h->T, h->G, h->S, id, part, 1, c.m2l, h->st));
+    CK(cudaEventRecord(ev[2], h->st));
     CK(cudaGetLastError());
+    CK(cudaEventSynchronize(ev[2]));
+    CK(cudaEventElapsedTime(&h->fill_ms[0], ev[0], ev[1]));
+    CK(cudaEventElapsedTime(&h->fill_ms[1], ev[1], ev[2]));
+    for (auto& e : ev) cudaEventDestroy(e);
     h->fill_counts[0] = h->p2p.nnz;
     h->fill_counts[1] = h->m2l.nnz;
     return h->ops[key] = c;
@@ -448,9 +458,16 @@ StencilCache& ensure_stencils(aniso_handle* h, int id) {
     s.c8 = dalloc<double>(h, n9);
     s.call = dalloc<double>(h, n9);
     s.c9 = dalloc<double>(h, (size_t)h->G.c2 * h->nown);
+    cudaEvent_t ev[2];
+    for (auto& e : ev) CK(cudaEventCreate(&e));
+    CK(cudaEventRecord(ev[0], h->st));
     LAUNCH(h, launch_build_stencils(h->G, id, h->slot0, h->nown, s.c7, s.c8, s.c9, h->st));
     LAUNCH(h, launch_combine_stencils(h->G, h->slot0, h->nown, s.c7, s.c8, s.c9, s.call, h->st));
+    CK(cudaEventRecord(ev[1], h->st));
     CK(cudaGetLastError());
+    CK(cudaEventSynchronize(ev[1]));
+    CK(cudaEventElapsedTime(&h->fill_ms[2], ev[0], ev[1]));
+    for (auto& e : ev) cudaEventDestroy(e);
     return h->stencils[id] = s;
 }
 
@@ -616,6 +633,12 @@ int aniso_cache_counts(const aniso_t* h, int64_t out[2]) {
     if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
     out[0] = h->fill_counts[0];
     out[1] = h->fill_counts[1];
+    return ANISO_OK;
+}
+
+int aniso_cache_times(const aniso_t* h, double out[3]) {
+    if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
+    for (int i = 0; i < 3; ++i) out[i] = h->fill_ms[i];
     return ANISO_OK;
 }
 

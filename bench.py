@@ -1,0 +1,349 @@
+#!/usr/bin/env python
+"""bench.py - headline benchmark of the aniso hot path (BASELINE.json: FMM matvec time & near-field interactions/s;
+GMRES time-to-solve at N = 2^20 on 1/2/4/8 GPUs).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--sz 1024]
+
+Workload (config C5 of SURVEY 8): unit square, sz x sz cells, deg 1 => N = sz^2 nodes (2^20), Chebyshev order 4,
+g = 0.9, piecewise sigma_s / sigma_t layers, Gaussian source; kernel id 0.  One "step" = one application of the
+GMRES operator y = x - mapping_0(sigma_s .* x) (main.cpp:123-136), i.e. exactly one FMM matvec `mapping`.
+  value  device-resident throughput, target points per second (N / time of one matvec), CUDA events on the
+         library's stream, max over ranks.  Every step streams the cached operators (5.9 GB at C5 >> 126 MB L2), so
+         no L2 flush is needed between iterations.
+  e2e    the same through the reference-facing C-ABI call aniso_mapping() with HOST buffers (H2D + D2H inside).
+  --impl reference  times the compiled, unmodified reference (oracle/_ref/libaniso_ref_fast.so, OpenMP on all host
+         cores) on a bounded sample of the same workload (smaller sz; the FMM is O(N), the metric is per point).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import cases  # noqa: E402
+
+METRIC = "fmm_matvec_points_per_s"
+UNIT = "points/s"
+NP_ORDER, SING_RULE, G_ANISO, MAX_LEVEL = 4, 10, 0.9, 20
+
+
+def workload_name(sz):
+    return ("C5: N=%d (sz %d, deg 1), np %d, g %.1f, sigma layers, kernel id 0; step = y = x - mapping_0(sigma_s x)"
+            % (sz * sz, sz, NP_ORDER, G_ANISO))
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop = index, [], False
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop:
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in o.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+
+
+def reference_sample_sz(cores):
+    return 256 if cores >= 16 else 128
+
+
+def run_reference(args):
+    """The reference's own CPU implementation (compiled unmodified, its own -Ofast/-ffast-math flags, OpenMP on all
+    host cores) on a bounded sample; rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle import refapi  # the one place bench.py executes oracle/ besides cpu_baseline
+
+    cores = host_cores()
+    sz = args.ref_sz or reference_sample_sz(cores)
+    kind = "reference" if refapi.available(fast=True) else "port"
+    if kind == "reference":
+        r = refapi.RefAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL, fast=True)
+    else:
+        from oracle import oracleapi
+
+        r = oracleapi.OracleAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
+        cores = 1
+    x, y, w = r.nodes()
+    ss, st = cases.sigma_fields("layers", x, y, sz, 1)
+    t0 = time.perf_counter()
+    r.set_coeff(ss, st)
+    r.cache(0)
+    t_cache = time.perf_counter() - t0
+    f = cases.gaussian_source(x, y)
+    for _ in range(args.warmup):
+        r.mapping(ss * f, 0)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = f - r.mapping(ss * f, 0)  # same operator as our step
+    dt = (time.perf_counter() - t0) / max(args.steps, 1)
+    n = sz * sz
+    val = n / dt
+    sample = "N=%d (sz %d) sub-problem of the same workload; per-point cost of the O(N) FMM; cache phase %.1f s" % (n, sz, t_cache)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args.sz), "sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                             "cache_phase_s": t_cache, "near_field_interactions_per_s": None},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "checksum": float(np.linalg.norm(out))}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(args):
+    """Bounded CPU sample (about 10-30 s) timed beside the GPU run: rank 0, N=1 only."""
+    from oracle import refapi
+
+    cores = host_cores()
+    if refapi.available(fast=True):
+        sz, kind = 128, "reference"
+        r = refapi.RefAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL, fast=True)
+    else:
+        from oracle import oracleapi
+
+        sz, kind, cores = 64, "port", 1
+        r = oracleapi.OracleAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
+    x, y, w = r.nodes()
+    ss, st = cases.sigma_fields("layers", x, y, sz, 1)
+    t0 = time.perf_counter()
+    r.set_coeff(ss, st)
+    r.cache(0)
+    t_cache = time.perf_counter() - t0
+    pairs = r.tree_stats(0)["p2p_pairs"] if hasattr(r, "tree_stats") else None
+    f = cases.gaussian_source(x, y)
+    r.mapping(f, 0)
+    reps = 3
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        r.mapping(ss * f, 0)
+    dt = (time.perf_counter() - t0) / reps
+    n = sz * sz
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": "N=%d (sz %d) sub-problem, %d matvecs after a %.1f s cache phase" % (n, sz, reps, t_cache),
+            "ms_per_matvec": dt * 1e3, "cache_phase_s": t_cache,
+            "cache_evals_per_s": None if not pairs else None}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from aniso_b200 import Aniso, _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    torch.cuda.set_device(local)
+    L = _lib.load()
+    uid = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        buf = torch.zeros(128, dtype=torch.uint8)
+        if rank == 0:
+            import ctypes
+
+            raw = ctypes.create_string_buffer(128)
+            _lib.check(L.aniso_nccl_unique_id(raw))
+            buf = torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8).clone()
+        buf = buf.cuda()
+        dist.broadcast(buf, 0)
+        uid = bytes(buf.cpu().numpy().tobytes())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sz = args.sz
+    t0 = time.perf_counter()
+    a = Aniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL, nranks=world, rank=rank, nccl_uid=uid, device=local)
+    t_setup = time.perf_counter() - t0
+    n = a.numberOfNodes
+    x, y, w = a.nodes()
+    ss, st = cases.sigma_fields("layers", x, y, sz, 1)
+    t0 = time.perf_counter()
+    a.setCoeff(ss, st)
+    a.cache(0)
+    a.synchronize()
+    t_cache = max_over_ranks(time.perf_counter() - t0)
+    ct = a.cache_times()
+    counts = a.cache_counts()
+    slot0, slot1 = a.owned_range()
+    nown = slot1 - slot0
+    perm = a.slot_permutation()
+    f_host = cases.gaussian_source(x, y)
+    stream = torch.cuda.ExternalStream(L.aniso_stream(a.h))
+    x_full = torch.from_numpy(f_host[perm]).cuda()          # slot order
+    x_own = x_full[slot0:slot1].contiguous()
+    y_own = torch.empty(nown, dtype=torch.float64, device="cuda")
+    torch.cuda.synchronize()
+
+    def step():
+        _lib.check(L.aniso_forward_dev(a.h, x_own.data_ptr(), y_own.data_ptr()))
+
+    # ---- device-resident timed region ----
+    for _ in range(max(args.warmup, 3)):
+        step()
+    a.synchronize()
+    barrier()
+    l0 = a.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        e0.record(stream)
+        for _ in range(args.steps):
+            step()
+        e1.record(stream)
+        e1.synchronize()
+        barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = a.launch_count() - l0
+    ms_step = ms_total / args.steps
+    value = n / (ms_step * 1e-3)
+
+    # ---- end-to-end through the C-ABI with host buffers ----
+    out_host = np.zeros(n)
+    charge = f_host * ss
+    _lib.check(L.aniso_mapping(a.h, charge, 0, out_host))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        _lib.check(L.aniso_mapping(a.h, charge, 0, out_host))
+    a.synchronize()
+    barrier()
+    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+
+    # ---- roofline of the dominant kernel: the M2L streaming apply (bsr_apply_kernel over the V/X blocks) ----
+    ab = a.apply_bytes()
+    tr = a.tree_stats()
+    m2l_ms = max_over_ranks(a.time_kernel(0, 0, 20))
+    p2p_ms = max_over_ranks(a.time_kernel(0, 1, 20))
+    r = NP_ORDER * NP_ORDER
+    m2l_alg = ab["m2l"] + 8 * 2 * r * tr["nodes"]  # operator blocks + multipoles read + locals written
+    peak, peak_src = measured_peak()
+    roof = {"bound": "hbm", "kernel": "bsr_apply_kernel (M2L, V/X blocks)", "achieved": m2l_alg / (m2l_ms * 1e-3) / 1e9,
+            "peak": peak, "unit": "GB/s", "frac": m2l_alg / (m2l_ms * 1e-3) / 1e9 / peak, "traffic": None,
+            "peak_source": peak_src, "algorithmic_bytes_per_launch": m2l_alg, "ms_per_launch": m2l_ms,
+            "p2p_apply": {"algorithmic_bytes": ab["p2p"] + 16 * n, "ms_per_launch": p2p_ms,
+                          "achieved": (ab["p2p"] + 16 * n) / (p2p_ms * 1e-3) / 1e9}}
+
+    # ---- GMRES time-to-solve (main.cpp:141: GMRES(80, 400, 1e-12), x0 = 0) ----
+    b_own = torch.empty(nown, dtype=torch.float64, device="cuda")
+    _lib.check(L.aniso_mapping_dev(a.h, x_full.data_ptr(), 0, b_own.data_ptr()))
+    xs = torch.zeros(nown, dtype=torch.float64, device="cuda")
+    a.synchronize()
+    barrier()
+    import ctypes
+
+    it = ctypes.c_int(0)
+    hist = np.zeros(402)
+    l1 = a.launch_count()
+    t0 = time.perf_counter()
+    rc = _lib.check(L.aniso_gmres_dev(a.h, b_own.data_ptr(), xs.data_ptr(), 80, 400, 1e-12, ctypes.byref(it), hist, hist.size))
+    a.synchronize()
+    barrier()
+    t_gmres = max_over_ranks(time.perf_counter() - t0)
+    gm_launches = a.launch_count() - l1
+
+    line = None
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": workload_name(sz), "l2": "operator stream %.2f GB per step > 126 MB L2, no flush needed"
+                           % ((ab["p2p"] + ab["m2l"]) / 1e9), "partition": "target leaves by quadtree ownership, %d rank(s)" % world},
+                "e2e": {"value": n / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * nown,
+                        "ms_per_step": e2e_s * 1e3},
+                "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof,
+                "near_field_interactions_per_s": counts["p2p"] / (ct["p2p_fill_ms"] * 1e-3) if ct["p2p_fill_ms"] else None,
+                "cache": {"wall_s": t_cache, "p2p_pairs": counts["p2p"], "m2l_pairs": counts["m2l"], **ct,
+                          "m2l_evals_per_s": counts["m2l"] / (ct["m2l_fill_ms"] * 1e-3) if ct["m2l_fill_ms"] else None},
+                "gmres": {"rc": int(rc), "iters": int(it.value), "final_resid": float(hist[it.value]), "time_to_solve_s": t_gmres,
+                          "m": 80, "tol": 1e-12, "gpu_launches": int(gm_launches)},
+                "setup_s": t_setup}
+        if world == 1 and not args.no_cpu:
+            try:
+                line["cpu_baseline"] = cpu_baseline(args)
+            except Exception as e:  # the checker is optional equipment; never fail the GPU number for it
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference",
+                                        "sample": "failed: %r" % (e,)}
+        print(json.dumps(line), flush=True)
+    a.delete()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sz", type=int, default=1024, help="cells per side (N = sz^2); 1024 = BASELINE C5")
+    ap.add_argument("--ref-sz", type=int, default=0, help="sample size of the reference arm (0 = by core count)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

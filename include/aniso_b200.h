@@ -99,6 +99,9 @@ int aniso_cache(aniso_t* h, int id);
 size_t aniso_cache_bytes(const aniso_t* h, int id);
 /* number of kernel evaluations the last aniso_cache(id) performed: out[0] = P2P pairs, out[1] = M2L pairs */
 int aniso_cache_counts(const aniso_t* h, int64_t out[2]);
+/* device time (CUDA events, ms) of the last operator fill: out[0] = P2P evaluator, out[1] = M2L evaluator,
+ * out[2] = correction-stencil build */
+int aniso_cache_times(const aniso_t* h, double out[3]);
 
 /* ---- the matvec ------------------------------------------------------------------------------------------- */
 /* MEX op 'mapping' AnisoWrapper.cpp:92-136 == apply_mapping main.cpp:78-119.  Host in, host out (H2D + D2H inside). */
