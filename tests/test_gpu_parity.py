@@ -99,10 +99,14 @@ def test_gmres_vs_reference_golden(golden, name):
     a.cache(0)
     b = a.mapping(cases.gaussian_source(x, y), 0)
     assert np.linalg.norm(b[::stride] - g["gm_b"]) / np.linalg.norm(g["gm_b"]) < TOL
+    # The residual stalls near 1e-12 (rounding level), so the step at which it crosses tol is sensitive to a 1e-15
+    # perturbation of b (tests/test_oracle.py::test_gmres): where the fixture holds the reference's full right-hand
+    # side, start from it and demand the same count; with our own b (sub-sampled fixtures) allow one step.
+    if stride == 1:
+        b = g["gm_b"]
     xs, rc, it, hist = a.gmres(b, m=80, max_iter=400, tol=1e-12)
     assert rc == int(g["gm_rc"]) == 0
-    # the last residuals sit at rounding level (1e-12): the crossing step may move by one (see test_oracle.py)
-    assert abs(it - int(g["gm_iters"])) <= 1, (it, int(g["gm_iters"]))
+    assert abs(it - int(g["gm_iters"])) <= (0 if stride == 1 else 1), (it, int(g["gm_iters"]))
     assert abs(np.linalg.norm(xs) / float(g["gm_x_norm"]) - 1) < 1e-8
     assert np.linalg.norm(xs[::stride] - g["gm_x"]) / np.linalg.norm(g["gm_x"]) < 1e-8
     n = min(it, len(g["gm_hist"])) - 2
