@@ -99,6 +99,7 @@ DevCSR upload_csr(aniso_handle* h, const BlockCSR& b) {
     d.entries = (int)b.col_off.size();
     d.nrows_total = b.nrows_total;
     d.uniform_nrow = b.uniform_nrow;
+    d.uniform_block = b.uniform_block;
     d.nnz = b.nnz;
     d.row_off = upload(h, b.row_off);
     d.nrow = upload(h, b.nrow);
@@ -137,6 +138,15 @@ void ensure_device(aniso_handle* h) {
     G.sz = p.sz; G.deg = p.deg; G.c2 = p.c2; G.rq = p.rq; G.nsing = p.nsing; G.N = N; G.dx = p.dx;
     G.px = upload(h, sx); G.py = upload(h, sy); G.pw = upload(h, sw);
     G.perm = upload(h, p.perm); G.inv_perm = upload(h, p.inv_perm);
+    {
+        std::vector<double> sxn(N), syn(N);
+        for (int s = 0; s < N; ++s) {  // (x - center)/radius exactly as bbfmm.h:737-740
+            const TreeNode& lf = p.nodes[p.leaf_of_slot[s]];
+            sxn[s] = (sx[s] - lf.cx) / lf.rx;
+            syn[s] = (sy[s] - lf.cy) / lf.ry;
+        }
+        G.sxn = upload(h, sxn); G.syn = upload(h, syn);
+    }
     G.sqrtw = upload(h, p.sqrtw); G.interp = upload(h, p.interp); G.lnorm = upload(h, p.lnorm);
     G.nearMap = upload(h, p.nearMap); G.rqx = upload(h, p.rqx); G.rqy = upload(h, p.rqy); G.rqw = upload(h, p.rqw);
     G.singX = upload(h, p.singX); G.singY = upload(h, p.singY); G.singW = upload(h, p.singW);
@@ -158,7 +168,32 @@ void ensure_device(aniso_handle* h) {
     T.parent = upload(h, parent); T.index = upload(h, index); T.child = upload(h, child);
     T.pt_off = upload(h, pt_off); T.npts = upload(h, npts); T.flags = upload(h, flags);
     T.cheb = upload(h, p.cheb); T.tnode = upload(h, p.tnode); T.R = upload(h, p.R);
+    {
+        std::vector<double> RT(p.R.size());
+        for (int c = 0; c < 4; ++c)
+            for (int a = 0; a < r; ++a)
+                for (int b = 0; b < r; ++b) RT[((size_t)c * r + b) * r + a] = p.R[((size_t)c * r + a) * r + b];
+        T.RT = upload(h, RT);
+    }
     T.leaves = upload(h, p.leaves); T.nleaves = (int)p.leaves.size();
+    {
+        std::vector<int4> info(p.leaves.size());
+        std::vector<int> child0(nn);
+        T.max_leaf = 0;
+        for (size_t k = 0; k < p.leaves.size(); ++k) {
+            const TreeNode& n = p.nodes[p.leaves[k]];
+            info[k] = make_int4(p.leaves[k], n.pt_off, n.npts, 0);
+            T.max_leaf = std::max(T.max_leaf, n.npts);
+        }
+        for (int i = 0; i < nn; ++i) {
+            const TreeNode& n = p.nodes[i];
+            child0[i] = n.leaf ? -1 : n.child[0];
+            if (!n.leaf)
+                for (int c = 1; c < 4; ++c)
+                    if (n.child[c] != n.child[0] + c) throw std::runtime_error("internal: children not consecutive");
+        }
+        T.leaf_info = upload(h, info); T.child0 = upload(h, child0);
+    }
     h->d_leaf_of_slot = upload(h, p.leaf_of_slot);
     h->m2l = upload_csr(h, p.m2l);
     h->p2p = upload_csr(h, p.p2p);
@@ -473,7 +508,8 @@ StencilCache& ensure_stencils(aniso_handle* h, int id) {
 
 // kernel::runFast (bbfmm.h:565-592): upPass + downPassFast from the cached operators.
 // q: scaled source, full vector in slot order.  out: owned range.
-void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* out) {
+void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* out, int mode = 0, const double* stencil = nullptr,
+             const double* f = nullptr, const double* x_own = nullptr) {
     const HostPlan& p = h->plan;
     const DevTree& T = h->T;
     const int L0 = h->first_m2l_level;
@@ -485,7 +521,7 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     for (int L = L0 + 1; L < T.nlevels; ++L)
         LAUNCH(h, launch_l2l(T, p.level_ptr[L], p.level_ptr[L + 1] - p.level_ptr[L], h->d_mpot, h->st));
     LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, h->st));
-    LAUNCH(h, launch_l2p(T, h->G, h->d_leaf_of_slot, h->slot0, h->nown, h->d_mpot, h->d_pot, out, h->st));
+    LAUNCH(h, launch_l2p(T, h->G, h->d_leaf_of_slot, h->slot0, h->nown, h->d_mpot, h->d_pot, stencil, f, x_own, out, mode, h->st));
 }
 
 // all-gather of the owned shards into a full slot-order vector; counts differ per rank, so this is a
@@ -520,13 +556,11 @@ void mapping_slots(aniso_handle* h, const double* f_full, int id, const double* 
     StencilCache& s = ensure_stencils(h, id);
     const double* f = f_full;
     if (sig_s) {
-        LAUNCH(h, launch_scale(h->plan.N, f_full, sig_s, h->G.pw, h->d_f, h->d_q, h->st));
-        f = h->d_f;
+        LAUNCH(h, launch_scale(h->plan.N, f_full, sig_s, h->G.pw, h->G.perm, h->d_f, h->d_q, h->st));
     } else
-        LAUNCH(h, launch_scale(h->plan.N, f_full, nullptr, h->G.pw, nullptr, h->d_q, h->st));
-    run_fmm(h, c, h->d_q, h->d_fmm);
-    LAUNCH(h, launch_stencil_apply(h->G, h->slot0, h->nown, s.call, f, h->d_corr, 0, h->st));
-    LAUNCH(h, launch_finalize(h->nown, h->d_fmm, h->d_corr, x_own, out, subtract, h->st));
+        LAUNCH(h, launch_scale(h->plan.N, f_full, nullptr, h->G.pw, h->G.perm, h->d_f, h->d_q, h->st));
+    f = h->d_f;  // unscaled source in reference node order
+    run_fmm(h, c, h->d_q, out, subtract ? 2 : 1, s.call, f, x_own);
 }
 
 // host vector (N doubles) -> h->d_stage through the pinned buffer; the stream is drained first so the pinned

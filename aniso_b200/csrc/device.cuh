@@ -20,7 +20,7 @@ struct SigmaGrid {
 
 // block-CSR operator (see plan.hpp BlockCSR); all pointers are device memory
 struct DevCSR {
-    int groups = 0, entries = 0, nrows_total = 0, uniform_nrow = 0;
+    int groups = 0, entries = 0, nrows_total = 0, uniform_nrow = 0, uniform_block = 0;
     int64_t nnz = 0;
     int *row_off = nullptr, *nrow = nullptr, *ent_ptr = nullptr, *col_off = nullptr, *ncol = nullptr;
     int64_t* blk_off = nullptr;
@@ -34,8 +34,11 @@ struct DevTree {
     int *pt_off = nullptr, *npts = nullptr;
     unsigned char* flags = nullptr;                             // bit0 leaf, bit1 empty
     double *cheb = nullptr, *tnode = nullptr, *R = nullptr;     // R: [4][r][r]
-    int* leaves = nullptr;                                      // owned non-empty leaves
-    int nleaves = 0;
+    double* RT = nullptr;                                       // R transposed per child: [4][b][a]
+    int* leaves = nullptr;                                      // all non-empty leaves (DFS order)
+    int nleaves = 0, max_leaf = 0;
+    int4* leaf_info = nullptr;                                  // per leaf: node id, pt_off, npts, 0
+    int* child0 = nullptr;                                      // first child (children are consecutive) or -1
 };
 
 // cell-based correction tables (Geometry / singPrecompute data, uploaded once)
@@ -43,6 +46,7 @@ struct DevGeom {
     int sz, deg, c2, rq, nsing, N;
     double dx;
     const double *px, *py, *pw;          // slot order
+    const double *sxn, *syn;             // box-local coordinates (x - cx)/rx, (y - cy)/ry of each slot in its leaf
     const int *perm, *inv_perm;          // slot <-> reference node index
     const double *sqrtw, *interp, *lnorm, *nearMap, *rqx, *rqy, *rqw, *singX, *singY, *singW;
 };
@@ -54,13 +58,17 @@ void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const Sigm
                  double* A, cudaStream_t st);
 // y[row] (=) sum over entries: the HBM-streaming cached apply (K3 / K4)
 void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, cudaStream_t st);
-void launch_scale(int n, const double* x, const double* sig_s, const double* w, double* f, double* q, cudaStream_t st);
+// q = f.*w, f = x or sig_s.*x; f_ref (optional) = f scattered into reference node order
+void launch_scale(int n, const double* x, const double* sig_s, const double* w, const int* perm, double* f_ref, double* q,
+                  cudaStream_t st);
 void launch_p2m(const DevTree& T, const DevGeom& G, const double* q, double* mcharge, cudaStream_t st);
 void launch_m2m(const DevTree& T, int first, int count, double* mcharge, cudaStream_t st);
 void launch_l2l(const DevTree& T, int first, int count, double* mpot, cudaStream_t st);
-// out[p] = pot[p] + L2P(p) for slots [slot0, slot0+n)
+// L2P + tail of the matvec for slots [slot0, slot0+n):  fmm = pot[p] + L2P(p)
+//   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi   (C: fused stencil, f_ref: full unscaled source in reference order)
 void launch_l2p(const DevTree& T, const DevGeom& G, const int* leaf_of_slot, int slot0, int n, const double* mpot,
-                const double* pot, double* out, cudaStream_t st);
+                const double* pot, const double* C, const double* f_ref, const double* x, double* out, int mode,
+                cudaStream_t st);
 // correction stencils: C[(slotcell*c2+q)*nown + (p-slot0)], slotcell in 0..8 ((dr+1)*3+(dc+1))
 void launch_build_stencils(const DevGeom& G, int id, int slot0, int nown, double* c7, double* c8, double* c9, cudaStream_t st);
 // c7/c8 act on the scaled source, c9 ([c2][nown]) on the Legendre coefficients of the unscaled source;

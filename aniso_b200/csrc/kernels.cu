@@ -200,184 +200,6 @@ void launch_probe_kernel(const SigmaGrid& S, int id, int part, int n, const doub
 }
 
 // ------------------------------------------------------------------------------------------------
-// K3/K4 cached apply: y[row] = sum_e sum_s A[blk_e + s*nrow + t] x[col_e + s].
-// One thread per output row; the nrow threads of a row group read nrow consecutive doubles per source index
-// (blocks are stored source-major), so a warp's loads are full 128-byte lines.  The operator is read exactly
-// once per apply and never reused: loads bypass L1 allocation (ld.global.nc.L1::no_allocate).
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ double ld_stream(const double* p) {
-    double v;
-    asm volatile("ld.global.nc.L1::no_allocate.f64 %0, [%1];" : "=d"(v) : "l"(p));
-    return v;
-}
-
-__global__ void __launch_bounds__(128) bsr_apply_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
-                                                        double* __restrict__ y) {
-    const int row = blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= m.nrows_total) return;
-    int g, t, nrow;
-    if (m.uniform_nrow) {
-        nrow = m.uniform_nrow;
-        g = row / nrow;
-        t = row - g * nrow;
-    } else {
-        g = m.row_group[row];
-        t = row - m.grow_ptr[g];
-        nrow = m.nrow[g];
-    }
-    const int e0 = m.ent_ptr[g], e1 = m.ent_ptr[g + 1];
-    double acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
-    for (int e = e0; e < e1; ++e) {
-        const double* __restrict__ blk = A + m.blk_off[e] + t;
-        const double* __restrict__ xs = x + m.col_off[e];
-        const int nc = m.ncol[e];
-        int s = 0;
-        for (; s + 4 <= nc; s += 4) {
-            const double a0 = ld_stream(blk + (size_t)(s + 0) * nrow);
-            const double a1 = ld_stream(blk + (size_t)(s + 1) * nrow);
-            const double a2 = ld_stream(blk + (size_t)(s + 2) * nrow);
-            const double a3 = ld_stream(blk + (size_t)(s + 3) * nrow);
-            acc0 = fma(a0, __ldg(xs + s + 0), acc0);
-            acc1 = fma(a1, __ldg(xs + s + 1), acc1);
-            acc2 = fma(a2, __ldg(xs + s + 2), acc2);
-            acc3 = fma(a3, __ldg(xs + s + 3), acc3);
-        }
-        for (; s < nc; ++s) acc0 = fma(ld_stream(blk + (size_t)s * nrow), __ldg(xs + s), acc0);
-    }
-    y[m.row_off[g] + t] = (acc0 + acc1) + (acc2 + acc3);
-}
-
-void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, cudaStream_t st) {
-    if (m.nrows_total == 0) return;
-    bsr_apply_kernel<<<(m.nrows_total + 127) / 128, 128, 0, st>>>(m, A, x, y);
-}
-
-// ------------------------------------------------------------------------------------------------
-// K5/K6 Chebyshev passes (bbfmm.h:825-861, 1066-1113)
-// ------------------------------------------------------------------------------------------------
-// S(x, m) = (2 sum_k T_k(x) T_k(t_m) - 1)/np   (bbfmm.h:635-656, 742-746)
-__device__ __forceinline__ double cheb_weight(const double* __restrict__ tnode, int np, double x, int m) {
-    double s = -1.0, t0 = 1.0, t1 = x;
-    for (int k = 0; k < np; ++k) {
-        double tk = k == 0 ? 1.0 : x;
-        if (k >= 2) {
-            tk = 2.0 * x * t1 - t0;
-            t0 = t1;
-            t1 = tk;
-        }
-        s += 2.0 * tk * __ldg(tnode + m * np + k);
-    }
-    return s / np;
-}
-
-__global__ void scale_kernel(int n, const double* __restrict__ x, const double* __restrict__ sig_s, const double* __restrict__ w,
-                             double* __restrict__ f, double* __restrict__ q) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const double v = sig_s ? x[i] * sig_s[i] : x[i];
-    if (f) f[i] = v;
-    q[i] = v * w[i];
-}
-void launch_scale(int n, const double* x, const double* sig_s, const double* w, double* f, double* q, cudaStream_t st) {
-    scale_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, x, sig_s, w, f, q);
-}
-
-// P2M: nodeCharge[j*np+i] = sum_k Sx(k,i) Sy(k,j) q_k over the leaf's points (bbfmm.h:723-759, 832-844).
-// r threads per leaf; the leaf list covers ALL non-empty leaves (the upward pass is replicated on every rank,
-// SURVEY 8e).
-__global__ void p2m_kernel(DevTree T, DevGeom G, const int* __restrict__ leaves, int nleaves, const double* __restrict__ q,
-                           double* __restrict__ mcharge) {
-    const int r = T.r, np = T.np;
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int li = gid / r, mth = gid - li * r;
-    if (li >= nleaves) return;
-    const int id = leaves[li];
-    const double cx = T.cx[id], cy = T.cy[id], rx = T.rx[id], ry = T.ry[id];
-    const int off = T.pt_off[id], n = T.npts[id];
-    const int i = mth % np, j = mth / np;
-    double acc = 0;
-    for (int k = 0; k < n; ++k) {
-        const double sx = (G.px[off + k] - cx) / rx, sy = (G.py[off + k] - cy) / ry;
-        acc += cheb_weight(T.tnode, np, sx, i) * cheb_weight(T.tnode, np, sy, j) * q[off + k];
-    }
-    mcharge[(size_t)id * r + mth] = acc;
-}
-
-// M2M: parent[b] = sum_{c non-empty} sum_a R[c][a][b] child_c[a]  (bbfmm.h:855-859)
-__global__ void m2m_kernel(DevTree T, int first, int count, double* __restrict__ mcharge) {
-    const int r = T.r;
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ni = gid / r, b = gid - ni * r;
-    if (ni >= count) return;
-    const int id = first + ni;
-    if (T.flags[id] & 1) return;  // leaf: set by P2M (or empty)
-    double acc = 0;
-    for (int c = 0; c < 4; ++c) {
-        const int ch = T.child[id * 4 + c];
-        if (T.flags[ch] & 2) continue;
-        const double* __restrict__ Rc = T.R + (size_t)c * r * r;
-        const double* __restrict__ src = mcharge + (size_t)ch * r;
-        for (int a = 0; a < r; ++a) acc = fma(__ldg(Rc + a * r + b), src[a], acc);
-    }
-    mcharge[(size_t)id * r + b] = acc;
-}
-
-// L2L: child[a] += sum_b R[index][a][b] parent[b]  (bbfmm.h:1070-1071)
-__global__ void l2l_kernel(DevTree T, int first, int count, double* __restrict__ mpot) {
-    const int r = T.r;
-    const int gid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int ni = gid / r, a = gid - ni * r;
-    if (ni >= count) return;
-    const int id = first + ni;
-    if (T.flags[id] & 2) return;
-    const int par = T.parent[id];
-    const double* __restrict__ Rc = T.R + (size_t)T.index[id] * r * r + (size_t)a * r;
-    const double* __restrict__ src = mpot + (size_t)par * r;
-    double acc = 0;
-    for (int b = 0; b < r; ++b) acc = fma(__ldg(Rc + b), src[b], acc);
-    mpot[(size_t)id * r + a] += acc;
-}
-
-// L2P + P2P sum: out[p] = pot[p] + sum_{i,j} Sx(p,i) Sy(p,j) nodePotential[leaf][j*np+i]  (bbfmm.h:1104-1113)
-__global__ void l2p_kernel(DevTree T, DevGeom G, const int* __restrict__ leaf_of_slot, int slot0, int n,
-                           const double* __restrict__ mpot, const double* __restrict__ pot, double* __restrict__ out) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    const int p = slot0 + k;
-    const int id = leaf_of_slot[p];
-    const int np = T.np;
-    const double sx = (G.px[p] - T.cx[id]) / T.rx[id], sy = (G.py[p] - T.cy[id]) / T.ry[id];
-    const double* __restrict__ mp = mpot + (size_t)id * T.r;
-    double acc = 0;
-    for (int j = 0; j < np; ++j) {
-        const double wy = cheb_weight(T.tnode, np, sy, j);
-        for (int i = 0; i < np; ++i) acc += cheb_weight(T.tnode, np, sx, i) * wy * mp[j * np + i];
-    }
-    out[k] = pot[p] + acc;
-}
-
-void launch_p2m(const DevTree& T, const DevGeom& G, const double* q, double* mcharge, cudaStream_t st) {
-    const long threads = (long)T.nleaves * T.r;
-    if (threads == 0) return;
-    p2m_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(T, G, T.leaves, T.nleaves, q, mcharge);
-}
-void launch_m2m(const DevTree& T, int first, int count, double* mcharge, cudaStream_t st) {
-    const long threads = (long)count * T.r;
-    if (threads == 0) return;
-    m2m_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(T, first, count, mcharge);
-}
-void launch_l2l(const DevTree& T, int first, int count, double* mpot, cudaStream_t st) {
-    const long threads = (long)count * T.r;
-    if (threads == 0) return;
-    l2l_kernel<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(T, first, count, mpot);
-}
-void launch_l2p(const DevTree& T, const DevGeom& G, const int* leaf_of_slot, int slot0, int n, const double* mpot,
-                const double* pot, double* out, cudaStream_t st) {
-    if (n == 0) return;
-    l2p_kernel<<<(n + 127) / 128, 128, 0, st>>>(T, G, leaf_of_slot, slot0, n, mpot, pot, out);
-}
-
-// ------------------------------------------------------------------------------------------------
 // K7 + K8 + K9 corrections.  All three are linear in the (unscaled) source with support in the 3x3 cell
 // neighbourhood of the target, so each is stored once per kernel id as a stencil
 //     C[(cs*c2 + q)*nown + k],  cs = (dr+1)*3 + (dc+1),  k = target slot - slot0

@@ -484,6 +484,11 @@ static void finish_csr(BlockCSR& b) {
     b.grow_ptr.assign(groups + 1, 0);
     for (int g = 0; g < groups; ++g) b.grow_ptr[g + 1] = b.grow_ptr[g] + b.nrow[g];
     b.nrows_total = b.grow_ptr[groups];
+    b.uniform_block = groups ? b.nrow[0] : 0;
+    for (int g = 0; g < groups; ++g)
+        if (b.nrow[g] != b.uniform_block) b.uniform_block = 0;
+    for (int nc : b.ncol)
+        if (nc != b.uniform_block) b.uniform_block = 0;
     b.row_group.resize(b.nrows_total);
     for (int g = 0; g < groups; ++g)
         for (int k = b.grow_ptr[g]; k < b.grow_ptr[g + 1]; ++k) b.row_group[k] = g;
@@ -574,6 +579,7 @@ void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, i
     if (sr < 1 || sr > 128) throw std::runtime_error("The degree is not implemented.");
     if (K < 1) throw std::runtime_error("kernel_size must be >= 1");
     if (np < 1) throw std::runtime_error("np must be >= 1");
+    if (np > 16) throw std::runtime_error("np > 16 (rank > 256) is not supported by the device kernels");
     if ((double)sz * sz * deg * deg > 2.0e9) throw std::runtime_error("number of nodes exceeds index_t (int)");
     p = HostPlan();
     p.sz = sz; p.deg = deg; p.K = K; p.kernelSize = 2 * K - 1; p.g = g; p.sr = sr; p.np = np; p.maxLevelArg = maxLevel;

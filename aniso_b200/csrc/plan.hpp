@@ -41,6 +41,7 @@ struct BlockCSR {
     std::vector<int> grow_ptr;            // groups+1: launch rows of group g are [grow_ptr[g], grow_ptr[g+1])
     std::vector<int> row_group;           // per launch row -> group
     int uniform_nrow = 0;                 // >0 when every group has this many rows (M2L: r)
+    int uniform_block = 0;                // >0 when every block is uniform_block x uniform_block
     int64_t nnz = 0;                      // total doubles of operator storage
     int nrows_total = 0;                  // launch rows
 };

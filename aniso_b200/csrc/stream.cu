@@ -1,0 +1,168 @@
+// K3/K4 cached apply: y[row] = sum_e sum_s A[blk_e + s*nrow + t] x[col_e + s]  (downPassFast, bbfmm.h:1051-1065 and
+// 1081-1099).  HBM-bound: the operator blocks (5.9 GB at N = 2^20) are read exactly once per matvec and never reused,
+// so every load of A bypasses L1 allocation and the kernels are organised around keeping enough bytes in flight.
+//
+//   bsr_apply_warp_kernel<R>   all blocks R x R with 64 % R == 0 (np = 4 -> R 16, np = 8 -> R 64; also the P2P tiles of
+//                              uniform 16- or 64-point leaves).  The blocks of one target are contiguous, so a warp
+//                              walks them as one linear stream of 16-byte loads; each lane always lands on the same
+//                              target pair (t, t+1), accumulates in registers, and a few shuffles finish the sum.
+//   bsr_apply_row_kernel       any block shape: one thread per output row, 8 independent 8-byte loads in flight,
+//                              next entry's metadata prefetched.
+#include <cstdlib>
+
+#include "device.cuh"
+
+namespace an {
+
+// Streaming loads: no L1 allocation, and an L2 evict-first policy so that the 5.9 GB operator stream does not flush the
+// ~100 MB of vectors, tree tables and multipole/local coefficients that every other kernel of the matvec re-reads
+// (the L2 holds 126 MB).
+__device__ __forceinline__ uint64_t stream_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ double ld_stream(const double* p, uint64_t pol) {
+    double v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(v) : "l"(p), "l"(pol));
+    return v;
+}
+__device__ __forceinline__ double2 ld_stream2(const double2* p, uint64_t pol) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0, %1}, [%2], %3;"
+                 : "=d"(v.x), "=d"(v.y)
+                 : "l"(p), "l"(pol));
+    return v;
+}
+
+template <int R>
+__global__ void __launch_bounds__(256) bsr_apply_warp_kernel(DevCSR m, const double* __restrict__ A,
+                                                             const double* __restrict__ x, double* __restrict__ y) {
+    constexpr int PAIRS = R * R / 2;  // double2 per block
+    constexpr int ITERS = PAIRS / 32;
+    static_assert(64 % R == 0 && PAIRS % 32 == 0, "lane -> target pair must be loop invariant");
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (g >= m.groups) return;
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const uint64_t pol = stream_policy();
+    const double2* __restrict__ base = reinterpret_cast<const double2*>(A + m.blk_off[e0]);
+    // source index of this lane inside a block for iteration it: s = (it*64 + 2*lane) / R
+    const int s_lane = (2 * lane) / R;
+    constexpr int S_STEP = 64 / R;
+    constexpr int CH = ITERS < 4 ? ITERS : 4;  // iterations per chunk: 2*CH 16-byte loads in flight per lane
+    double acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
+    for (int eb = 0; eb < ne; eb += 32) {
+        const int cnt = min(32, ne - eb);
+        const int mycol = lane < cnt ? m.col_off[e0 + eb + lane] : 0;
+        int j = 0;
+        for (; j + 2 <= cnt; j += 2) {  // two blocks per trip
+            const int c0 = __shfl_sync(0xffffffffu, mycol, j) + s_lane, c1 = __shfl_sync(0xffffffffu, mycol, j + 1) + s_lane;
+            const double2* __restrict__ b0 = base + (size_t)(eb + j) * PAIRS + lane;
+            const double2* __restrict__ b1 = b0 + PAIRS;
+#pragma unroll 1
+            for (int it0 = 0; it0 < ITERS; it0 += CH) {
+                double2 a0[CH], a1[CH];
+#pragma unroll
+                for (int u = 0; u < CH; ++u) {
+                    a0[u] = ld_stream2(b0 + (it0 + u) * 32, pol);
+                    a1[u] = ld_stream2(b1 + (it0 + u) * 32, pol);
+                }
+#pragma unroll
+                for (int u = 0; u < CH; ++u) {
+                    const double x0 = __ldg(x + c0 + (it0 + u) * S_STEP), x1 = __ldg(x + c1 + (it0 + u) * S_STEP);
+                    acc0 = fma(a0[u].x, x0, acc0);
+                    acc1 = fma(a0[u].y, x0, acc1);
+                    acc2 = fma(a1[u].x, x1, acc2);
+                    acc3 = fma(a1[u].y, x1, acc3);
+                }
+            }
+        }
+        if (j < cnt) {
+            const int c0 = __shfl_sync(0xffffffffu, mycol, j) + s_lane;
+            const double2* __restrict__ b0 = base + (size_t)(eb + j) * PAIRS + lane;
+#pragma unroll 1
+            for (int it0 = 0; it0 < ITERS; it0 += CH) {
+                double2 a0[CH];
+#pragma unroll
+                for (int u = 0; u < CH; ++u) a0[u] = ld_stream2(b0 + (it0 + u) * 32, pol);
+#pragma unroll
+                for (int u = 0; u < CH; ++u) {
+                    const double x0 = __ldg(x + c0 + (it0 + u) * S_STEP);
+                    acc0 = fma(a0[u].x, x0, acc0);
+                    acc1 = fma(a0[u].y, x0, acc1);
+                }
+            }
+        }
+    }
+    acc0 += acc2;
+    acc1 += acc3;
+#pragma unroll
+    for (int off = 16; off >= R / 2; off >>= 1) {  // lanes l, l + R/2, l + R, ... hold the same target pair
+        acc0 += __shfl_down_sync(0xffffffffu, acc0, off);
+        acc1 += __shfl_down_sync(0xffffffffu, acc1, off);
+    }
+    if (lane < R / 2) {
+        double* __restrict__ out = y + m.row_off[g] + 2 * lane;
+        out[0] = acc0;
+        out[1] = acc1;
+    }
+}
+
+__global__ void __launch_bounds__(128) bsr_apply_row_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
+                                                            double* __restrict__ y) {
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= m.nrows_total) return;
+    int g, t, nrow;
+    if (m.uniform_nrow) {
+        nrow = m.uniform_nrow;
+        g = row / nrow;
+        t = row - g * nrow;
+    } else {
+        g = m.row_group[row];
+        t = row - m.grow_ptr[g];
+        nrow = m.nrow[g];
+    }
+    const int e0 = m.ent_ptr[g], e1 = m.ent_ptr[g + 1];
+    const uint64_t pol = stream_policy();
+    double acc[4] = {0, 0, 0, 0};
+    // software pipeline over the entry metadata: the loads of entry e+1 are issued before the block of e is consumed
+    int64_t boff = e0 < e1 ? m.blk_off[e0] : 0;
+    int coff = e0 < e1 ? m.col_off[e0] : 0, nc = e0 < e1 ? m.ncol[e0] : 0;
+    for (int e = e0; e < e1; ++e) {
+        const double* __restrict__ blk = A + boff + t;
+        const double* __restrict__ xs = x + coff;
+        const int ncur = nc;
+        if (e + 1 < e1) {
+            boff = m.blk_off[e + 1];
+            coff = m.col_off[e + 1];
+            nc = m.ncol[e + 1];
+        }
+        int s = 0;
+        for (; s + 8 <= ncur; s += 8) {
+            double a[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) a[u] = ld_stream(blk + (size_t)(s + u) * nrow, pol);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) acc[u & 3] = fma(a[u], __ldg(xs + s + u), acc[u & 3]);
+        }
+        for (; s < ncur; ++s) acc[0] = fma(ld_stream(blk + (size_t)s * nrow, pol), __ldg(xs + s), acc[0]);
+    }
+    y[m.row_off[g] + t] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
+void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, cudaStream_t st) {
+    if (m.nrows_total == 0) return;
+    const unsigned warps_per_cta = 8, ctas = (m.groups + warps_per_cta - 1) / warps_per_cta;
+    static const bool force_row = getenv("ANISO_BSR_ROW") != nullptr;  // A/B switch for profiling only
+    if (force_row)
+        bsr_apply_row_kernel<<<(m.nrows_total + 127) / 128, 128, 0, st>>>(m, A, x, y);
+    else if (m.uniform_block == 16)
+        bsr_apply_warp_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, y);
+    else if (m.uniform_block == 64)
+        bsr_apply_warp_kernel<64><<<ctas, 256, 0, st>>>(m, A, x, y);
+    else
+        bsr_apply_row_kernel<<<(m.nrows_total + 127) / 128, 128, 0, st>>>(m, A, x, y);
+}
+
+}  // namespace an
