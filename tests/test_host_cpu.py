@@ -1,0 +1,164 @@
+"""CPU tests (no GPU): the C-ABI library loads and exports every symbol include/aniso_b200.h declares, the host-side
+set-up (geometry tables, Gauss-Legendre rules, quadtree and interaction lists, leaf partition) reproduces the golden
+fixtures generated from the compiled reference, and compute entry points fail loudly without a device."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SMALL = ["a16", "b8d3", "h32", "nu6d5", "ml12d2"]
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from aniso_b200 import _lib
+
+    if not os.path.exists(_lib.LIB_PATH):
+        subprocess.check_call(["make", "-s", "-j4", "-C", os.path.join(ROOT, "aniso_b200", "csrc")])
+    return _lib.load()
+
+
+def make(name):
+    from aniso_b200 import Aniso
+
+    sz, deg, K, g, sr, np_, ml, kind = cases.CASES[name]
+    return Aniso(sz, deg, K, g, sr, np_, ml)
+
+
+def test_header_symbols_exported(lib):
+    from aniso_b200 import _lib
+
+    hdr = open(os.path.join(ROOT, "include", "aniso_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(aniso_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 40
+    for name in declared:
+        assert hasattr(lib, name), "symbol %s declared in aniso_b200.h but not exported" % name
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+
+
+def test_gl_tables_bit_exact(lib, golden):
+    from aniso_b200.api import gl_table
+    from aniso_b200 import AnisoError
+
+    g = golden("gl_tables")
+    for d in range(1, 129):
+        x, w = gl_table(d)
+        assert np.array_equal(x, g["x%d" % d]) and np.array_equal(w, g["w%d" % d]), d
+    with pytest.raises(AnisoError):  # "The degree is not implemented." Quadrature.cpp:22189-22191
+        gl_table(129)
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_geometry_tables(lib, golden, name):
+    g = golden(name)
+    a = make(name)
+    x, y, w = a.nodes()
+    assert np.array_equal(x, g["x"]) and np.array_equal(y, g["y"]) and np.array_equal(w, g["w"])
+    assert np.array_equal(a.getNodes(), np.stack([g["x"], g["y"]], axis=1))
+    for k, v in a.geometry_tables().items():
+        np.testing.assert_allclose(v, g["geo_" + k], rtol=0, atol=1e-15)
+    for got, want in zip(a.sing_tables(), (g["singX"], g["singY"], g["singW"])):
+        np.testing.assert_allclose(got, want, rtol=0, atol=1e-15)
+    a.delete()
+
+
+@pytest.mark.parametrize("name", SMALL + ["c2", "c1"])
+def test_tree_matches_reference(lib, golden, name):
+    g = golden(name)
+    a = make(name)
+    ts = a.tree_stats()
+    got = [ts[k] for k in ("nodes", "leaves", "max_level", "sumU", "sumV", "sumW", "sumX", "p2p_pairs", "max_leaf")]
+    assert got == list(g["tree_stats"])
+    if "tree_geom" in g:  # same boxes as the reference tree (numbering differs: compare as sorted sets)
+        geom, info = a.tree_nodes()
+        key = lambda G, I: sorted(zip(I[:, 0], np.round(G[:, 1], 12), np.round(G[:, 0], 12), I[:, 1], I[:, 2]))
+        assert key(geom, info) == key(g["tree_geom"], g["tree_info"])
+        # parent links are consistent with the geometry
+        for i in range(1, len(geom)):
+            p = info[i, 3]
+            assert info[p, 0] == info[i, 0] - 1
+            assert abs(geom[p, 2] - 2 * geom[i, 2]) < 1e-15 and abs(abs(geom[p, 0] - geom[i, 0]) - geom[i, 2]) < 1e-12
+    a.delete()
+
+
+def test_interaction_lists_against_oracle(lib):
+    """U/V/W/X lists node by node (non-uniform tree with W and X entries) against the CPU oracle."""
+    from oracle import oracleapi
+
+    sz, deg, K, g, sr, np_, ml, kind = cases.CASES["nu6d5"]
+    a = make("nu6d5")
+    o = oracleapi.OracleAniso(sz, deg, K, g, sr, np_, ml)
+    x, y, _ = o.nodes()
+    o.set_coeff(*cases.sigma_fields(kind, x, y, sz, deg))  # builds the oracle tree
+    ga, ia = a.tree_nodes()
+    go, io = o.tree_nodes()
+    box = lambda G, I, i: (int(I[i, 0]), round(float(G[i, 0]), 12), round(float(G[i, 1]), 12))
+    omap = {box(go, io, i): i for i in range(len(go))}
+    seen_w = seen_x = 0
+    for i in range(len(ga)):
+        ids, kinds = a.node_lists(i)
+        oid, okinds = o.node_lists(omap[box(ga, ia, i)])
+        mine = sorted((int(k), box(ga, ia, int(j))) for j, k in zip(ids, kinds))
+        theirs = sorted((int(k), box(go, io, int(j))) for j, k in zip(oid, okinds))
+        assert mine == theirs, i
+        seen_w += int((kinds == 3).sum())
+        seen_x += int((kinds == 1).sum())
+    assert seen_w == 704 and seen_x == 704
+    a.delete()
+
+
+@pytest.mark.parametrize("name,nranks", [("c2", 2), ("c2", 4), ("c2", 8), ("nu6d5", 3), ("a16", 8)])
+def test_partition_covers_and_balances(lib, name, nranks):
+    a = make(name)
+    n = a.numberOfNodes
+    ranges = [a.partition(nranks, r) for r in range(nranks)]
+    assert ranges[0][0] == 0 and ranges[-1][1] == n
+    for (b0, e0, _), (b1, e1, _) in zip(ranges, ranges[1:]):
+        assert e0 == b1 and b0 <= e0
+    perm = a.slot_permutation()
+    assert sorted(perm) == list(range(n))
+    if name == "c2":  # uniform tree: near-equal shares
+        sizes = [e - b for b, e, _ in ranges]
+        assert max(sizes) <= 1.25 * n / nranks
+    a.delete()
+
+
+def test_compute_fails_loudly_without_device(lib):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    from aniso_b200 import AnisoError
+
+    a = make("a16")
+    with pytest.raises(AnisoError) as e:
+        a.setCoeff(np.ones(a.numberOfNodes), np.ones(a.numberOfNodes))
+    assert e.value.code == -2 and "no CPU fallback" in str(e.value)
+    with pytest.raises(AnisoError):
+        a.mapping(np.ones(a.numberOfNodes), 0)
+    a.delete()
+
+
+def test_bad_arguments(lib):
+    from aniso_b200 import Aniso, AnisoError
+
+    for args in [(0, 1, 1, 0.5, 4, 2, 20), (8, 0, 1, 0.5, 4, 2, 20), (8, 1, 0, 0.5, 4, 2, 20), (8, 1, 1, 0.5, 4, 0, 20),
+                 (8, 1, 1, 0.5, 4, 17, 20)]:
+        with pytest.raises(AnisoError):
+            Aniso(*args)
+
+
+def test_product_does_not_import_oracle():
+    """the product package must never route through the CPU oracle"""
+    for root, _, files in os.walk(os.path.join(ROOT, "aniso_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".hpp", ".cuh", ".h")):
+                src = open(os.path.join(root, f)).read()
+                assert "oracle" not in src.lower(), os.path.join(root, f)
