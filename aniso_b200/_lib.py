@@ -39,6 +39,7 @@ SIGNATURES = {
     "aniso_set_coeff": (C.c_int, [_H, _dp, _dp]),
     "aniso_sigma_coeff": (C.c_int, [_H, _dp, _dp]),
     "aniso_cache": (C.c_int, [_H, C.c_int]),
+    "aniso_cache_part": (C.c_int, [_H, C.c_int, C.c_int]),
     "aniso_cache_bytes": (C.c_size_t, [_H, C.c_int]),
     "aniso_cache_counts": (C.c_int, [_H, _lp]),
     "aniso_cache_times": (C.c_int, [_H, _dp]),

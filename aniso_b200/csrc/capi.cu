@@ -654,6 +654,19 @@ int aniso_cache(aniso_t* h, int id) {
     API_END
 }
 
+int aniso_cache_part(aniso_t* h, int id, int part) {
+    API_BEGIN
+    REQUIRE(h && part >= 0 && part <= 3, "bad arguments");
+    check_id(h, id);
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (part == 0) ensure_stencils(h, id);
+    else ensure_ops(h, id, part);
+    CK(cudaStreamSynchronize(h->st));
+    return ANISO_OK;
+    API_END
+}
+
 size_t aniso_cache_bytes(const aniso_t* h, int id) {
     if (!h) return 0;
     size_t b = 0;

@@ -95,6 +95,10 @@ int aniso_sigma_coeff(aniso_t* h, double* coeff_t_host, double* coeff_s_host);
  * singularAddCache (KernelFactory.cpp:323-334, 279-288, 550-609, 752-788): evaluates every P2P/M2L operator block
  * of kernel `id` on the device (fused real+imag), and the correction stencils. */
 int aniso_cache(aniso_t* h, int id);
+/* The four cache steps of the reference one at a time (main.cpp:60-76): part = ANISO_PART_IMAG: runKernelsCache
+ * (KernelFactory.cpp:323-334), ANISO_PART_REAL: runKernelsCacheSing (:279-288), ANISO_PART_BOTH: the fused operators
+ * aniso_cache builds, 0: refineAddOnCache + singularAddCache (+ the nearRemoval table) as correction stencils. */
+int aniso_cache_part(aniso_t* h, int id, int part);
 /* bytes held for kernel id (Aniso::displayKernelCacheSize, Aniso.cpp:19-47) */
 size_t aniso_cache_bytes(const aniso_t* h, int id);
 /* number of kernel evaluations the last aniso_cache(id) performed: out[0] = P2P pairs, out[1] = M2L pairs */
