@@ -34,6 +34,7 @@ static int fail(int code, const std::string& msg) {
 struct OperatorCache {  // Cache[node][slot] of bbfmm.h:466, flattened
     double* p2p = nullptr;
     double* m2l = nullptr;
+    double sign = 1.0;  // (-1)^id
 };
 struct StencilCache {
     double *c7 = nullptr, *c8 = nullptr, *c9 = nullptr, *call = nullptr;
@@ -46,6 +47,7 @@ struct aniso_handle {
     std::vector<int> all_slot_begin, all_slot_end;  // ownership of every rank
     bool dev_ready = false, coeff_set = false;
     cudaStream_t st = nullptr;
+    int m2l_top_groups = 0;  // M2L groups of the first level that has V lists (a prefix: level-major numbering)
     std::vector<void*> allocs;
     DevTree T;
     DevGeom G;
@@ -95,6 +97,11 @@ void dfree(aniso_handle* h, void* p) {
 
 DevCSR upload_csr(aniso_handle* h, const BlockCSR& b) {
     DevCSR d;
+    {
+        std::vector<int> gof(h->plan.nodes.size(), -1);
+        for (size_t g = 0; g < b.group_node.size(); ++g) gof[b.group_node[g]] = (int)g;
+        d.group_of_node = upload(h, gof);
+    }
     d.groups = (int)b.nrow.size();
     d.entries = (int)b.col_off.size();
     d.nrows_total = b.nrows_total;
@@ -111,6 +118,13 @@ DevCSR upload_csr(aniso_handle* h, const BlockCSR& b) {
     d.src_node = upload(h, b.src_node);
     d.grow_ptr = upload(h, b.grow_ptr);
     d.row_group = upload(h, b.row_group);
+    d.symmetric = b.symmetric ? 1 : 0;
+    d.scratch_rows = b.scratch_rows;
+    if (b.symmetric) {
+        d.mirror_row = upload(h, b.mirror_row);
+        d.srow_ptr = upload(h, b.srow_ptr);
+        d.scratch = dalloc<double>(h, (size_t)b.scratch_rows * b.uniform_block);
+    }
     return d;
 }
 
@@ -193,12 +207,16 @@ void ensure_device(aniso_handle* h) {
                     if (n.child[c] != n.child[0] + c) throw std::runtime_error("internal: children not consecutive");
         }
         T.leaf_info = upload(h, info); T.child0 = upload(h, child0);
+        T.level_ptr = upload(h, p.level_ptr);
     }
     h->d_leaf_of_slot = upload(h, p.leaf_of_slot);
     h->m2l = upload_csr(h, p.m2l);
     h->p2p = upload_csr(h, p.p2p);
     h->first_m2l_level = T.nlevels;
-    for (int t : p.m2l.tgt_node) h->first_m2l_level = std::min(h->first_m2l_level, p.nodes[t].level);
+    for (int g : p.m2l.group_node) h->first_m2l_level = std::min(h->first_m2l_level, p.nodes[g].level);
+    h->m2l_top_groups = 0;
+    for (int g : p.m2l.group_node)
+        if (p.nodes[g].level == h->first_m2l_level) ++h->m2l_top_groups;
     // sigma grid
     h->d_chat = dalloc<double>(h, N);
     h->d_sig_s = dalloc<double>(h, N);
@@ -441,6 +459,18 @@ int aniso_owned_range(const aniso_t* h, int* slot_begin, int* slot_end) {
 // ---------------------------------------------------------------------------------------------------
 namespace {
 
+// the same block-CSR restricted to groups [g0, g0+count): used to launch the M2L of one level range
+DevCSR sub_range(const DevCSR& m, int g0, int count) {
+    DevCSR s = m;
+    s.groups = count;
+    s.row_off += g0;
+    s.nrow += g0;
+    s.ent_ptr += g0;
+    if (s.srow_ptr) s.srow_ptr += g0;
+    s.nrows_total = count * m.uniform_nrow;
+    return s;
+}
+
 void free_caches(aniso_handle* h) {
     for (auto& kv : h->ops) {
         dfree(h, kv.second.p2p);
@@ -464,6 +494,7 @@ OperatorCache& ensure_ops(aniso_handle* h, int id, int part) {
     if (it != h->ops.end()) return it->second;
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede cache/mapping");
     OperatorCache c;
+    c.sign = (id & 1) ? -1.0 : 1.0;
     c.p2p = dalloc<double>(h, (size_t)h->p2p.nnz);
     c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz);
     cudaEvent_t ev[3];
@@ -512,16 +543,25 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
              const double* f = nullptr, const double* x_own = nullptr) {
     const HostPlan& p = h->plan;
     const DevTree& T = h->T;
-    const int L0 = h->first_m2l_level;
+    const int L0 = h->first_m2l_level, deepest = T.nlevels - 1;
+    const bool sym_m = h->m2l.symmetric, sym_p = h->p2p.symmetric;
+    auto count = [&](int L) { return p.level_ptr[L + 1] - p.level_ptr[L]; };
+    // levels [L0, Lt] hold at most 256 nodes each (a single CTA is slower than a launch beyond that): one single-CTA launch walks them (top of the tree)
+    int Lt = L0 - 1;
+    while (Lt + 1 <= deepest && count(Lt + 1) <= 256) ++Lt;
     LAUNCH(h, launch_p2m(T, h->G, q, h->d_mcharge, h->st));
-    for (int L = T.nlevels - 2; L >= L0; --L)
-        LAUNCH(h, launch_m2m(T, p.level_ptr[L], p.level_ptr[L + 1] - p.level_ptr[L], h->d_mcharge, h->st));
-    CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
-    LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, h->st));
-    for (int L = L0 + 1; L < T.nlevels; ++L)
-        LAUNCH(h, launch_l2l(T, p.level_ptr[L], p.level_ptr[L + 1] - p.level_ptr[L], h->d_mpot, h->st));
-    LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, h->st));
-    LAUNCH(h, launch_l2p(T, h->G, h->d_leaf_of_slot, h->slot0, h->nown, h->d_mpot, h->d_pot, stencil, f, x_own, out, mode, h->st));
+    for (int L = deepest - 1; L >= L0 && L > Lt; --L) LAUNCH(h, launch_m2m(T, p.level_ptr[L], count(L), h->d_mcharge, h->st));
+    if (std::min(Lt, deepest - 1) >= L0) LAUNCH(h, launch_m2m_top(T, std::min(Lt, deepest - 1), L0, h->d_mcharge, h->st));
+    if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
+    LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
+    if (sym_m && h->m2l_top_groups > 0)  // level L0 has no L2L step: finish its sums here, every other level folds them in L2L
+        LAUNCH(h, launch_bsr_reduce(sub_range(h->m2l, 0, h->m2l_top_groups), h->d_mpot, h->st));
+    if (Lt >= L0 + 1) LAUNCH(h, launch_l2l_top(T, h->m2l, sym_m, L0 + 1, Lt, h->d_mpot, h->st));
+    for (int L = std::max(L0 + 1, Lt + 1); L <= deepest; ++L)
+        LAUNCH(h, launch_l2l(T, h->m2l, sym_m, p.level_ptr[L], count(L), h->d_mpot, h->st));
+    LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, h->st));
+    LAUNCH(h, launch_l2p(T, h->G, h->p2p, sym_p, h->d_leaf_of_slot, h->slot0, h->nown, h->d_mpot, h->d_pot, stencil, f, x_own, out,
+                         mode, h->st));
 }
 
 // all-gather of the owned shards into a full slot-order vector; counts differ per rank, so this is a
@@ -1023,8 +1063,10 @@ int aniso_from_slots(aniso_t* h, const double* dev, double* host) {
 int64_t aniso_launch_count(const aniso_t* h) { return h ? h->launches : 0; }
 int aniso_apply_bytes(const aniso_t* h, int64_t out[3]) {
     if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
-    out[0] = h->plan.p2p.nnz * 8;
-    out[1] = h->plan.m2l.nnz * 8;
+    // bytes the streaming kernels must move per matvec: stored operator blocks (half of the pairs under symmetric
+    // storage) plus one scratch row (8R bytes) written per target and per dropped block
+    out[0] = h->plan.p2p.nnz * 8 + (int64_t)h->plan.p2p.scratch_rows * h->plan.p2p.uniform_block * 8;
+    out[1] = h->plan.m2l.nnz * 8 + (int64_t)h->plan.m2l.scratch_rows * h->plan.m2l.uniform_block * 8;
     out[2] = (int64_t)9 * h->plan.c2 * h->nown * 8;
     return ANISO_OK;
 }
@@ -1040,8 +1082,8 @@ int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms) {
     CK(cudaEventCreate(&e1));
     CK(cudaEventRecord(e0, h->st));
     for (int i = 0; i < reps; ++i) {
-        if (which == 0) LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, h->st));
-        else LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, h->d_q, h->d_pot, h->st));
+        if (which == 0) LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
+        else LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, h->d_q, h->d_pot, c.sign, false, h->st));
     }
     CK(cudaEventRecord(e1, h->st));
     CK(cudaEventSynchronize(e1));

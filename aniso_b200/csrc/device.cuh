@@ -25,6 +25,10 @@ struct DevCSR {
     int *row_off = nullptr, *nrow = nullptr, *ent_ptr = nullptr, *col_off = nullptr, *ncol = nullptr;
     int64_t* blk_off = nullptr;
     int *tgt_node = nullptr, *src_node = nullptr, *grow_ptr = nullptr, *row_group = nullptr;
+    int symmetric = 0, scratch_rows = 0;                       // symmetric storage, see plan.hpp
+    int *mirror_row = nullptr, *srow_ptr = nullptr;
+    int* group_of_node = nullptr;                              // tree node -> group (or -1)
+    double* scratch = nullptr;                                 // [scratch_rows][uniform_block]
 };
 
 struct DevTree {
@@ -37,6 +41,7 @@ struct DevTree {
     double* RT = nullptr;                                       // R transposed per child: [4][b][a]
     int* leaves = nullptr;                                      // all non-empty leaves (DFS order)
     int nleaves = 0, max_leaf = 0;
+    int* level_ptr = nullptr;                                   // nodes of level L: [level_ptr[L], level_ptr[L+1])
     int4* leaf_info = nullptr;                                  // per leaf: node id, pt_off, npts, 0
     int* child0 = nullptr;                                      // first child (children are consecutive) or -1
 };
@@ -57,16 +62,24 @@ struct DevGeom {
 void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const SigmaGrid& S, int id, int part, int cheb,
                  double* A, cudaStream_t st);
 // y[row] (=) sum over entries: the HBM-streaming cached apply (K3 / K4)
-void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, cudaStream_t st);
+// sign = (-1)^id: parity of the kernel family under source<->target exchange (symmetric storage only)
+// reduce = false (symmetric storage only): leave the per-target sums in the scratch rows for the consumer to fold
+void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, double sign, bool reduce, cudaStream_t st);
+void launch_bsr_reduce(const DevCSR& m, double* y, cudaStream_t st);
 // q = f.*w, f = x or sig_s.*x; f_ref (optional) = f scattered into reference node order
 void launch_scale(int n, const double* x, const double* sig_s, const double* w, const int* perm, double* f_ref, double* q,
                   cudaStream_t st);
 void launch_p2m(const DevTree& T, const DevGeom& G, const double* q, double* mcharge, cudaStream_t st);
 void launch_m2m(const DevTree& T, int first, int count, double* mcharge, cudaStream_t st);
-void launch_l2l(const DevTree& T, int first, int count, double* mpot, cudaStream_t st);
+// fold: the M2L result of each node is still spread over its scratch rows (symmetric storage) and is reduced inside
+void launch_l2l(const DevTree& T, const DevCSR& m2l, bool fold, int first, int count, double* mpot, cudaStream_t st);
+// levels [Llo, Lhi] (at most 1024 nodes each) in one single-CTA launch
+void launch_m2m_top(const DevTree& T, int Lhi, int Llo, double* mcharge, cudaStream_t st);
+void launch_l2l_top(const DevTree& T, const DevCSR& m2l, bool fold, int Llo, int Lhi, double* mpot, cudaStream_t st);
 // L2P + tail of the matvec for slots [slot0, slot0+n):  fmm = pot[p] + L2P(p)
 //   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi   (C: fused stencil, f_ref: full unscaled source in reference order)
-void launch_l2p(const DevTree& T, const DevGeom& G, const int* leaf_of_slot, int slot0, int n, const double* mpot,
+void launch_l2p(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,
+                const double* mpot,
                 const double* pot, const double* C, const double* f_ref, const double* x, double* out, int mode,
                 cudaStream_t st);
 // correction stencils: C[(slotcell*c2+q)*nown + (p-slot0)], slotcell in 0..8 ((dr+1)*3+(dc+1))

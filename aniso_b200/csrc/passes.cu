@@ -139,10 +139,25 @@ __global__ void __launch_bounds__(256) m2m_kernel(DevTree T, int first, int coun
     }
 }
 
-// L2L: child[a] += sum_b R[index][a][b] parent[b]  (bbfmm.h:1070-1071); RT = R transposed ([c][b][a]) so that the
-// threads of a child read consecutive addresses.  Dependent-load depth: parent -> coefficients.
-template <bool SMEM_R>
-__global__ void __launch_bounds__(256) l2l_kernel(DevTree T, int first, int count, double* __restrict__ mpot) {
+// Sum of the scratch rows of one target (symmetric storage, see stream.cu): the fixed-order reduction that completes
+// the cached apply, folded into the kernel that consumes the result.
+__device__ __forceinline__ double fold_rows(const DevCSR& m, int g, int t) {
+    const int R = m.uniform_block, r1 = m.srow_ptr[g + 1];
+    double s0 = 0, s1 = 0;
+    int r = m.srow_ptr[g];
+    for (; r + 2 <= r1; r += 2) {
+        s0 += m.scratch[(size_t)r * R + t];
+        s1 += m.scratch[(size_t)(r + 1) * R + t];
+    }
+    if (r < r1) s0 += m.scratch[(size_t)r * R + t];
+    return s0 + s1;
+}
+
+// L2L: child[a] (+)= sum_b R[index][a][b] parent[b]  (bbfmm.h:1070-1071); RT = R transposed ([c][b][a]) so that the
+// threads of a child read consecutive addresses.  FOLD: the child's own M2L sum is still spread over its scratch rows
+// (symmetric storage) and is reduced here; otherwise it already sits in mpot.  Dependent-load depth: parent -> coefficients.
+template <bool SMEM_R, bool FOLD>
+__global__ void __launch_bounds__(256) l2l_kernel(DevTree T, DevCSR m2l, int first, int count, double* __restrict__ mpot) {
     extern __shared__ double sm[];
     const int r = T.r;
     const int G = max(1, (int)blockDim.x / r);
@@ -160,6 +175,12 @@ __global__ void __launch_bounds__(256) l2l_kernel(DevTree T, int first, int coun
         const int g = o / r, a = o - g * r;
         if (n0 + g >= count) break;
         const int id = first + n0 + g;
+        double own;
+        if (FOLD) {
+            const int grp = m2l.group_of_node[id];
+            own = grp >= 0 ? fold_rows(m2l, grp, a) : 0.0;
+        } else
+            own = mpot[(size_t)id * r + a];
         const size_t roff = (size_t)T.index[id] * r * r + a;
         const double* __restrict__ RT = SMEM_R ? Rs + roff : T.RT + roff;
         const double* __restrict__ src = par + (size_t)g * r;
@@ -171,7 +192,71 @@ __global__ void __launch_bounds__(256) l2l_kernel(DevTree T, int first, int coun
             a1 = fma(SMEM_R ? RT[(size_t)(b + 1) * r] : __ldg(RT + (size_t)(b + 1) * r), src[b + 1], a1);
         }
         if (b < r) a0 = fma(SMEM_R ? RT[(size_t)b * r] : __ldg(RT + (size_t)b * r), src[b], a0);
-        mpot[(size_t)id * r + a] += a0 + a1;
+        mpot[(size_t)id * r + a] = own + (a0 + a1);
+    }
+}
+
+// The top of the tree in one launch each way: the levels with at most 256 nodes are walked by a single CTA with a
+// block barrier between levels (saves two launches of ~9 us each way at N = 2^20).
+template <bool SMEM_R>
+__global__ void __launch_bounds__(1024) m2m_top_kernel(DevTree T, int Lhi, int Llo, double* __restrict__ mcharge) {
+    extern __shared__ double Rs[];
+    const int r = T.r;
+    if (SMEM_R)
+        for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.R + i);
+    __syncthreads();
+    for (int L = Lhi; L >= Llo; --L) {
+        const int first = T.level_ptr[L], count = T.level_ptr[L + 1] - first;
+        for (int o = threadIdx.x; o < count * r; o += blockDim.x) {
+            const int g = o / r, b = o - g * r;
+            const int c0 = T.child0[first + g];
+            if (c0 < 0) continue;
+            const double* __restrict__ src = mcharge + (size_t)c0 * r;
+            const double* __restrict__ Rc = SMEM_R ? Rs + b : T.R + b;
+            double a0 = 0, a1 = 0;
+#pragma unroll 4
+            for (int ca = 0; ca < 4 * r; ca += 2) {
+                a0 = fma(SMEM_R ? Rc[(size_t)ca * r] : __ldg(Rc + (size_t)ca * r), src[ca], a0);
+                a1 = fma(SMEM_R ? Rc[(size_t)(ca + 1) * r] : __ldg(Rc + (size_t)(ca + 1) * r), src[ca + 1], a1);
+            }
+            mcharge[(size_t)(first + g) * r + b] = a0 + a1;
+        }
+        __syncthreads();
+    }
+}
+
+template <bool SMEM_R, bool FOLD>
+__global__ void __launch_bounds__(1024) l2l_top_kernel(DevTree T, DevCSR m2l, int Llo, int Lhi, double* __restrict__ mpot) {
+    extern __shared__ double Rs[];
+    const int r = T.r;
+    if (SMEM_R)
+        for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.RT + i);
+    __syncthreads();
+    for (int L = Llo; L <= Lhi; ++L) {
+        const int first = T.level_ptr[L], count = T.level_ptr[L + 1] - first;
+        for (int o = threadIdx.x; o < count * r; o += blockDim.x) {
+            const int g = o / r, a = o - g * r;
+            const int id = first + g;
+            double own;
+            if (FOLD) {
+                const int grp = m2l.group_of_node[id];
+                own = grp >= 0 ? fold_rows(m2l, grp, a) : 0.0;
+            } else
+                own = mpot[(size_t)id * r + a];
+            const double* __restrict__ src = mpot + (size_t)T.parent[id] * r;
+            const size_t roff = (size_t)T.index[id] * r * r + a;
+            const double* __restrict__ RT = SMEM_R ? Rs + roff : T.RT + roff;
+            double a0 = 0, a1 = 0;
+            int b = 0;
+#pragma unroll 4
+            for (; b + 2 <= r; b += 2) {
+                a0 = fma(SMEM_R ? RT[(size_t)b * r] : __ldg(RT + (size_t)b * r), src[b], a0);
+                a1 = fma(SMEM_R ? RT[(size_t)(b + 1) * r] : __ldg(RT + (size_t)(b + 1) * r), src[b + 1], a1);
+            }
+            if (b < r) a0 = fma(SMEM_R ? RT[(size_t)b * r] : __ldg(RT + (size_t)b * r), src[b], a0);
+            mpot[(size_t)id * r + a] = own + (a0 + a1);
+        }
+        __syncthreads();
     }
 }
 
@@ -182,7 +267,8 @@ __global__ void __launch_bounds__(256) l2l_kernel(DevTree T, int first, int coun
 //   mode 2: out = x - (fmm + stencil . f) / 2pi                   forwardOperator, main.cpp:129-134
 // f_ref is the unscaled source in REFERENCE node order: the 3x3 cell neighbourhood is plain index arithmetic.
 template <int NP>
-__global__ void __launch_bounds__(128) l2p_kernel(DevTree T, DevGeom G, const int* __restrict__ leaf_of_slot, int slot0, int n,
+__global__ void __launch_bounds__(128) l2p_kernel(DevTree T, DevGeom G, DevCSR p2p, int fold, const int* __restrict__ leaf_of_slot,
+                                                  int slot0, int n,
                                                   const double* __restrict__ mpot, const double* __restrict__ pot,
                                                   const double* __restrict__ C, const double* __restrict__ f_ref,
                                                   const double* __restrict__ x, double* __restrict__ out, int mode) {
@@ -220,7 +306,13 @@ __global__ void __launch_bounds__(128) l2p_kernel(DevTree T, DevGeom G, const in
             if (i < np) row = fma(wx[i], mp[j * np + i], row);
         acc = fma(wy[j], row, acc);
     }
-    double v = pot[p] + acc;
+    double near;  // P2P sum of this target: already reduced in pot, or still spread over the leaf's scratch rows
+    if (fold) {
+        const int grp = p2p.group_of_node[id];
+        near = grp >= 0 ? fold_rows(p2p, grp, p - p2p.row_off[grp]) : 0.0;
+    } else
+        near = pot[p];
+    double v = near + acc;
     if (mode) {
         v = (v + corr) * (M_1_PI / 2.0);
         if (mode == 2) v = x[k] - v;
@@ -261,25 +353,46 @@ void launch_m2m(const DevTree& T, int first, int count, double* mcharge, cudaStr
     else
         m2m_kernel<false><<<(count + G - 1) / G, threads, kids, st>>>(T, first, count, mcharge);
 }
-void launch_l2l(const DevTree& T, int first, int count, double* mpot, cudaStream_t st) {
+void launch_l2l(const DevTree& T, const DevCSR& m2l, bool fold, int first, int count, double* mpot, cudaStream_t st) {
     if (count == 0) return;
     const int threads = pass_threads(T.r), G = std::max(1, threads / T.r);
-    const size_t par = (size_t)G * T.r * sizeof(double);
-    if (smem_R(T.r))
-        l2l_kernel<true><<<(count + G - 1) / G, threads, par + (size_t)4 * T.r * T.r * sizeof(double), st>>>(T, first, count, mpot);
-    else
-        l2l_kernel<false><<<(count + G - 1) / G, threads, par, st>>>(T, first, count, mpot);
+    const size_t par = (size_t)G * T.r * sizeof(double), rb = (size_t)4 * T.r * T.r * sizeof(double);
+    const unsigned blocks = (count + G - 1) / G;
+    if (smem_R(T.r)) {
+        if (fold) l2l_kernel<true, true><<<blocks, threads, par + rb, st>>>(T, m2l, first, count, mpot);
+        else l2l_kernel<true, false><<<blocks, threads, par + rb, st>>>(T, m2l, first, count, mpot);
+    } else {
+        if (fold) l2l_kernel<false, true><<<blocks, threads, par, st>>>(T, m2l, first, count, mpot);
+        else l2l_kernel<false, false><<<blocks, threads, par, st>>>(T, m2l, first, count, mpot);
+    }
 }
-void launch_l2p(const DevTree& T, const DevGeom& G, const int* leaf_of_slot, int slot0, int n, const double* mpot,
+void launch_m2m_top(const DevTree& T, int Lhi, int Llo, double* mcharge, cudaStream_t st) {
+    if (Lhi < Llo) return;
+    if (smem_R(T.r)) m2m_top_kernel<true><<<1, 1024, (size_t)4 * T.r * T.r * sizeof(double), st>>>(T, Lhi, Llo, mcharge);
+    else m2m_top_kernel<false><<<1, 1024, 0, st>>>(T, Lhi, Llo, mcharge);
+}
+void launch_l2l_top(const DevTree& T, const DevCSR& m2l, bool fold, int Llo, int Lhi, double* mpot, cudaStream_t st) {
+    if (Lhi < Llo) return;
+    const size_t rb = (size_t)4 * T.r * T.r * sizeof(double);
+    if (smem_R(T.r)) {
+        if (fold) l2l_top_kernel<true, true><<<1, 1024, rb, st>>>(T, m2l, Llo, Lhi, mpot);
+        else l2l_top_kernel<true, false><<<1, 1024, rb, st>>>(T, m2l, Llo, Lhi, mpot);
+    } else {
+        if (fold) l2l_top_kernel<false, true><<<1, 1024, 0, st>>>(T, m2l, Llo, Lhi, mpot);
+        else l2l_top_kernel<false, false><<<1, 1024, 0, st>>>(T, m2l, Llo, Lhi, mpot);
+    }
+}
+void launch_l2p(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,
+                const double* mpot,
                 const double* pot, const double* C, const double* f_ref, const double* x, double* out, int mode,
                 cudaStream_t st) {
     if (n == 0) return;
     const int blocks = (n + 127) / 128;
     switch (T.np) {
-        case 4: l2p_kernel<4><<<blocks, 128, 0, st>>>(T, G, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode); break;
-        case 6: l2p_kernel<6><<<blocks, 128, 0, st>>>(T, G, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode); break;
-        case 8: l2p_kernel<8><<<blocks, 128, 0, st>>>(T, G, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode); break;
-        default: l2p_kernel<0><<<blocks, 128, 0, st>>>(T, G, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode);
+        case 4: l2p_kernel<4><<<blocks, 128, 0, st>>>(T, G, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode); break;
+        case 6: l2p_kernel<6><<<blocks, 128, 0, st>>>(T, G, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode); break;
+        case 8: l2p_kernel<8><<<blocks, 128, 0, st>>>(T, G, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode); break;
+        default: l2p_kernel<0><<<blocks, 128, 0, st>>>(T, G, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode);
     }
 }
 

@@ -6,6 +6,7 @@
 #include <cstring>
 #include <functional>
 #include <stdexcept>
+#include <unordered_map>
 
 namespace an {
 
@@ -494,6 +495,65 @@ static void finish_csr(BlockCSR& b) {
         for (int k = b.grow_ptr[g]; k < b.grow_ptr[g + 1]; ++k) b.row_group[k] = g;
 }
 
+// Rewrites a uniform-block CSR into symmetric storage (see BlockCSR::symmetric).
+static void symmetrize(BlockCSR& b) {
+    const int groups = (int)b.nrow.size(), R = b.uniform_block;
+    if (!groups || (R != 16 && R != 64) || getenv("ANISO_NO_SYM")) return;
+    auto key = [](int t, int s) { return ((int64_t)t << 32) | (uint32_t)s; };
+    std::unordered_map<int64_t, int> entry_of;  // (tgt, src) -> entry
+    entry_of.reserve(b.col_off.size() * 2);
+    for (size_t e = 0; e < b.col_off.size(); ++e) entry_of[key(b.tgt_node[e], b.src_node[e])] = (int)e;
+    // Of a pair (A,B) the block is kept by A when A+B is even and A < B, or A+B is odd and A > B: every target keeps
+    // about half of its pairs, so the warps of the streaming kernel stay balanced.  An entry is a mirror (dropped)
+    // when its partner exists and the partner owns the pair.
+    auto owns = [](int t, int s) { return ((t + s) & 1) ? t > s : t < s; };
+    std::vector<char> is_mirror(b.col_off.size(), 0);
+    std::vector<int> row_of_entry(b.col_off.size(), -1);
+    b.srow_ptr.assign(groups + 1, 0);
+    for (int g = 0; g < groups; ++g) {
+        int rows = 1;
+        for (int e = b.ent_ptr[g]; e < b.ent_ptr[g + 1]; ++e) {
+            const int t = b.tgt_node[e], s = b.src_node[e];
+            if (t != s && !owns(t, s) && entry_of.count(key(s, t))) {
+                is_mirror[e] = 1;
+                row_of_entry[e] = b.srow_ptr[g] + rows++;
+            }
+        }
+        b.srow_ptr[g + 1] = b.srow_ptr[g] + rows;
+    }
+    b.scratch_rows = b.srow_ptr[groups];
+    BlockCSR n;
+    n.ent_ptr.push_back(0);
+    for (int g = 0; g < groups; ++g) {
+        for (int e = b.ent_ptr[g]; e < b.ent_ptr[g + 1]; ++e) {
+            if (is_mirror[e]) continue;
+            const int t = b.tgt_node[e], s = b.src_node[e];
+            int mrow = -1;
+            if (t != s && owns(t, s)) {
+                auto it = entry_of.find(key(s, t));
+                if (it != entry_of.end()) mrow = row_of_entry[it->second];
+            }
+            n.col_off.push_back(b.col_off[e]);
+            n.ncol.push_back(b.ncol[e]);
+            n.blk_off.push_back(n.nnz);
+            n.tgt_node.push_back(t);
+            n.src_node.push_back(s);
+            n.mirror_row.push_back(mrow);
+            n.nnz += (int64_t)R * R;
+        }
+        n.ent_ptr.push_back((int)n.col_off.size());
+    }
+    b.ent_ptr.swap(n.ent_ptr);
+    b.col_off.swap(n.col_off);
+    b.ncol.swap(n.ncol);
+    b.blk_off.swap(n.blk_off);
+    b.tgt_node.swap(n.tgt_node);
+    b.src_node.swap(n.src_node);
+    b.mirror_row.swap(n.mirror_row);
+    b.nnz = n.nnz;
+    b.symmetric = true;
+}
+
 void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
     const int r = p.rank, nn = (int)p.nodes.size();
     std::vector<char> need(nn, 0);
@@ -520,6 +580,7 @@ void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
             }
         if (!cnt) continue;
         m.row_off.push_back(id * r);
+        m.group_node.push_back(id);
         m.nrow.push_back(r);
         m.ent_ptr.push_back((int)m.col_off.size());
     }
@@ -537,11 +598,14 @@ void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
                 q.nnz += (int64_t)n.npts * p.nodes[s].npts;
             }
         q.row_off.push_back(n.pt_off);
+        q.group_node.push_back(id);
         q.nrow.push_back(n.npts);
         q.ent_ptr.push_back((int)q.col_off.size());
     }
     finish_csr(m);
     finish_csr(q);
+    symmetrize(m);
+    symmetrize(q);
     p.m2l = std::move(m);
     p.p2p = std::move(q);
 }

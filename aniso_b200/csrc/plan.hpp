@@ -34,6 +34,7 @@ struct TreeNode {
 //                         A[blk_off[e] + s*nrow[g] + t] * x[col_off[e] + s]
 struct BlockCSR {
     std::vector<int> row_off, nrow;       // per row group (target node / target leaf)
+    std::vector<int> group_node;          // tree node of each group
     std::vector<int> ent_ptr;             // size groups+1
     std::vector<int> col_off, ncol;       // per entry
     std::vector<int64_t> blk_off;         // per entry, in doubles
@@ -42,6 +43,14 @@ struct BlockCSR {
     std::vector<int> row_group;           // per launch row -> group
     int uniform_nrow = 0;                 // >0 when every group has this many rows (M2L: r)
     int uniform_block = 0;                // >0 when every block is uniform_block x uniform_block
+    // symmetric storage (uniform blocks only): K(tgt A <- src B) = (-1)^id K(tgt B <- src A)^T, so only one block of
+    // each pair is stored (the one with A < B); while streaming it the kernel also forms the transposed product and
+    // drops it into the partner's scratch row `mirror_row`.  Scratch rows of group g: [srow_ptr[g], srow_ptr[g+1]),
+    // the first one holding the group's own partial result.
+    bool symmetric = false;
+    std::vector<int> mirror_row;          // per entry: scratch row of the partner group, or -1
+    std::vector<int> srow_ptr;            // groups+1
+    int scratch_rows = 0;
     int64_t nnz = 0;                      // total doubles of operator storage
     int nrows_total = 0;                  // launch rows
 };

@@ -109,6 +109,130 @@ __global__ void __launch_bounds__(256) bsr_apply_warp_kernel(DevCSR m, const dou
     }
 }
 
+// One block's worth of work for the symmetric kernel, iterations [it0, it0+4) already loaded into a[].
+// Forward part: acc += K x_B.  Transposed part (paired blocks): the four partial products of this chunk are reduced
+// over the LG lanes that share a source index with a butterfly that halves the live values at every step (2 + 1
+// shuffles over lane bits 0 and 1, then one shuffle per remaining lane bit), instead of 4 x log2(LG) full reductions.
+template <int R>
+__device__ __forceinline__ void sym_consume(const double2 (&a)[4], int it0, const double* __restrict__ xs_base, double xa0,
+                                            double xa1, int mr, int lane, int s_lane, double sign, double& acc0, double& acc1,
+                                            double* __restrict__ scratch) {
+    constexpr int S_STEP = 64 / R, LG = R / 2 < 32 ? R / 2 : 32;
+    static_assert(LG >= 4, "butterfly needs at least four lanes per source index");
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const double xs = __ldg(xs_base + (it0 + u) * S_STEP);
+        acc0 = fma(a[u].x, xs, acc0);
+        acc1 = fma(a[u].y, xs, acc1);
+    }
+    if (mr < 0) return;  // warp-uniform
+    const double p0 = fma(a[0].x, xa0, a[0].y * xa1), p1 = fma(a[1].x, xa0, a[1].y * xa1);
+    const double p2 = fma(a[2].x, xa0, a[2].y * xa1), p3 = fma(a[3].x, xa0, a[3].y * xa1);
+    const bool b0 = lane & 1, b1 = lane & 2;
+    // lane bit 0: keep iterations {2,3} if set, else {0,1}
+    double k0 = b0 ? p2 : p0, k1 = b0 ? p3 : p1;
+    k0 += __shfl_xor_sync(0xffffffffu, b0 ? p0 : p2, 1);
+    k1 += __shfl_xor_sync(0xffffffffu, b0 ? p1 : p3, 1);
+    // lane bit 1: keep the second of the pair if set
+    double z = b1 ? k1 : k0;
+    z += __shfl_xor_sync(0xffffffffu, b1 ? k0 : k1, 2);
+#pragma unroll
+    for (int off = 4; off < LG; off <<= 1) z += __shfl_xor_sync(0xffffffffu, z, off);
+    // lanes with (lane % LG) < 4 hold the finished z[s] for iteration it0 + u, u = 2*b0 + b1
+    if ((lane % LG) < 4) {
+        const int u = (b0 ? 2 : 0) + (b1 ? 1 : 0);
+        scratch[(size_t)mr * R + (it0 + u) * S_STEP + s_lane] = sign * z;
+    }
+}
+
+// Symmetric storage: only one block of each (A,B)/(B,A) pair is in memory.  While a warp streams the blocks of its
+// target A it also forms, for every paired block, z = sign * K^T x_A (the contribution of that block to the partner B)
+// and writes the R values into B's scratch row; its own partial sum goes into A's first scratch row.  A second, tiny
+// kernel adds up the rows of each target in a fixed order, so the result is deterministic (no atomics).  HBM traffic
+// per matvec: half the blocks + 2 x 8R bytes of scratch per dropped block.
+template <int R>
+__global__ void __launch_bounds__(256, 4) bsr_apply_sym_kernel(DevCSR m, const double* __restrict__ A,
+                                                            const double* __restrict__ x, double sign) {
+    constexpr int PAIRS = R * R / 2, ITERS = PAIRS / 32;
+    static_assert(64 % R == 0 && PAIRS % 32 == 0, "lane -> target pair must be loop invariant");
+    constexpr int CH = 4;  // per block; two blocks per trip => 8 16-byte loads in flight per lane
+    static_assert(ITERS % CH == 0, "chunking");
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (g >= m.groups) return;
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const uint64_t pol = stream_policy();
+    const double2* __restrict__ base = reinterpret_cast<const double2*>(A + (ne ? m.blk_off[e0] : 0));
+    const int s_lane = (2 * lane) / R, t0 = (2 * lane) % R;
+    const int self = m.row_off[g];
+    const double xa0 = __ldg(x + self + t0), xa1 = __ldg(x + self + t0 + 1);
+    double* __restrict__ scratch = m.scratch;
+    double acc0 = 0, acc1 = 0, acc2 = 0, acc3 = 0;
+    for (int eb = 0; eb < ne; eb += 32) {
+        const int cnt = min(32, ne - eb);
+        const int mycol = lane < cnt ? m.col_off[e0 + eb + lane] : 0;
+        const int mymir = lane < cnt ? m.mirror_row[e0 + eb + lane] : -1;
+        int j = 0;
+        for (; j + 2 <= cnt; j += 2) {
+            const int c0 = __shfl_sync(0xffffffffu, mycol, j) + s_lane, c1 = __shfl_sync(0xffffffffu, mycol, j + 1) + s_lane;
+            const int m0 = __shfl_sync(0xffffffffu, mymir, j), m1 = __shfl_sync(0xffffffffu, mymir, j + 1);
+            const double2* __restrict__ b0 = base + (size_t)(eb + j) * PAIRS + lane;
+            const double2* __restrict__ b1 = b0 + PAIRS;
+#pragma unroll 1
+            for (int it0 = 0; it0 < ITERS; it0 += CH) {
+                double2 a0[CH], a1[CH];
+#pragma unroll
+                for (int u = 0; u < CH; ++u) {
+                    a0[u] = ld_stream2(b0 + (it0 + u) * 32, pol);
+                    a1[u] = ld_stream2(b1 + (it0 + u) * 32, pol);
+                }
+                sym_consume<R>(a0, it0, x + c0, xa0, xa1, m0, lane, s_lane, sign, acc0, acc1, scratch);
+                sym_consume<R>(a1, it0, x + c1, xa0, xa1, m1, lane, s_lane, sign, acc2, acc3, scratch);
+            }
+        }
+        if (j < cnt) {
+            const int c0 = __shfl_sync(0xffffffffu, mycol, j) + s_lane;
+            const int m0 = __shfl_sync(0xffffffffu, mymir, j);
+            const double2* __restrict__ b0 = base + (size_t)(eb + j) * PAIRS + lane;
+#pragma unroll 1
+            for (int it0 = 0; it0 < ITERS; it0 += CH) {
+                double2 a0[CH];
+#pragma unroll
+                for (int u = 0; u < CH; ++u) a0[u] = ld_stream2(b0 + (it0 + u) * 32, pol);
+                sym_consume<R>(a0, it0, x + c0, xa0, xa1, m0, lane, s_lane, sign, acc0, acc1, scratch);
+            }
+        }
+    }
+    acc0 += acc2;
+    acc1 += acc3;
+#pragma unroll
+    for (int off = 16; off >= R / 2; off >>= 1) {
+        acc0 += __shfl_down_sync(0xffffffffu, acc0, off);
+        acc1 += __shfl_down_sync(0xffffffffu, acc1, off);
+    }
+    if (lane < R / 2) {
+        double* __restrict__ out = scratch + (size_t)m.srow_ptr[g] * R + 2 * lane;
+        out[0] = acc0;
+        out[1] = acc1;
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(256) bsr_reduce_kernel(DevCSR m, double* __restrict__ y) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int g = i / R, t = i - g * R;
+    if (g >= m.groups) return;
+    const int r0 = m.srow_ptr[g], r1 = m.srow_ptr[g + 1];
+    double s0 = 0, s1 = 0;
+    int r = r0;
+    for (; r + 2 <= r1; r += 2) {
+        s0 += m.scratch[(size_t)r * R + t];
+        s1 += m.scratch[(size_t)(r + 1) * R + t];
+    }
+    if (r < r1) s0 += m.scratch[(size_t)r * R + t];
+    y[m.row_off[g] + t] = s0 + s1;
+}
+
 __global__ void __launch_bounds__(128) bsr_apply_row_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
                                                             double* __restrict__ y) {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
@@ -151,9 +275,22 @@ __global__ void __launch_bounds__(128) bsr_apply_row_kernel(DevCSR m, const doub
     y[m.row_off[g] + t] = (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
 
-void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, cudaStream_t st) {
+void launch_bsr_reduce(const DevCSR& m, double* y, cudaStream_t st) {
+    if (!m.symmetric || m.groups == 0) return;
+    const unsigned rb = ((unsigned)m.groups * m.uniform_block + 255) / 256;
+    if (m.uniform_block == 16) bsr_reduce_kernel<16><<<rb, 256, 0, st>>>(m, y);
+    else bsr_reduce_kernel<64><<<rb, 256, 0, st>>>(m, y);
+}
+
+void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, double sign, bool reduce, cudaStream_t st) {
     if (m.nrows_total == 0) return;
     const unsigned warps_per_cta = 8, ctas = (m.groups + warps_per_cta - 1) / warps_per_cta;
+    if (m.symmetric) {
+        if (m.uniform_block == 16) bsr_apply_sym_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else bsr_apply_sym_kernel<64><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        if (reduce) launch_bsr_reduce(m, y, st);
+        return;
+    }
     static const bool force_row = getenv("ANISO_BSR_ROW") != nullptr;  // A/B switch for profiling only
     if (force_row)
         bsr_apply_row_kernel<<<(m.nrows_total + 127) / 128, 128, 0, st>>>(m, A, x, y);

@@ -47,37 +47,44 @@ def host_cores():
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks + throttle reasons DURING the measured regions (B200_PROFILING.md): one `nvidia-smi -lms 50`
+    child for the whole measurement section (device-timed steps, e2e steps, roofline launches), rows read by a thread."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.stop = index, [], False
-        self.t = threading.Thread(target=self.run, daemon=True)
+        self.index, self.rows, self.proc, self.t = index, [], None, None
 
-    def run(self):
-        while not self.stop:
-            try:
-                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in o.strip().split(",")])
-            except Exception:
-                pass
-            time.sleep(0.05)
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.strip().split(",")])
 
     def __enter__(self):
-        self.t.start()
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
         return self
 
     def __exit__(self, *a):
-        self.stop = True
-        self.t.join(timeout=6)
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+            self.t.join(timeout=5)
 
     def summary(self):
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        ok = [r for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        sm = [float(r[0]) for r in ok]
+        mx = [float(r[1]) for r in ok if r[1].replace(".", "").isdigit()]
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
+        reasons = sorted({n for r in ok for n, v in zip(names, r[2:6]) if v.lower() == "active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
 
@@ -138,12 +145,13 @@ def run_reference(args):
 
 
 def cpu_baseline(args):
-    """Bounded CPU sample (about 10-30 s) timed beside the GPU run: rank 0, N=1 only."""
+    """Bounded CPU sample (10-30 s of CPU work) timed beside the GPU run: rank 0, N=1 only.  The compiled reference
+    (its own -Ofast flags, OpenMP on all host cores) when oracle/_ref is present, else the scalar C port."""
     from oracle import refapi
 
     cores = host_cores()
     if refapi.available(fast=True):
-        sz, kind = 128, "reference"
+        sz, kind = (256 if cores >= 12 else 128), "reference"
         r = refapi.RefAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL, fast=True)
     else:
         from oracle import oracleapi
@@ -154,21 +162,24 @@ def cpu_baseline(args):
     ss, st = cases.sigma_fields("layers", x, y, sz, 1)
     t0 = time.perf_counter()
     r.set_coeff(ss, st)
-    r.cache(0)
+    times = r.cache(0)
     t_cache = time.perf_counter() - t0
-    pairs = r.tree_stats(0)["p2p_pairs"] if hasattr(r, "tree_stats") else None
+    ts = r.tree_stats(0)
+    evals = ts["p2p_pairs"] + (ts["sumV"] + ts["sumX"]) * NP_ORDER ** 4
     f = cases.gaussian_source(x, y)
     r.mapping(f, 0)
-    reps = 3
+    reps = 5
     t0 = time.perf_counter()
     for _ in range(reps):
         r.mapping(ss * f, 0)
     dt = (time.perf_counter() - t0) / reps
     n = sz * sz
-    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": "N=%d (sz %d) sub-problem, %d matvecs after a %.1f s cache phase" % (n, sz, reps, t_cache),
-            "ms_per_matvec": dt * 1e3, "cache_phase_s": t_cache,
-            "cache_evals_per_s": None if not pairs else None}
+    out = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": kind,
+           "sample": "N=%d (sz %d) sub-problem of the same workload, %d matvecs after a %.1f s cache phase" % (n, sz, reps, t_cache),
+           "ms_per_matvec": dt * 1e3, "cache_phase_s": t_cache}
+    if times is not None and len(times) and times[0] > 0:
+        out["kernel_evals_per_s"] = evals / float(times[0])  # 'Non Singular Cache': P2P + M2L evaluations with line integrals
+    return out
 
 
 def run_ours(args):
@@ -244,15 +255,24 @@ def run_ours(args):
     barrier()
     l0 = a.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
-        e0.record(stream)
-        for _ in range(args.steps):
-            step()
-        e1.record(stream)
-        e1.synchronize()
-        barrier()
+    clk = ClockSampler(local)
+    clk.__enter__()
+    time.sleep(0.12)  # let the sampler produce its first rows
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    e1.synchronize()
+    barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     launches = a.launch_count() - l0
+    tot = torch.tensor([float(counts["p2p"]), float(counts["m2l"]), ct["p2p_fill_ms"], ct["m2l_fill_ms"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = tot.clone()
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        tot[2:] = mx[2:]
+    all_p2p, all_m2l, p2p_fill_ms, m2l_fill_ms = (float(v) for v in tot.tolist())
     ms_step = ms_total / args.steps
     value = n / (ms_step * 1e-3)
 
@@ -271,16 +291,20 @@ def run_ours(args):
     # ---- roofline of the dominant kernel: the M2L streaming apply (bsr_apply_kernel over the V/X blocks) ----
     ab = a.apply_bytes()
     tr = a.tree_stats()
-    m2l_ms = max_over_ranks(a.time_kernel(0, 0, 20))
-    p2p_ms = max_over_ranks(a.time_kernel(0, 1, 20))
+    m2l_ms = max_over_ranks(a.time_kernel(0, 0, 50))
+    p2p_ms = max_over_ranks(a.time_kernel(0, 1, 50))
+    for _ in range(200):  # keep the device under load long enough for the clock sampler to see it
+        step()
+    a.synchronize()
+    clk.__exit__()
     r = NP_ORDER * NP_ORDER
-    m2l_alg = ab["m2l"] + 8 * 2 * r * tr["nodes"]  # operator blocks + multipoles read + locals written
+    m2l_alg = ab["m2l"] + 8 * r * tr["nodes"]  # stored blocks + scratch rows written + multipoles read
     peak, peak_src = measured_peak()
-    roof = {"bound": "hbm", "kernel": "bsr_apply_kernel (M2L, V/X blocks)", "achieved": m2l_alg / (m2l_ms * 1e-3) / 1e9,
+    roof = {"bound": "hbm", "kernel": "bsr_apply_sym_kernel<16> (M2L stream over the V/X blocks, symmetric storage)", "achieved": m2l_alg / (m2l_ms * 1e-3) / 1e9,
             "peak": peak, "unit": "GB/s", "frac": m2l_alg / (m2l_ms * 1e-3) / 1e9 / peak, "traffic": None,
             "peak_source": peak_src, "algorithmic_bytes_per_launch": m2l_alg, "ms_per_launch": m2l_ms,
-            "p2p_apply": {"algorithmic_bytes": ab["p2p"] + 16 * n, "ms_per_launch": p2p_ms,
-                          "achieved": (ab["p2p"] + 16 * n) / (p2p_ms * 1e-3) / 1e9}}
+            "p2p_stream": {"algorithmic_bytes": ab["p2p"] + 8 * n, "ms_per_launch": p2p_ms,
+                           "achieved": (ab["p2p"] + 8 * n) / (p2p_ms * 1e-3) / 1e9}}
 
     # ---- GMRES time-to-solve (main.cpp:141: GMRES(80, 400, 1e-12), x0 = 0) ----
     b_own = torch.empty(nown, dtype=torch.float64, device="cuda")
@@ -310,9 +334,10 @@ def run_ours(args):
                 "e2e": {"value": n / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * nown,
                         "ms_per_step": e2e_s * 1e3},
                 "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof,
-                "near_field_interactions_per_s": counts["p2p"] / (ct["p2p_fill_ms"] * 1e-3) if ct["p2p_fill_ms"] else None,
-                "cache": {"wall_s": t_cache, "p2p_pairs": counts["p2p"], "m2l_pairs": counts["m2l"], **ct,
-                          "m2l_evals_per_s": counts["m2l"] / (ct["m2l_fill_ms"] * 1e-3) if ct["m2l_fill_ms"] else None},
+                "near_field_interactions_per_s": all_p2p / (p2p_fill_ms * 1e-3) if p2p_fill_ms else None,
+                "cache": {"wall_s": t_cache, "p2p_pairs": int(all_p2p), "m2l_pairs": int(all_m2l), "p2p_fill_ms": p2p_fill_ms,
+                          "m2l_fill_ms": m2l_fill_ms, "stencil_ms": ct["stencil_ms"],
+                          "m2l_evals_per_s": all_m2l / (m2l_fill_ms * 1e-3) if m2l_fill_ms else None},
                 "gmres": {"rc": int(rc), "iters": int(it.value), "final_resid": float(hist[it.value]), "time_to_solve_s": t_gmres,
                           "m": 80, "tol": 1e-12, "gpu_launches": int(gm_launches)},
                 "setup_s": t_setup}

@@ -154,9 +154,10 @@ int aniso_from_slots(aniso_t* h, const double* slot_order_dev, double* ref_order
                                                                                             when sharded: others untouched) */
 /* kernels launched by this handle since creation (bench.py's gpu_launches) */
 int64_t aniso_launch_count(const aniso_t* h);
-/* algorithmic operator bytes one mapping streams: out[0] = P2P, out[1] = M2L, out[2] = stencil */
+/* bytes the cached-apply kernels must move per mapping: out[0] = P2P, out[1] = M2L (stored blocks, i.e. one of each
+ * symmetric pair when the blocks are uniform, plus the per-target scratch rows they write), out[2] = stencil */
 int aniso_apply_bytes(const aniso_t* h, int64_t out[3]);
-/* time the streaming apply kernels alone: `reps` back-to-back launches of (0) M2L apply, (1) P2P apply on the cache of `id`,
+/* time the streaming apply kernels alone: `reps` back-to-back launches of (0) M2L stream, (1) P2P stream on the cache of `id`,
  * CUDA events on the handle's stream; returns average milliseconds per launch */
 int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms_per_launch);
 
