@@ -47,13 +47,16 @@ def _worker(rank, port, name, out_q):
         assert int(allr[0][0]) == 0 and int(allr[-1][1]) == n
         for r in range(WORLD - 1):
             assert int(allr[r][1]) == int(allr[r + 1][0])
-        # operator bytes: P2P rows are split exactly; M2L rows of shared ancestors are replicated
+        # operator bytes: every rank stores the blocks its own targets need.  Under symmetric storage a pair whose two
+        # leaves sit on different ranks is kept by both (neither can write into the other's scratch rows), so the
+        # sum lies between the single-device (half-stored) total and the unsymmetrised one; M2L rows of shared
+        # ancestors are replicated on top of that
         mine = a.apply_bytes()
         tot = torch.tensor([mine["p2p"], mine["m2l"]], dtype=torch.long)
         dist.all_reduce(tot)
         full = single.apply_bytes()
-        assert int(tot[0]) == full["p2p"]
-        assert full["m2l"] <= int(tot[1]) <= 1.02 * full["m2l"] + 64 * 8 * (np_ ** 4) * 30
+        assert full["p2p"] <= int(tot[0]) <= 2 * full["p2p"]
+        assert full["m2l"] <= int(tot[1]) <= 2.04 * full["m2l"] + 64 * 8 * (np_ ** 4) * 30
         # replay of the per-matvec exchange: rows owned by this rank -> all-gather (unequal counts) -> full vector
         perm = a.slot_permutation()
         assert np.array_equal(perm, single.slot_permutation())
