@@ -47,7 +47,15 @@ struct aniso_handle {
     std::vector<int> all_slot_begin, all_slot_end;  // ownership of every rank
     bool dev_ready = false, coeff_set = false;
     cudaStream_t st = nullptr;
+    // second stream of the matvec: the two big operator streams (P2P, deepest-level M2L) run here while the
+    // latency-bound tree passes run on `st`; forked and joined with events inside every run_fmm
+    cudaStream_t st_bulk = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr;
+    bool overlap = true;
     int m2l_top_groups = 0;  // M2L groups of the first level that has V lists (a prefix: level-major numbering)
+    int m2l_deep_g0 = 0;     // M2L groups [m2l_deep_g0, groups) belong to the deepest level and read only leaf multipoles
+    bool subtree_ok = false;  // complete uniform tree: the sub-tree passes of subtree.cu replace the level-by-level ones
+    SubtreePlan sub;
     std::vector<void*> allocs;
     DevTree T;
     DevGeom G;
@@ -124,6 +132,9 @@ DevCSR upload_csr(aniso_handle* h, const BlockCSR& b) {
         d.mirror_row = upload(h, b.mirror_row);
         d.srow_ptr = upload(h, b.srow_ptr);
         d.scratch = dalloc<double>(h, (size_t)b.scratch_rows * b.uniform_block);
+        std::vector<int2> rows(h->plan.nodes.size(), make_int2(0, 0));
+        for (size_t g = 0; g < b.group_node.size(); ++g) rows[b.group_node[g]] = make_int2(b.srow_ptr[g], b.srow_ptr[g + 1]);
+        d.node_rows = upload(h, rows);
     }
     return d;
 }
@@ -139,6 +150,9 @@ void ensure_device(aniso_handle* h) {
     if (h->device < 0) CK(cudaGetDevice(&h->device));
     CK(cudaSetDevice(h->device));
     CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->st_bulk, cudaStreamNonBlocking));
+    for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
     const HostPlan& p = h->plan;
     const int N = p.N, nn = (int)p.nodes.size(), r = p.rank;
     // geometry in slot order
@@ -217,6 +231,26 @@ void ensure_device(aniso_handle* h) {
     h->m2l_top_groups = 0;
     for (int g : p.m2l.group_node)
         if (p.nodes[g].level == h->first_m2l_level) ++h->m2l_top_groups;
+    {
+        // suffix of groups at the deepest level whose sources are all leaves (their multipoles come straight from P2M)
+        const int deepest = T.nlevels - 1, ng = (int)p.m2l.group_node.size();
+        int g0 = ng;
+        while (g0 > 0 && p.nodes[p.m2l.group_node[g0 - 1]].level == deepest) --g0;
+        bool leaf_sources = true;
+        for (int e = g0 < ng ? p.m2l.ent_ptr[g0] : (int)p.m2l.src_node.size(); e < (int)p.m2l.src_node.size(); ++e)
+            leaf_sources = leaf_sources && p.nodes[p.m2l.src_node[e]].leaf;
+        h->m2l_deep_g0 = (leaf_sources && h->first_m2l_level < deepest) ? g0 : ng;
+    }
+    {
+        // complete uniform quadtree?  (every node non-empty, all leaves on the deepest level, 4^L nodes on level L)
+        const int deepest = T.nlevels - 1;
+        bool ok = getenv("ANISO_NO_SUBTREE") == nullptr && !p.m2l.group_node.empty() && r <= 64 && (int)p.leaves.size() == (1 << (2 * deepest));
+        for (int L = 0; ok && L <= deepest; ++L) ok = p.level_ptr[L + 1] - p.level_ptr[L] == (1 << (2 * L));
+        for (int i = 0; ok && i < nn; ++i) ok = !p.nodes[i].empty && p.nodes[i].leaf == (p.nodes[i].level == deepest);
+        for (size_t k = 0; ok && k < p.leaves.size(); ++k) ok = p.leaves[k] == p.level_ptr[deepest] + (int)k;
+        h->subtree_ok = ok;
+        if (ok) h->sub = make_subtree_plan(h->first_m2l_level, deepest, r);
+    }
     // sigma grid
     h->d_chat = dalloc<double>(h, N);
     h->d_sig_s = dalloc<double>(h, N);
@@ -352,6 +386,10 @@ int aniso_destroy(aniso_t* h) {
         if (h->comm && h->nccl) h->nccl->CommDestroy(h->comm);
         for (void* p : h->allocs) cudaFree(p);
         if (h->pinned) cudaFreeHost(h->pinned);
+        cudaStreamSynchronize(h->st_bulk);
+        for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join})
+            if (e) cudaEventDestroy(e);
+        cudaStreamDestroy(h->st_bulk);
         cudaStreamDestroy(h->st);
     }
     delete h;
@@ -549,17 +587,60 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     // levels [L0, Lt] hold at most 256 nodes each (a single CTA is slower than a launch beyond that): one single-CTA launch walks them (top of the tree)
     int Lt = L0 - 1;
     while (Lt + 1 <= deepest && count(Lt + 1) <= 256) ++Lt;
+    // Two streams.  `st` carries the latency-bound chain (P2M, M2M, shallow M2L, L2L), `st_bulk` the two big operator
+    // streams that depend on little: P2P needs only q, the deepest-level M2L only the leaf multipoles from P2M.
+    const int ng = h->m2l.groups, gd = h->overlap ? h->m2l_deep_g0 : ng;
+    cudaStream_t sb = h->overlap ? h->st_bulk : h->st;
+    if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
+    if (h->overlap) {
+        CK(cudaEventRecord(h->ev_fork, h->st));
+        CK(cudaStreamWaitEvent(sb, h->ev_fork, 0));
+    }
+    LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, sb));
+    if (h->subtree_ok) {
+        // complete uniform tree: each pass is ceil(levels/3) launches (subtree.cu)
+        h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, h->overlap ? h->ev_leaf : nullptr);
+        if (h->overlap) {
+            CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
+            if (gd < ng) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd, ng - gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, sb));
+            CK(cudaEventRecord(h->ev_join, sb));
+        }
+        if (gd > 0) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, 0, gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
+        h->launches += launch_down_mid_tree(T, h->m2l, sym_m, h->sub, L0, h->d_mpot, h->st);
+        if (h->overlap) CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
+        h->launches += launch_down_leaf_tree(T, h->G, h->m2l, sym_m, h->p2p, sym_p, h->sub, L0, h->d_leaf_of_slot, h->slot0, h->nown,
+                                             h->d_mpot, h->d_pot, stencil, f, x_own, out, mode, h->st);
+        CK(cudaGetLastError());
+        return;
+    }
     LAUNCH(h, launch_p2m(T, h->G, q, h->d_mcharge, h->st));
+    if (h->overlap) {
+        CK(cudaEventRecord(h->ev_leaf, h->st));
+        CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
+        if (gd < ng) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd, ng - gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, sb));
+        CK(cudaEventRecord(h->ev_join, sb));
+    }
     for (int L = deepest - 1; L >= L0 && L > Lt; --L) LAUNCH(h, launch_m2m(T, p.level_ptr[L], count(L), h->d_mcharge, h->st));
     if (std::min(Lt, deepest - 1) >= L0) LAUNCH(h, launch_m2m_top(T, std::min(Lt, deepest - 1), L0, h->d_mcharge, h->st));
-    if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
-    LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
+    if (gd > 0) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, 0, gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
     if (sym_m && h->m2l_top_groups > 0)  // level L0 has no L2L step: finish its sums here, every other level folds them in L2L
         LAUNCH(h, launch_bsr_reduce(sub_range(h->m2l, 0, h->m2l_top_groups), h->d_mpot, h->st));
-    if (Lt >= L0 + 1) LAUNCH(h, launch_l2l_top(T, h->m2l, sym_m, L0 + 1, Lt, h->d_mpot, h->st));
-    for (int L = std::max(L0 + 1, Lt + 1); L <= deepest; ++L)
+    bool joined = !h->overlap;
+    auto join = [&](int L) {  // the deepest level's M2L sums (and the P2P sums) come from the bulk stream
+        if (!joined && L >= deepest) {
+            CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
+            joined = true;
+        }
+    };
+    if (Lt >= L0 + 1) {
+        join(Lt);
+        LAUNCH(h, launch_l2l_top(T, h->m2l, sym_m, L0 + 1, Lt, h->d_mpot, h->st));
+    }
+    for (int L = std::max(L0 + 1, Lt + 1); L <= deepest; ++L) {
+        join(L);
         LAUNCH(h, launch_l2l(T, h->m2l, sym_m, p.level_ptr[L], count(L), h->d_mpot, h->st));
-    LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, h->st));
+    }
+    join(deepest);
     LAUNCH(h, launch_l2p(T, h->G, h->p2p, sym_p, h->d_leaf_of_slot, h->slot0, h->nown, h->d_mpot, h->d_pot, stencil, f, x_own, out,
                          mode, h->st));
 }

@@ -28,6 +28,7 @@ struct DevCSR {
     int symmetric = 0, scratch_rows = 0;                       // symmetric storage, see plan.hpp
     int *mirror_row = nullptr, *srow_ptr = nullptr;
     int* group_of_node = nullptr;                              // tree node -> group (or -1)
+    int2* node_rows = nullptr;                                 // tree node -> [first, last) scratch row (empty without a group)
     double* scratch = nullptr;                                 // [scratch_rows][uniform_block]
 };
 
@@ -76,6 +77,20 @@ void launch_l2l(const DevTree& T, const DevCSR& m2l, bool fold, int first, int c
 // levels [Llo, Lhi] (at most 1024 nodes each) in one single-CTA launch
 void launch_m2m_top(const DevTree& T, int Lhi, int Llo, double* mcharge, cudaStream_t st);
 void launch_l2l_top(const DevTree& T, const DevCSR& m2l, bool fold, int Llo, int Lhi, double* mpot, cudaStream_t st);
+// ---- sub-tree passes for complete uniform trees (subtree.cu) ----
+struct SubtreePlan {
+    int leaf_Ls = 0, leaf_D = 0;          // sub-trees holding the leaves: roots at level leaf_Ls, leaf_D levels below
+    int nmid = 0, mid_Ls[8], mid_D[8];    // the chunks above, bottom-up
+};
+SubtreePlan make_subtree_plan(int first_m2l_level, int deepest, int r);
+// P2M + M2M of every level down to first_m2l_level; leaf_done (optional) is recorded once the leaf multipoles exist.
+// Return value: kernels launched.
+int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
+                   cudaEvent_t leaf_done);
+int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st);
+int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
+                          const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
+                          const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st);
 // L2P + tail of the matvec for slots [slot0, slot0+n):  fmm = pot[p] + L2P(p)
 //   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi   (C: fused stencil, f_ref: full unscaled source in reference order)
 void launch_l2p(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,

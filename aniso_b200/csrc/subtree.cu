@@ -1,0 +1,383 @@
+// Tree passes of the matvec for COMPLETE UNIFORM quadtrees (every BASELINE configuration; SURVEY 8: "all BASELINE
+// trees are complete uniform quadtrees"), restructured around sub-trees instead of levels.
+//
+// The level-by-level passes of passes.cu (upPass bbfmm.h:825-861; L2L/L2P of downPassFast bbfmm.h:1066-1113) make a
+// chain of 2 x (depth - 2) dependent launches, each bounded by launch + DRAM latency, not by bytes: at N = 2^20 they
+// take 0.31 ms of a 0.82 ms matvec.  Here one CTA owns a sub-tree of up to three levels and walks it in shared memory
+// with block barriers, so a pass over the whole tree is ceil(levels / 3) launches and the intermediate levels never
+// leave the SM:
+//   up_leaf_kernel    points -> multipoles of the leaf level (P2M) and of the up-to-3 levels above it (M2M)
+//   up_mid_kernel     multipoles of level Ls+D (global) -> levels Ls+D-1 .. Ls
+//   down_mid_kernel   locals of level Ls (global, or the folded M2L sum when Ls is the first M2L level) -> level Ls+D
+//   down_leaf_kernel  the same down to the leaf level, then L2P + near-field fold + correction stencil + 1/2pi
+//                     (the fused tail of `mapping`, AnisoWrapper.cpp:129-130 / main.cpp:129-134)
+// Node numbering (plan.cpp): level-major, Morton order inside a level, so the descendants of node m of level L at
+// level L+d are the 4^d consecutive nodes starting at level_ptr[L+d] + 4^d m, leaf k of the DFS order is node
+// level_ptr[deepest] + k, and a sub-tree's points are one contiguous slot range.
+#include <algorithm>
+
+#include "device.cuh"
+#include "passes_inl.cuh"
+
+namespace an {
+
+__host__ __device__ __forceinline__ int lvoff(int d) { return ((1 << (2 * d)) - 1) / 3; }  // boxes above level d of a sub-tree
+
+// M2M inside shared memory: levels D-1 .. 0 of the sub-tree rooted at node (Ls, m); sm holds level d at lvoff(d)*r.
+template <bool SMEM_R>
+__device__ __forceinline__ void subtree_m2m(const DevTree& T, int Ls, int m, int D, double* __restrict__ sm,
+                                            const double* __restrict__ Rs, double* __restrict__ mcharge) {
+    const int r = T.r;
+    for (int d = D - 1; d >= 0; --d) {
+        const int nb = 1 << (2 * d);
+        const double* __restrict__ kids = sm + (size_t)lvoff(d + 1) * r;
+        double* __restrict__ mine = sm + (size_t)lvoff(d) * r;
+        const size_t gbase = ((size_t)T.level_ptr[Ls + d] + ((size_t)m << (2 * d))) * r;
+        for (int o = threadIdx.x; o < nb * r; o += blockDim.x) {
+            const int g = o / r, b = o - g * r;
+            const double* __restrict__ src = kids + (size_t)g * 4 * r;
+            const double* __restrict__ Rc = (SMEM_R ? Rs : T.R) + b;
+            double a0 = 0, a1 = 0;
+#pragma unroll 4
+            for (int ca = 0; ca < 4 * r; ca += 2) {
+                a0 = fma(SMEM_R ? Rc[(size_t)ca * r] : __ldg(Rc + (size_t)ca * r), src[ca], a0);
+                a1 = fma(SMEM_R ? Rc[(size_t)(ca + 1) * r] : __ldg(Rc + (size_t)(ca + 1) * r), src[ca + 1], a1);
+            }
+            const double v = a0 + a1;
+            mine[o] = v;
+            mcharge[gbase + o] = v;
+        }
+        __syncthreads();
+    }
+}
+
+// P2M of the 4^D leaves of one sub-tree (same scheme as p2m_kernel: LANES lanes per leaf, weights of a point computed
+// once and parked in shared memory), then M2M up to the sub-tree root.
+template <int NP, int LANES, bool SMEM_R>
+__global__ void __launch_bounds__(256) up_leaf_kernel(DevTree T, DevGeom G, const double* __restrict__ q, double* __restrict__ mcharge,
+                                                      int Ls, int D) {
+    extern __shared__ double sm[];
+    __shared__ double tn[NP_MAX * NP_MAX];
+    constexpr int UMAX = NP ? (NP * NP + LANES - 1) / LANES : (NP_MAX * NP_MAX + LANES - 1) / LANES;
+    const int np = NP ? NP : T.np, r = np * np;
+    const int m = blockIdx.x, nl = 1 << (2 * D);
+    const int grp = threadIdx.x / LANES, lane = threadIdx.x % LANES, ngrp = blockDim.x / LANES;
+    const int stride = 2 * np + 1;
+    double* __restrict__ mult = sm;                                   // [lvoff(D+1)][r]
+    double* __restrict__ ws = sm + (size_t)lvoff(D + 1) * r + (size_t)grp * LANES * stride;
+    double* __restrict__ Rs = sm + (size_t)lvoff(D + 1) * r + (size_t)ngrp * LANES * stride;
+    for (int i = threadIdx.x; i < np * np; i += blockDim.x) tn[i] = T.tnode[i];
+    if (SMEM_R)
+        for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.R + i);
+    __syncthreads();
+    const unsigned mask = LANES == 32 ? 0xffffffffu : 0xffffu << (16 * ((threadIdx.x >> 4) & 1));
+    for (int j0 = 0; j0 < nl; j0 += ngrp) {
+        const int j = j0 + grp;  // nl and ngrp are powers of two: a group is either fully inside or fully outside
+        if (j >= nl) break;
+        const int4 info = T.leaf_info[(size_t)m * nl + j];  // id, pt_off, npts
+        const int id = info.x, off = info.y, n = info.z;
+        double acc[UMAX];
+#pragma unroll
+        for (int u = 0; u < UMAX; ++u) acc[u] = 0;
+        for (int k0 = 0; k0 < n; k0 += LANES) {
+            const int cnt = min(LANES, n - k0);
+            if (lane < cnt) {
+                double w[2 * (NP ? NP : NP_MAX)];
+                cheb_weights<NP>(tn, np, G.sxn[off + k0 + lane], w);
+                cheb_weights<NP>(tn, np, G.syn[off + k0 + lane], w + np);
+#pragma unroll
+                for (int mm = 0; mm < 2 * (NP ? NP : NP_MAX); ++mm)
+                    if (mm < 2 * np) ws[lane * stride + mm] = w[mm];
+                ws[lane * stride + 2 * np] = q[off + k0 + lane];
+            }
+            __syncwarp(mask);
+#pragma unroll
+            for (int u = 0; u < UMAX; ++u) {
+                const int mm = lane + LANES * u;
+                if (mm < r) {
+                    const int i = mm % np, jj = mm / np;
+                    double a = acc[u];
+                    for (int k = 0; k < cnt; ++k) a += ws[k * stride + i] * ws[k * stride + np + jj] * ws[k * stride + 2 * np];
+                    acc[u] = a;
+                }
+            }
+            __syncwarp(mask);
+        }
+#pragma unroll
+        for (int u = 0; u < UMAX; ++u) {
+            const int mm = lane + LANES * u;
+            if (mm < r) {
+                mult[(size_t)(lvoff(D) + j) * r + mm] = acc[u];
+                mcharge[(size_t)id * r + mm] = acc[u];
+            }
+        }
+    }
+    __syncthreads();
+    subtree_m2m<SMEM_R>(T, Ls, m, D, mult, Rs, mcharge);
+}
+
+template <bool SMEM_R>
+__global__ void __launch_bounds__(256) up_mid_kernel(DevTree T, double* __restrict__ mcharge, int Ls, int D) {
+    extern __shared__ double sm[];
+    const int r = T.r, m = blockIdx.x, nb = 1 << (2 * D);
+    double* __restrict__ Rs = sm + (size_t)lvoff(D + 1) * r;
+    if (SMEM_R)
+        for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.R + i);
+    const double* __restrict__ src = mcharge + ((size_t)T.level_ptr[Ls + D] + (size_t)m * nb) * r;
+    double* __restrict__ dst = sm + (size_t)lvoff(D) * r;
+    for (int i = threadIdx.x; i < nb * r; i += blockDim.x) dst[i] = src[i];
+    __syncthreads();
+    subtree_m2m<SMEM_R>(T, Ls, m, D, sm, Rs, mcharge);
+}
+
+// Scratch rows of a tree node (symmetric storage) summed in their fixed order; node_rows[node] = [first, last) row.
+__device__ __forceinline__ double fold_node(const DevCSR& m, int node, int t) {
+    const int2 rr = m.node_rows[node];
+    const int R = m.uniform_block;
+    double s0 = 0, s1 = 0;
+    int r = rr.x;
+    for (; r + 2 <= rr.y; r += 2) {
+        s0 += m.scratch[(size_t)r * R + t];
+        s1 += m.scratch[(size_t)(r + 1) * R + t];
+    }
+    if (r < rr.y) s0 += m.scratch[(size_t)r * R + t];
+    return s0 + s1;
+}
+
+// L2L inside shared memory: levels 0 .. D of the sub-tree rooted at node (Ls, m).  top: the root has no parent
+// contribution (first level with M2L lists), its local expansion is its own M2L sum.  FOLD: M2L sums are still spread
+// over scratch rows (symmetric storage), otherwise they sit in mpot.
+template <bool SMEM_R, bool FOLD>
+__device__ __forceinline__ void subtree_l2l(const DevTree& T, const DevCSR& m2l, int Ls, int m, int D, bool top, bool write_last,
+                                            double* __restrict__ sm, const double* __restrict__ RTs, double* __restrict__ mpot) {
+    const int r = T.r;
+    {
+        const int root = T.level_ptr[Ls] + m;
+        for (int a = threadIdx.x; a < r; a += blockDim.x)
+            sm[a] = (FOLD && top) ? fold_node(m2l, root, a) : mpot[(size_t)root * r + a];
+    }
+    __syncthreads();
+    for (int d = 1; d <= D; ++d) {
+        const int nb = 1 << (2 * d);
+        const double* __restrict__ pars = sm + (size_t)lvoff(d - 1) * r;
+        double* __restrict__ mine = sm + (size_t)lvoff(d) * r;
+        const int first = T.level_ptr[Ls + d] + (m << (2 * d));
+        for (int o = threadIdx.x; o < nb * r; o += blockDim.x) {
+            const int g = o / r, a = o - g * r;
+            const int id = first + g;
+            const double own = FOLD ? fold_node(m2l, id, a) : mpot[(size_t)id * r + a];
+            const size_t roff = (size_t)(g & 3) * r * r + a;  // children are consecutive: sibling position = child index
+            const double* __restrict__ RT = (SMEM_R ? RTs : T.RT) + roff;
+            const double* __restrict__ src = pars + (size_t)(g >> 2) * r;
+            double a0 = 0, a1 = 0;
+            int b = 0;
+#pragma unroll 4
+            for (; b + 2 <= r; b += 2) {
+                a0 = fma(SMEM_R ? RT[(size_t)b * r] : __ldg(RT + (size_t)b * r), src[b], a0);
+                a1 = fma(SMEM_R ? RT[(size_t)(b + 1) * r] : __ldg(RT + (size_t)(b + 1) * r), src[b + 1], a1);
+            }
+            if (b < r) a0 = fma(SMEM_R ? RT[(size_t)b * r] : __ldg(RT + (size_t)b * r), src[b], a0);
+            const double v = own + (a0 + a1);
+            mine[o] = v;
+            if (write_last && d == D) mpot[(size_t)id * r + a] = v;
+        }
+        __syncthreads();
+    }
+}
+
+template <bool SMEM_R, bool FOLD>
+__global__ void __launch_bounds__(256) down_mid_kernel(DevTree T, DevCSR m2l, double* __restrict__ mpot, int Ls, int D, int top) {
+    extern __shared__ double sm[];
+    const int r = T.r;
+    double* __restrict__ RTs = sm + (size_t)lvoff(D + 1) * r;
+    if (SMEM_R)
+        for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) RTs[i] = __ldg(T.RT + i);
+    subtree_l2l<SMEM_R, FOLD>(T, m2l, Ls, blockIdx.x, D, top != 0, true, sm, RTs, mpot);  // starts with a barrier
+}
+
+// L2L down to the leaves of one sub-tree, then per point of the sub-tree (one contiguous slot range)
+//   fmm = near(p) + sum_{i,j} Sx(p,i) Sy(p,j) local[leaf][j*np+i]                 L2P, bbfmm.h:1104-1113
+//   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi
+// near(p): P2P sum, already reduced in pot or still spread over the leaf's scratch rows (fold_p2p).
+template <int NP, bool SMEM_R, bool FOLD>
+__global__ void __launch_bounds__(256) down_leaf_kernel(DevTree T, DevGeom G, DevCSR m2l, DevCSR p2p, int fold_p2p,
+                                                        const int* __restrict__ leaf_of_slot, int slot0, int n,
+                                                        double* __restrict__ mpot, const double* __restrict__ pot,
+                                                        const double* __restrict__ C, const double* __restrict__ f_ref,
+                                                        const double* __restrict__ x, double* __restrict__ out, int mode, int Ls,
+                                                        int D, int top) {
+    extern __shared__ double sm[];
+    __shared__ double tn[NP_MAX * NP_MAX];
+    const int np = NP ? NP : T.np, r = np * np, m = blockIdx.x;
+    const int root = T.level_ptr[Ls] + m;
+    const int p_begin = max(T.pt_off[root], slot0), p_end = min(T.pt_off[root] + T.npts[root], slot0 + n);
+    if (p_begin >= p_end) return;  // no owned target below this root (multi-GPU partition)
+    double* __restrict__ RTs = sm + (size_t)lvoff(D + 1) * r;
+    for (int i = threadIdx.x; i < np * np; i += blockDim.x) tn[i] = T.tnode[i];
+    if (SMEM_R)
+        for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) RTs[i] = __ldg(T.RT + i);
+    subtree_l2l<SMEM_R, FOLD>(T, m2l, Ls, m, D, top != 0, false, sm, RTs, mpot);
+    const double* __restrict__ locals = sm + (size_t)lvoff(D) * r;
+    const int leaf0 = T.level_ptr[Ls + D] + (m << (2 * D));
+    for (int p = p_begin + threadIdx.x; p < p_end; p += blockDim.x) {
+        const int k = p - slot0;
+        double corr = 0;
+        if (mode) {
+            const int c2 = G.c2, sz = G.sz;
+            const int tc = G.perm[p] / c2;
+            const int ti = tc / sz, tj = tc - ti * sz;
+            for (int cs = 0; cs < 9; ++cs) {
+                const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
+                if (si < 0 || si >= sz || sj < 0 || sj >= sz) continue;
+                const double* __restrict__ fs = f_ref + (size_t)(si * sz + sj) * c2;
+                for (int qq = 0; qq < c2; ++qq) corr = fma(C[(size_t)(cs * c2 + qq) * n + k], fs[qq], corr);
+            }
+        }
+        const int id = leaf_of_slot[p], lo = id - leaf0;
+        const double* __restrict__ mp = locals + (size_t)lo * r;
+        double wx[NP ? NP : NP_MAX], wy[NP ? NP : NP_MAX];
+        cheb_weights<NP>(tn, np, G.sxn[p], wx);
+        cheb_weights<NP>(tn, np, G.syn[p], wy);
+        double acc = 0;
+#pragma unroll
+        for (int j = 0; j < (NP ? NP : NP_MAX); ++j) {
+            if (j >= np) break;
+            double row = 0;
+#pragma unroll
+            for (int i = 0; i < (NP ? NP : NP_MAX); ++i)
+                if (i < np) row = fma(wx[i], mp[j * np + i], row);
+            acc = fma(wy[j], row, acc);
+        }
+        const double near = fold_p2p ? fold_node(p2p, id, p - T.pt_off[id]) : pot[p];
+        double v = near + acc;
+        if (mode) {
+            v = (v + corr) * (M_1_PI / 2.0);
+            if (mode == 2) v = x[k] - v;
+        }
+        out[k] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+static bool smem_R(int r) { return (size_t)4 * r * r * sizeof(double) <= 36 * 1024; }  // r <= 33 (np <= 5)
+
+template <class K>
+static void want_smem(K kernel, size_t bytes) {
+    if (bytes > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+SubtreePlan make_subtree_plan(int L0, int deepest, int r) {
+    SubtreePlan s;
+    const int dmax = r <= 36 ? 3 : 2;
+    s.leaf_D = std::min(dmax, deepest - L0);
+    s.leaf_Ls = deepest - s.leaf_D;
+    s.nmid = 0;
+    for (int cur = s.leaf_Ls; cur > L0 && s.nmid < 8;) {  // bottom-up order
+        const int D = std::min(dmax, cur - L0);
+        s.mid_Ls[s.nmid] = cur - D;
+        s.mid_D[s.nmid] = D;
+        ++s.nmid;
+        cur -= D;
+    }
+    return s;
+}
+
+template <int NP>
+static void up_leaf_launch(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st) {
+    const int r = T.r, D = sp.leaf_D, ctas = 1 << (2 * sp.leaf_Ls);
+    const bool sr = smem_R(r);
+    const size_t bytes = ((size_t)lvoff(D + 1) * r + (size_t)256 * (2 * T.np + 1) + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
+    const bool l16 = T.r <= 16 && T.max_leaf <= 16;
+#define UP_LEAF(LANES, SR)                                                             \
+    do {                                                                               \
+        want_smem(up_leaf_kernel<NP, LANES, SR>, bytes);                               \
+        up_leaf_kernel<NP, LANES, SR><<<ctas, 256, bytes, st>>>(T, G, q, mcharge, sp.leaf_Ls, D); \
+    } while (0)
+    if (l16 && sr) UP_LEAF(16, true);
+    else if (l16) UP_LEAF(16, false);
+    else if (sr) UP_LEAF(32, true);
+    else UP_LEAF(32, false);
+#undef UP_LEAF
+}
+
+int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
+                   cudaEvent_t leaf_done) {
+    switch (T.np) {
+        case 4: up_leaf_launch<4>(T, G, sp, q, mcharge, st); break;
+        case 6: up_leaf_launch<6>(T, G, sp, q, mcharge, st); break;
+        case 8: up_leaf_launch<8>(T, G, sp, q, mcharge, st); break;
+        default: up_leaf_launch<0>(T, G, sp, q, mcharge, st);
+    }
+    if (leaf_done) cudaEventRecord(leaf_done, st);
+    const int r = T.r;
+    const bool sr = smem_R(r);
+    for (int c = 0; c < sp.nmid; ++c) {
+        const int D = sp.mid_D[c], ctas = 1 << (2 * sp.mid_Ls[c]);
+        const size_t bytes = ((size_t)lvoff(D + 1) * r + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
+        if (sr) {
+            want_smem(up_mid_kernel<true>, bytes);
+            up_mid_kernel<true><<<ctas, 256, bytes, st>>>(T, mcharge, sp.mid_Ls[c], D);
+        } else {
+            want_smem(up_mid_kernel<false>, bytes);
+            up_mid_kernel<false><<<ctas, 256, bytes, st>>>(T, mcharge, sp.mid_Ls[c], D);
+        }
+    }
+    return 1 + sp.nmid;
+}
+
+int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st) {
+    const int r = T.r;
+    const bool sr = smem_R(r);
+    for (int c = sp.nmid - 1; c >= 0; --c) {  // top-down
+        const int D = sp.mid_D[c], Ls = sp.mid_Ls[c], ctas = 1 << (2 * Ls), top = Ls == L0;
+        const size_t bytes = ((size_t)lvoff(D + 1) * r + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
+#define DOWN_MID(SR, FO)                                                          \
+    do {                                                                          \
+        want_smem(down_mid_kernel<SR, FO>, bytes);                                \
+        down_mid_kernel<SR, FO><<<ctas, 256, bytes, st>>>(T, m2l, mpot, Ls, D, top); \
+    } while (0)
+        if (sr && fold) DOWN_MID(true, true);
+        else if (sr) DOWN_MID(true, false);
+        else if (fold) DOWN_MID(false, true);
+        else DOWN_MID(false, false);
+#undef DOWN_MID
+    }
+    return sp.nmid;
+}
+
+template <int NP>
+static void down_leaf_launch(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
+                             const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
+                             const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st) {
+    const int r = T.r, D = sp.leaf_D, Ls = sp.leaf_Ls, ctas = 1 << (2 * Ls), top = Ls == L0;
+    const bool sr = smem_R(r);
+    const size_t bytes = ((size_t)lvoff(D + 1) * r + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
+#define DOWN_LEAF(SR, FO)                                                                                                       \
+    do {                                                                                                                        \
+        want_smem(down_leaf_kernel<NP, SR, FO>, bytes);                                                                         \
+        down_leaf_kernel<NP, SR, FO><<<ctas, 256, bytes, st>>>(T, G, m2l, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, C, \
+                                                               f_ref, x, out, mode, Ls, D, top);                                \
+    } while (0)
+    if (sr && fold) DOWN_LEAF(true, true);
+    else if (sr) DOWN_LEAF(true, false);
+    else if (fold) DOWN_LEAF(false, true);
+    else DOWN_LEAF(false, false);
+#undef DOWN_LEAF
+}
+
+int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
+                          const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
+                          const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st) {
+    if (n == 0) return 0;
+    switch (T.np) {
+        case 4: down_leaf_launch<4>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st); break;
+        case 6: down_leaf_launch<6>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st); break;
+        case 8: down_leaf_launch<8>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st); break;
+        default: down_leaf_launch<0>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st);
+    }
+    return 1;
+}
+
+}  // namespace an
