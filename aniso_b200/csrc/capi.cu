@@ -149,8 +149,14 @@ void ensure_device(aniso_handle* h) {
     }
     if (h->device < 0) CK(cudaGetDevice(&h->device));
     CK(cudaSetDevice(h->device));
-    CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&h->st_bulk, cudaStreamNonBlocking));
+    {
+        // `st` carries the latency-bound kernels and gets the higher priority: its few CTAs are dispatched as soon as an
+        // SM slot frees up, instead of queueing behind the thousands of CTAs of a bulk operator stream on `st_bulk`
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&h->st, cudaStreamNonBlocking, hi));
+        CK(cudaStreamCreateWithPriority(&h->st_bulk, cudaStreamNonBlocking, lo));
+    }
     for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
     const HostPlan& p = h->plan;

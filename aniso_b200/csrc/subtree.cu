@@ -11,10 +11,12 @@
 //   down_mid_kernel   locals of level Ls (global, or the folded M2L sum when Ls is the first M2L level) -> level Ls+D
 //   down_leaf_kernel  the same down to the leaf level, then L2P + near-field fold + correction stencil + 1/2pi
 //                     (the fused tail of `mapping`, AnisoWrapper.cpp:129-130 / main.cpp:129-134)
-// Node numbering (plan.cpp): level-major, Morton order inside a level, so the descendants of node m of level L at
-// level L+d are the 4^d consecutive nodes starting at level_ptr[L+d] + 4^d m, leaf k of the DFS order is node
-// level_ptr[deepest] + k, and a sub-tree's points are one contiguous slot range.
+// Node numbering (plan.cpp): level-major, Morton order inside a level, and level L of a complete tree starts at node
+// (4^L - 1)/3 = lvoff(L); so the descendants of node m of level L at level L+d are the 4^d consecutive nodes starting
+// at lvoff(L+d) + 4^d m, leaf k of the DFS order is node lvoff(deepest) + k, and a sub-tree's points are one
+// contiguous slot range.
 #include <algorithm>
+#include <cstdlib>
 
 #include "device.cuh"
 #include "passes_inl.cuh"
@@ -32,7 +34,7 @@ __device__ __forceinline__ void subtree_m2m(const DevTree& T, int Ls, int m, int
         const int nb = 1 << (2 * d);
         const double* __restrict__ kids = sm + (size_t)lvoff(d + 1) * r;
         double* __restrict__ mine = sm + (size_t)lvoff(d) * r;
-        const size_t gbase = ((size_t)T.level_ptr[Ls + d] + ((size_t)m << (2 * d))) * r;
+        const size_t gbase = ((size_t)lvoff(Ls + d) + ((size_t)m << (2 * d))) * r;
         for (int o = threadIdx.x; o < nb * r; o += blockDim.x) {
             const int g = o / r, b = o - g * r;
             const double* __restrict__ src = kids + (size_t)g * 4 * r;
@@ -123,7 +125,7 @@ __global__ void __launch_bounds__(256) up_mid_kernel(DevTree T, double* __restri
     double* __restrict__ Rs = sm + (size_t)lvoff(D + 1) * r;
     if (SMEM_R)
         for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.R + i);
-    const double* __restrict__ src = mcharge + ((size_t)T.level_ptr[Ls + D] + (size_t)m * nb) * r;
+    const double* __restrict__ src = mcharge + ((size_t)lvoff(Ls + D) + (size_t)m * nb) * r;
     double* __restrict__ dst = sm + (size_t)lvoff(D) * r;
     for (int i = threadIdx.x; i < nb * r; i += blockDim.x) dst[i] = src[i];
     __syncthreads();
@@ -134,14 +136,15 @@ __global__ void __launch_bounds__(256) up_mid_kernel(DevTree T, double* __restri
 __device__ __forceinline__ double fold_node(const DevCSR& m, int node, int t) {
     const int2 rr = m.node_rows[node];
     const int R = m.uniform_block;
-    double s0 = 0, s1 = 0;
-    int r = rr.x;
-    for (; r + 2 <= rr.y; r += 2) {
-        s0 += m.scratch[(size_t)r * R + t];
-        s1 += m.scratch[(size_t)(r + 1) * R + t];
+    const double* __restrict__ base = m.scratch + t;
+    double s = 0;
+    for (int r = rr.x; r < rr.y; r += 8) {  // eight independent loads in flight per round
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = r + u < rr.y ? base[(size_t)(r + u) * R] : 0.0;
+        s += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
     }
-    if (r < rr.y) s0 += m.scratch[(size_t)r * R + t];
-    return s0 + s1;
+    return s;
 }
 
 // L2L inside shared memory: levels 0 .. D of the sub-tree rooted at node (Ls, m).  top: the root has no parent
@@ -152,7 +155,7 @@ __device__ __forceinline__ void subtree_l2l(const DevTree& T, const DevCSR& m2l,
                                             double* __restrict__ sm, const double* __restrict__ RTs, double* __restrict__ mpot) {
     const int r = T.r;
     {
-        const int root = T.level_ptr[Ls] + m;
+        const int root = lvoff(Ls) + m;
         for (int a = threadIdx.x; a < r; a += blockDim.x)
             sm[a] = (FOLD && top) ? fold_node(m2l, root, a) : mpot[(size_t)root * r + a];
     }
@@ -161,7 +164,7 @@ __device__ __forceinline__ void subtree_l2l(const DevTree& T, const DevCSR& m2l,
         const int nb = 1 << (2 * d);
         const double* __restrict__ pars = sm + (size_t)lvoff(d - 1) * r;
         double* __restrict__ mine = sm + (size_t)lvoff(d) * r;
-        const int first = T.level_ptr[Ls + d] + (m << (2 * d));
+        const int first = lvoff(Ls + d) + (m << (2 * d));
         for (int o = threadIdx.x; o < nb * r; o += blockDim.x) {
             const int g = o / r, a = o - g * r;
             const int id = first + g;
@@ -209,19 +212,23 @@ __global__ void __launch_bounds__(256) down_leaf_kernel(DevTree T, DevGeom G, De
     extern __shared__ double sm[];
     __shared__ double tn[NP_MAX * NP_MAX];
     const int np = NP ? NP : T.np, r = np * np, m = blockIdx.x;
-    const int root = T.level_ptr[Ls] + m;
+    const int root = lvoff(Ls) + m;
     const int p_begin = max(T.pt_off[root], slot0), p_end = min(T.pt_off[root] + T.npts[root], slot0 + n);
     if (p_begin >= p_end) return;  // no owned target below this root (multi-GPU partition)
     double* __restrict__ RTs = sm + (size_t)lvoff(D + 1) * r;
     for (int i = threadIdx.x; i < np * np; i += blockDim.x) tn[i] = T.tnode[i];
     if (SMEM_R)
         for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) RTs[i] = __ldg(T.RT + i);
-    subtree_l2l<SMEM_R, FOLD>(T, m2l, Ls, m, D, top != 0, false, sm, RTs, mpot);
-    const double* __restrict__ locals = sm + (size_t)lvoff(D) * r;
-    const int leaf0 = T.level_ptr[Ls + D] + (m << (2 * D));
-    for (int p = p_begin + threadIdx.x; p < p_end; p += blockDim.x) {
+    const int leaf0 = lvoff(Ls + D) + (m << (2 * D));
+    // Everything of a point that does not depend on the local expansions (correction stencil, near-field fold,
+    // interpolation weights) is loaded before the L2L levels, so those latencies overlap the L2L chain.
+    struct Pre {
+        double corr, near, wx[NP ? NP : NP_MAX], wy[NP ? NP : NP_MAX];
+        int lo;
+    };
+    auto pre = [&](int p, Pre& P) {
         const int k = p - slot0;
-        double corr = 0;
+        P.corr = 0;
         if (mode) {
             const int c2 = G.c2, sz = G.sz;
             const int tc = G.perm[p] / c2;
@@ -230,14 +237,19 @@ __global__ void __launch_bounds__(256) down_leaf_kernel(DevTree T, DevGeom G, De
                 const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
                 if (si < 0 || si >= sz || sj < 0 || sj >= sz) continue;
                 const double* __restrict__ fs = f_ref + (size_t)(si * sz + sj) * c2;
-                for (int qq = 0; qq < c2; ++qq) corr = fma(C[(size_t)(cs * c2 + qq) * n + k], fs[qq], corr);
+                for (int qq = 0; qq < c2; ++qq) P.corr = fma(C[(size_t)(cs * c2 + qq) * n + k], fs[qq], P.corr);
             }
         }
-        const int id = leaf_of_slot[p], lo = id - leaf0;
-        const double* __restrict__ mp = locals + (size_t)lo * r;
-        double wx[NP ? NP : NP_MAX], wy[NP ? NP : NP_MAX];
-        cheb_weights<NP>(tn, np, G.sxn[p], wx);
-        cheb_weights<NP>(tn, np, G.syn[p], wy);
+        const int id = leaf_of_slot[p];
+        P.lo = id - leaf0;
+        P.near = fold_p2p ? fold_node(p2p, id, p - T.pt_off[id]) : pot[p];
+        cheb_weights<NP>(tn, np, G.sxn[p], P.wx);
+        cheb_weights<NP>(tn, np, G.syn[p], P.wy);
+    };
+    const double* __restrict__ locals = sm + (size_t)lvoff(D) * r;
+    auto post = [&](int p, const Pre& P) {
+        const int k = p - slot0;
+        const double* __restrict__ mp = locals + (size_t)P.lo * r;
         double acc = 0;
 #pragma unroll
         for (int j = 0; j < (NP ? NP : NP_MAX); ++j) {
@@ -245,16 +257,26 @@ __global__ void __launch_bounds__(256) down_leaf_kernel(DevTree T, DevGeom G, De
             double row = 0;
 #pragma unroll
             for (int i = 0; i < (NP ? NP : NP_MAX); ++i)
-                if (i < np) row = fma(wx[i], mp[j * np + i], row);
-            acc = fma(wy[j], row, acc);
+                if (i < np) row = fma(P.wx[i], mp[j * np + i], row);
+            acc = fma(P.wy[j], row, acc);
         }
-        const double near = fold_p2p ? fold_node(p2p, id, p - T.pt_off[id]) : pot[p];
-        double v = near + acc;
+        double v = P.near + acc;
         if (mode) {
-            v = (v + corr) * (M_1_PI / 2.0);
+            v = (v + P.corr) * (M_1_PI / 2.0);
             if (mode == 2) v = x[k] - v;
         }
         out[k] = v;
+    };
+    __syncthreads();  // tn
+    const int p_first = p_begin + threadIdx.x;
+    Pre P0;
+    if (p_first < p_end) pre(p_first, P0);
+    subtree_l2l<SMEM_R, FOLD>(T, m2l, Ls, m, D, top != 0, false, sm, RTs, mpot);
+    if (p_first < p_end) post(p_first, P0);
+    for (int p = p_first + blockDim.x; p < p_end; p += blockDim.x) {
+        Pre P;
+        pre(p, P);
+        post(p, P);
     }
 }
 
@@ -270,7 +292,10 @@ static void want_smem(K kernel, size_t bytes) {
 
 SubtreePlan make_subtree_plan(int L0, int deepest, int r) {
     SubtreePlan s;
-    const int dmax = r <= 36 ? 3 : 2;
+    // levels per sub-tree: 2 keeps every launch wide (4^(deepest-2) CTAs at the leaves; the scratch-row folds of the
+    // levels above are spread over 16x more CTAs than with 3) at the price of one more launch each way
+    static const int denv = getenv("ANISO_SUBTREE_D") ? atoi(getenv("ANISO_SUBTREE_D")) : 2;
+    const int dmax = std::max(1, std::min(denv, r <= 36 ? 3 : 2));
     s.leaf_D = std::min(dmax, deepest - L0);
     s.leaf_Ls = deepest - s.leaf_D;
     s.nmid = 0;
