@@ -263,6 +263,10 @@ void ensure_device(aniso_handle* h) {
     SigmaGrid& S = h->S;
     S.sz = p.sz; S.deg = p.deg; S.c2 = p.c2; S.h = p.dx;  // cell edge k sits at k*dx (KernelFactory.cpp:71-72: k / (1/dx))
     S.chat = h->d_chat; S.glx = upload(h, p.glx); S.glw = upload(h, p.glw);
+    if (p.deg == 1 && !getenv("ANISO_CELL_WALK")) {  // line-integral tables of the deg-1 fast path, filled by setCoeff
+        S.ty = dalloc<double2>(h, N);
+        S.tx = dalloc<double2>(h, N);
+    }
     // work space
     h->d_f = dalloc<double>(h, N); h->d_q = dalloc<double>(h, N); h->d_pot = dalloc<double>(h, N);
     h->d_fmm = dalloc<double>(h, N); h->d_corr = dalloc<double>(h, N); h->d_a = dalloc<double>(h, N);
@@ -735,6 +739,7 @@ int aniso_set_coeff(aniso_t* h, const double* sigma_s, const double* sigma_t) {
     // interpolation() KernelFactory.cpp:212-227 on the device; chat = coeff / legendreNorms feeds the ray march
     stage_h2d(h, sigma_t);
     LAUNCH(h, launch_interpolate(h->G, h->d_stage, h->d_lnorm, h->d_chat, h->st));
+    if (h->S.ty) LAUNCH(h, launch_sigma_prefix(h->S, const_cast<double2*>(h->S.ty), const_cast<double2*>(h->S.tx), h->st));
     CK(cudaStreamSynchronize(h->st));
     h->coeff_t.clear();
     h->coeff_s.clear();

@@ -16,6 +16,11 @@ struct SigmaGrid {
     const double* chat;    // [ncell][c2]
     const double* glx;     // [deg] table order
     const double* glw;     // [deg]
+    // deg == 1 only (sigma piecewise constant): running integrals of sigma along each grid line, paired with sigma,
+    //   ty[cx*sz + j] = { h * sum_{j' < j} sigma[cx][j'], sigma[cx][j] }     (along y inside column cx)
+    //   tx[cy*sz + i] = { h * sum_{i' < i} sigma[i'][cy], sigma[i][cy] }     (along x inside row cy)
+    const double2* ty = nullptr;
+    const double2* tx = nullptr;
 };
 
 // block-CSR operator (see plan.hpp BlockCSR); all pointers are device memory
@@ -114,6 +119,8 @@ void launch_gather(int n, const double* src, const int* idx, double* dst, cudaSt
 void launch_add3(long n, const double* a, const double* b, const double* c, double* out, cudaStream_t st);
 // sigma interpolation on device: chat[c][r] = (sum_j interp[r][j] sqrtw[j] h[c*c2+j]) / (lnorm ? lnorm[r] : 1), h in REFERENCE order
 void launch_interpolate(const DevGeom& G, const double* h_ref, const double* lnorm_or_null, double* coeff, cudaStream_t st);
+// (re)builds S.ty / S.tx from S.chat (deg == 1)
+void launch_sigma_prefix(const SigmaGrid& S, double2* ty, double2* tx, cudaStream_t st);
 // probes for parity tests
 void launch_probe_line_integral(const SigmaGrid& S, int n, const double* pts4, double* out, cudaStream_t st);
 void launch_probe_kernel(const SigmaGrid& S, int id, int part, int n, const double* pts4, double* out, cudaStream_t st);

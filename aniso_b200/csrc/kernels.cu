@@ -107,6 +107,70 @@ __device__ double line_integral(const SigmaGrid& S, double x0, double y0, double
     return acc * len;
 }
 
+// deg == 1 fast path.  sigma is constant per cell, so along a grid line its integral is piecewise linear:
+//   F_c(v) = int_0^v sigma(c, v') dv' = P[c][j] + sigma[c][j] (v - j h),  j = floor(v / h)   (table S.ty or S.tx).
+// Take v = the coordinate with the larger extent and u = the other one.  The ray crosses |cell(u1) - cell(u0)| grid
+// lines u = b h; between two crossings it stays inside one line of cells c, where it contributes
+// (len/dv) (F_c(v_out) - F_c(v_in)).  Summed over the runs,
+//   tau = (len/dv) [ F_c1(v1) - F_c0(v0) + sum_crossings (F_c(v_b) - F_c'(v_b)) ],   c -> c' the line change at v_b,
+// one independent term per crossed line of the MINOR axis (on average 3.4x fewer terms than cells crossed, none at
+// all for axis-aligned rays), each two 16-byte table reads and a handful of FMAs.  Exact for the piecewise-constant
+// interpolant like the cell walk (the reference's bisection + one-point Gauss rule, KernelFactory.cpp:67-190).
+__device__ __forceinline__ double magic_floor(double v, double szd, double top, int& j) {
+    // t = round(v*sz - 0.5) = floor(v*sz) away from integers; at an integer either neighbour is fine (F is continuous)
+    const double MAGIC = 6755399441055744.0;  // 2^52 + 2^51: the integer sits in the low mantissa bits
+    double t = fma(v, szd, -0.5) + MAGIC;     // (MAGIC - 0.5 is not representable: the shift needs its own rounding)
+    t = fmin(fmax(t, MAGIC), top);            // getRow/getCol clamp
+    j = __double2loint(t);
+    return t - MAGIC;
+}
+
+__device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0, double y0, double x1, double y1, double len) {
+    const double ddx = x1 - x0, ddy = y1 - y0;
+    const bool steep = fabs(ddy) >= fabs(ddx);
+    const double u0 = steep ? x0 : y0, v0 = steep ? y0 : x0, u1 = steep ? x1 : y1, v1 = steep ? y1 : x1;
+    const double du = u1 - u0, dv = v1 - v0;
+    const double2* __restrict__ tab = steep ? S.ty : S.tx;
+    const int sz = S.sz;
+    const double szd = (double)sz, h = S.h, top = 6755399441055744.0 + (double)(sz - 1);
+    int c0, c1, j0, j1;
+    magic_floor(u0, szd, top, c0);
+    magic_floor(u1, szd, top, c1);
+    const double jd0 = magic_floor(v0, szd, top, j0), jd1 = magic_floor(v1, szd, top, j1);
+    const double2 e0 = __ldg(tab + (size_t)c0 * sz + j0), e1 = __ldg(tab + (size_t)c1 * sz + j1);
+    double acc = (e1.x - e0.x) + (fma(e1.y, fma(-jd1, h, v1), -e0.y * fma(-jd0, h, v0)));
+    if (c0 != c1) {
+        const double slope = dv / du;
+        const int sgn = c1 > c0 ? 1 : -1, ncross = abs(c1 - c0);
+        double bd = (double)(c1 > c0 ? c0 + 1 : c0);
+        const double sd = (double)sgn;
+        const double2* __restrict__ row = tab + (size_t)c0 * sz;
+        const ptrdiff_t rstep = (ptrdiff_t)sgn * sz;
+        double acc2 = 0;
+        int k = 0;
+        for (; k + 2 <= ncross; k += 2) {  // two crossings per trip: four independent table reads in flight
+            const double vb0 = fma(fma(bd, h, -u0), slope, v0), vb1 = fma(fma(bd + sd, h, -u0), slope, v0);
+            int ja, jb;
+            const double jda = magic_floor(vb0, szd, top, ja), jdb = magic_floor(vb1, szd, top, jb);
+            const double2 a0 = __ldg(row + ja), a1 = __ldg(row + rstep + ja);
+            const double2 b0 = __ldg(row + rstep + jb), b1 = __ldg(row + 2 * rstep + jb);
+            acc = acc + ((a0.x - a1.x) + (a0.y - a1.y) * fma(-jda, h, vb0));
+            acc2 = acc2 + ((b0.x - b1.x) + (b0.y - b1.y) * fma(-jdb, h, vb1));
+            bd += 2.0 * sd;
+            row += 2 * rstep;
+        }
+        if (k < ncross) {
+            const double vb0 = fma(fma(bd, h, -u0), slope, v0);
+            int ja;
+            const double jda = magic_floor(vb0, szd, top, ja);
+            const double2 a0 = __ldg(row + ja), a1 = __ldg(row + rstep + ja);
+            acc = acc + ((a0.x - a1.x) + (a0.y - a1.y) * fma(-jda, h, vb0));
+        }
+        acc += acc2;
+    }
+    return acc * (len / dv);
+}
+
 // Kernel family of makeKernels (KernelFactory.cpp:240-267): a = source, b = target (Q8).
 //   REAL: cos(k theta)/d        IMAG: (exp(-tau)-1) cos(k theta)/d, diagonal +sigma_t(a) for k = 0 (Q2)
 //   BOTH: their sum exp(-tau) cos(k theta)/d (the physical kernel; what the fused matvec caches)
@@ -126,11 +190,11 @@ __device__ double kernel_eval(const SigmaGrid& S, int id, int part, double ax, d
     if (dist == 0.0) return ((part & PART_IMAG) && id == 0) ? sigma_eval(S, ax, ay) : 0.0;
     const double inv = 1.0 / dist;
     const double ck = id == 0 ? 1.0 : cos_k_theta(id, ddx * inv, ddy * inv);
-    if (part == PART_REAL) return ck / dist;
-    const double tau = line_integral(S, ax, ay, bx, by);
+    if (part == PART_REAL) return ck * inv;
+    const double tau = S.ty ? line_integral_d1(S, ax, ay, bx, by, dist) : line_integral(S, ax, ay, bx, by);
     const double e = exp(-tau);
-    if (part == PART_IMAG) return (e - 1.0) * ck / dist;
-    return e * ck / dist;
+    if (part == PART_IMAG) return (e - 1.0) * ck * inv;
+    return e * ck * inv;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -185,7 +249,10 @@ void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const Sigm
 
 __global__ void probe_line_integral_kernel(SigmaGrid S, int n, const double* __restrict__ p, double* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = line_integral(S, p[4 * i], p[4 * i + 1], p[4 * i + 2], p[4 * i + 3]);
+    if (i >= n) return;
+    const double x0 = p[4 * i], y0 = p[4 * i + 1], x1 = p[4 * i + 2], y1 = p[4 * i + 3];
+    const double len = sqrt((x1 - x0) * (x1 - x0) + (y1 - y0) * (y1 - y0));
+    out[i] = (S.ty && len > 0.0) ? line_integral_d1(S, x0, y0, x1, y1, len) : line_integral(S, x0, y0, x1, y1);
 }
 __global__ void probe_kernel_kernel(SigmaGrid S, int id, int part, int n, const double* __restrict__ p,
                                     double* __restrict__ out) {
@@ -403,6 +470,31 @@ __global__ void interpolate_kernel(DevGeom G, const double* __restrict__ h, cons
 }
 void launch_interpolate(const DevGeom& G, const double* h_ref, const double* lnorm_or_null, double* coeff, cudaStream_t st) {
     interpolate_kernel<<<(G.N + 255) / 256, 256, 0, st>>>(G, h_ref, lnorm_or_null, coeff);
+}
+
+// Running integrals of the piecewise-constant sigma_t along every grid line (deg == 1): one thread per line.
+__global__ void sigma_prefix_kernel(SigmaGrid S, double2* __restrict__ ty, double2* __restrict__ tx) {
+    const int line = blockIdx.x * blockDim.x + threadIdx.x;
+    const int sz = S.sz;
+    if (line >= 2 * sz) return;
+    double run = 0;
+    if (line < sz) {  // column cx = line, along y
+        for (int j = 0; j < sz; ++j) {
+            const double sg = S.chat[(size_t)line * sz + j];
+            ty[(size_t)line * sz + j] = make_double2(run, sg);
+            run = fma(sg, S.h, run);
+        }
+    } else {  // row cy, along x
+        const int cy = line - sz;
+        for (int i = 0; i < sz; ++i) {
+            const double sg = S.chat[(size_t)i * sz + cy];
+            tx[(size_t)cy * sz + i] = make_double2(run, sg);
+            run = fma(sg, S.h, run);
+        }
+    }
+}
+void launch_sigma_prefix(const SigmaGrid& S, double2* ty, double2* tx, cudaStream_t st) {
+    sigma_prefix_kernel<<<(2 * S.sz + 63) / 64, 64, 0, st>>>(S, ty, tx);
 }
 
 }  // namespace an

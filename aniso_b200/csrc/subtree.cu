@@ -233,11 +233,17 @@ __global__ void __launch_bounds__(256) down_leaf_kernel(DevTree T, DevGeom G, De
             const int c2 = G.c2, sz = G.sz;
             const int tc = G.perm[p] / c2;
             const int ti = tc / sz, tj = tc - ti * sz;
-            for (int cs = 0; cs < 9; ++cs) {
-                const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
-                if (si < 0 || si >= sz || sj < 0 || sj >= sz) continue;
-                const double* __restrict__ fs = f_ref + (size_t)(si * sz + sj) * c2;
-                for (int qq = 0; qq < c2; ++qq) P.corr = fma(C[(size_t)(cs * c2 + qq) * n + k], fs[qq], P.corr);
+            for (int qq = 0; qq < c2; ++qq) {  // the 18 loads of one Legendre mode are issued together
+                double cv[9], fv[9];
+#pragma unroll
+                for (int cs = 0; cs < 9; ++cs) {
+                    const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
+                    const bool ok = si >= 0 && si < sz && sj >= 0 && sj < sz;
+                    cv[cs] = ok ? C[(size_t)(cs * c2 + qq) * n + k] : 0.0;
+                    fv[cs] = ok ? f_ref[(size_t)(si * sz + sj) * c2 + qq] : 0.0;
+                }
+#pragma unroll
+                for (int cs = 0; cs < 9; ++cs) P.corr = fma(cv[cs], fv[cs], P.corr);
             }
         }
         const int id = leaf_of_slot[p];
