@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(256) down_mid_kernel(DevTree T, DevCSR m2l, do
 //   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi
 // near(p): P2P sum, already reduced in pot or still spread over the leaf's scratch rows (fold_p2p).
 template <int NP, bool SMEM_R, bool FOLD>
-__global__ void __launch_bounds__(256) down_leaf_kernel(DevTree T, DevGeom G, DevCSR m2l, DevCSR p2p, int fold_p2p,
+__global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree T, DevGeom G, DevCSR m2l, DevCSR p2p, int fold_p2p,
                                                         const int* __restrict__ leaf_of_slot, int slot0, int n,
                                                         double* __restrict__ mpot, const double* __restrict__ pot,
                                                         const double* __restrict__ C, const double* __restrict__ f_ref,
