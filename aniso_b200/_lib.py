@@ -61,6 +61,8 @@ SIGNATURES = {
     "aniso_synchronize": (C.c_int, [_H]),
     "aniso_dev_alloc": (C.c_int, [_H, C.c_size_t, C.POINTER(C.c_void_p)]),
     "aniso_dev_free": (C.c_int, [_H, C.c_void_p]),
+    "aniso_host_alloc": (C.c_int, [_H, C.c_size_t, C.POINTER(C.c_void_p)]),
+    "aniso_host_free": (C.c_int, [_H, C.c_void_p]),
     "aniso_to_slots": (C.c_int, [_H, _dp, _V]),
     "aniso_from_slots": (C.c_int, [_H, _V, _dp]),
     "aniso_launch_count": (C.c_int64, [_H]),

@@ -41,10 +41,14 @@ class Aniso:
         self.kernelSize = self.L.aniso_kernel_size(h)
         self.sz, self.deg, self.sr, self.np, self.maxLevel = int(ds), int(qr), int(sr), int(fn), int(fm)
         self.sigma_s = self.sigma_t = None
+        self._pinned = []
 
     # -- life cycle --------------------------------------------------------------------------------------
     def delete(self):
         if getattr(self, "h", None):
+            for p in self._pinned:
+                self.L.aniso_host_free(self.h, p)
+            self._pinned = []
             self.L.aniso_destroy(self.h)
             self.h = None
 
@@ -232,6 +236,15 @@ class Aniso:
         ms = C.c_double()
         _lib.check(self.L.aniso_time_kernel(self.h, int(kid), int(which), int(reps), C.byref(ms)))
         return ms.value
+
+    def pinned_empty(self, n):
+        """float64 array of n entries in page-locked host memory (aniso_host_alloc): vectors passed to mapping()/gmres()
+        from it are DMA'd directly instead of being staged.  Freed with the handle."""
+        import ctypes as C
+        p = C.c_void_p()
+        _lib.check(self.L.aniso_host_alloc(self.h, 8 * n, C.byref(p)))
+        self._pinned.append(p)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_double)), shape=(n,))
 
     def synchronize(self):
         _lib.check(self.L.aniso_synchronize(self.h))

@@ -52,6 +52,7 @@ struct aniso_handle {
     cudaStream_t st_bulk = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr;
     bool overlap = true;
+    std::vector<cudaEvent_t> copy_ev;  // per-chunk events of the device -> host copy
     int m2l_top_groups = 0;  // M2L groups of the first level that has V lists (a prefix: level-major numbering)
     int m2l_deep_g0 = 0;     // M2L groups [m2l_deep_g0, groups) belong to the deepest level and read only leaf multipoles
     bool subtree_ok = false;  // complete uniform tree: the sub-tree passes of subtree.cu replace the level-by-level ones
@@ -399,6 +400,7 @@ int aniso_destroy(aniso_t* h) {
         cudaStreamSynchronize(h->st_bulk);
         for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join})
             if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : h->copy_ev) cudaEventDestroy(e);
         cudaStreamDestroy(h->st_bulk);
         cudaStreamDestroy(h->st);
     }
@@ -695,12 +697,28 @@ void mapping_slots(aniso_handle* h, const double* f_full, int id, const double* 
 }
 
 // host vector (N doubles) -> h->d_stage through the pinned buffer; the stream is drained first so the pinned
-// buffer is never rewritten under an in-flight copy
+// buffer is never rewritten under an in-flight copy.  Chunked: the CPU copy of chunk c+1 overlaps the DMA of chunk c.
+constexpr int COPY_CHUNK = 1 << 18;  // doubles (2 MB)
+bool is_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
 void stage_h2d(aniso_handle* h, const double* host) {
     const int N = h->plan.N;
+    if (is_pinned(host)) {  // caller's page-locked memory: one direct DMA
+        CK(cudaMemcpyAsync(h->d_stage, host, sizeof(double) * N, cudaMemcpyHostToDevice, h->st));
+        return;
+    }
     CK(cudaStreamSynchronize(h->st));
-    std::memcpy(h->pinned, host, sizeof(double) * N);
-    CK(cudaMemcpyAsync(h->d_stage, h->pinned, sizeof(double) * N, cudaMemcpyHostToDevice, h->st));
+    for (int off = 0; off < N; off += COPY_CHUNK) {
+        const int n = std::min(COPY_CHUNK, N - off);
+        std::memcpy(h->pinned + off, host + off, sizeof(double) * n);
+        CK(cudaMemcpyAsync(h->d_stage + off, h->pinned + off, sizeof(double) * n, cudaMemcpyHostToDevice, h->st));
+    }
 }
 
 // host (reference order) -> device slot order, full vector
@@ -713,6 +731,33 @@ void to_slots(aniso_handle* h, const double* host, double* dev) {
 void from_slots(aniso_handle* h, const double* dev_own, double* host) {
     const HostPlan& p = h->plan;
     double* stage = h->pinned + p.N;
+    if (h->nranks == 1) {
+        // permute on the device, then bring the vector back in chunks: the CPU copy of chunk c overlaps the DMA of c+1
+        const int N = p.N;
+        LAUNCH(h, launch_scatter(N, dev_own, h->G.perm, h->d_stage, h->st));
+        if (is_pinned(host)) {
+            CK(cudaMemcpyAsync(host, h->d_stage, sizeof(double) * N, cudaMemcpyDeviceToHost, h->st));
+            CK(cudaStreamSynchronize(h->st));
+            return;
+        }
+        const int nch = (N + COPY_CHUNK - 1) / COPY_CHUNK;
+        while ((int)h->copy_ev.size() < nch) {
+            cudaEvent_t e;
+            CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            h->copy_ev.push_back(e);
+        }
+        for (int c = 0; c < nch; ++c) {
+            const int off = c * COPY_CHUNK, n = std::min(COPY_CHUNK, N - off);
+            CK(cudaMemcpyAsync(stage + off, h->d_stage + off, sizeof(double) * n, cudaMemcpyDeviceToHost, h->st));
+            CK(cudaEventRecord(h->copy_ev[c], h->st));
+        }
+        for (int c = 0; c < nch; ++c) {
+            const int off = c * COPY_CHUNK, n = std::min(COPY_CHUNK, N - off);
+            CK(cudaEventSynchronize(h->copy_ev[c]));
+            std::memcpy(host + off, stage + off, sizeof(double) * n);
+        }
+        return;
+    }
     CK(cudaMemcpyAsync(stage, dev_own, sizeof(double) * h->nown, cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     for (int k = 0; k < h->nown; ++k) host[p.perm[h->slot0 + k]] = stage[k];
@@ -1035,11 +1080,14 @@ int gmres_core(aniso_handle* h, const double* b, double* x, int m, int max_iter,
             if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
             *iters = j;
             forward_own(h, g.v(i), g.w);
-            for (int k = 0; k <= i; ++k) {  // modified Gram-Schmidt, gmres.cpp:115-119
-                ddot_dev(h, n, g.w, g.v(k), dh + k, false);
-                LAUNCH(h, launch_axpy_neg_dev(n, dh + k, g.v(k), g.w, h->st));
+            // modified Gram-Schmidt, gmres.cpp:115-119: h_k = w . v_k; w -= h_k v_k.  The axpy of step k and the dot of
+            // step k+1 (or the final norm) share one pass over w.
+            ddot_dev(h, n, g.w, g.v(0), dh, false);
+            for (int k = 0; k <= i; ++k) {
+                LAUNCH(h, launch_axpy_dot(n, dh + k, g.v(k), g.w, k < i ? g.v(k + 1) : nullptr, dh + k + 1, h->dot, h->st));
+                allreduce_scalars(h, dh + k + 1, 1);
             }
-            ddot_dev(h, n, g.w, g.w, dh + i + 1, true);
+            LAUNCH(h, launch_sqrt1(dh + i + 1, h->st));
             LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), h->st));
             CK(cudaMemcpyAsync(col.data(), dh, sizeof(double) * (i + 2), cudaMemcpyDeviceToHost, h->st));
             CK(cudaStreamSynchronize(h->st));
@@ -1131,6 +1179,22 @@ int aniso_dev_free(aniso_t* h, void* p) {
     REQUIRE(h, "null handle");
     CK(cudaSetDevice(h->device));
     dfree(h, p);
+    return ANISO_OK;
+    API_END
+}
+int aniso_host_alloc(aniso_t* h, size_t bytes, void** out) {
+    API_BEGIN
+    REQUIRE(h && out, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    CK(cudaMallocHost(out, std::max<size_t>(bytes, 1)));
+    return ANISO_OK;
+    API_END
+}
+int aniso_host_free(aniso_t* h, void* p) {
+    API_BEGIN
+    REQUIRE(h, "null handle");
+    if (p) CK(cudaFreeHost(p));
     return ANISO_OK;
     API_END
 }

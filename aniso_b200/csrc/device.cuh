@@ -116,6 +116,7 @@ void launch_stencil_apply(const DevGeom& G, int slot0, int nown, const double* C
 void launch_finalize(int n, const double* fmm, const double* corr, const double* x, double* out, int subtract_from_x,
                      cudaStream_t st);
 void launch_gather(int n, const double* src, const int* idx, double* dst, cudaStream_t st);  // dst[i] = src[idx[i]]
+void launch_scatter(int n, const double* src, const int* idx, double* dst, cudaStream_t st);  // dst[idx[i]] = src[i]
 void launch_add3(long n, const double* a, const double* b, const double* c, double* out, cudaStream_t st);
 // sigma interpolation on device: chat[c][r] = (sum_j interp[r][j] sqrtw[j] h[c*c2+j]) / (lnorm ? lnorm[r] : 1), h in REFERENCE order
 void launch_interpolate(const DevGeom& G, const double* h_ref, const double* lnorm_or_null, double* coeff, cudaStream_t st);
@@ -132,6 +133,9 @@ struct DotWork {
     int blocks = 0;
 };
 void launch_dot(int n, const double* a, const double* b, double* result, DotWork& wk, cudaStream_t st);
+// w -= h[0] * v, then result = w . u (u == nullptr: w . w): one MGS step in one pass
+void launch_axpy_dot(int n, const double* h, const double* v, double* w, const double* u, double* result, DotWork& wk,
+                     cudaStream_t st);
 // w -= h[0] * v  (h read from device memory)
 void launch_axpy_neg_dev(int n, const double* h, const double* v, double* w, cudaStream_t st);
 void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t st);

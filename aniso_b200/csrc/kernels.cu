@@ -445,6 +445,13 @@ __global__ void gather_kernel(int n, const double* __restrict__ src, const int* 
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) dst[i] = src[idx[i]];
 }
+__global__ void scatter_kernel(int n, const double* __restrict__ src, const int* __restrict__ idx, double* __restrict__ dst) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[idx[i]] = src[i];
+}
+void launch_scatter(int n, const double* src, const int* idx, double* dst, cudaStream_t st) {
+    if (n) scatter_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, src, idx, dst);
+}
 void launch_gather(int n, const double* src, const int* idx, double* dst, cudaStream_t st) {
     if (n) gather_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, src, idx, dst);
 }

@@ -44,6 +44,58 @@ __global__ void __launch_bounds__(kDotThreads) dot_kernel(int n, const double* _
     }
 }
 
+// One modified Gram-Schmidt step in a single pass (gmres.cpp:115-119 does a dot and an axpy per basis vector):
+//   w -= h[0] * v          (h: the projection computed by the previous dot, still in device memory)
+//   result = w . u         (u = the next basis vector, or u == nullptr: w . w for the final norm)
+// Same deterministic two-stage reduction as dot_kernel.
+__global__ void __launch_bounds__(kDotThreads) axpy_dot_kernel(int n, const double* __restrict__ h, const double* __restrict__ v,
+                                                               double* __restrict__ w, const double* __restrict__ u,
+                                                               double* __restrict__ result, double* __restrict__ partial,
+                                                               unsigned int* __restrict__ counter) {
+    __shared__ double warp_sum[kDotThreads / 32];
+    __shared__ bool last;
+    const double alpha = -*h;
+    double acc = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const double wi = fma(alpha, v[i], w[i]);
+        w[i] = wi;
+        acc = fma(wi, u ? u[i] : wi, acc);
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int k = 0; k < kDotThreads / 32; ++k) s += warp_sum[k];
+        partial[blockIdx.x] = s;
+        __threadfence();
+        last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    double s = 0;
+    for (int i = threadIdx.x; i < gridDim.x; i += blockDim.x) s += ((volatile double*)partial)[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0;
+        for (int k = 0; k < kDotThreads / 32; ++k) tot += warp_sum[k];
+        *result = tot;
+        *counter = 0;
+    }
+}
+
+void launch_axpy_dot(int n, const double* h, const double* v, double* w, const double* u, double* result, DotWork& wk,
+                     cudaStream_t st) {
+    int blocks = (n + kDotThreads * 4 - 1) / (kDotThreads * 4);
+    if (blocks < 1) blocks = 1;
+    if (blocks > wk.blocks) blocks = wk.blocks;
+    axpy_dot_kernel<<<blocks, kDotThreads, 0, st>>>(n, h, v, w, u, result, wk.partial, wk.counter);
+}
+
 void launch_dot(int n, const double* a, const double* b, double* result, DotWork& wk, cudaStream_t st) {
     int blocks = (n + kDotThreads * 4 - 1) / (kDotThreads * 4);
     if (blocks < 1) blocks = 1;

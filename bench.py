@@ -277,8 +277,10 @@ def run_ours(args):
     value = n / (ms_step * 1e-3)
 
     # ---- end-to-end through the C-ABI with host buffers ----
-    out_host = np.zeros(n)
-    charge = f_host * ss
+    # host buffers in page-locked memory (aniso_host_alloc), as the e2e contract asks: the library DMAs them directly
+    out_host = a.pinned_empty(n)
+    charge = a.pinned_empty(n)
+    charge[:] = f_host * ss
     _lib.check(L.aniso_mapping(a.h, charge, 0, out_host))
     barrier()
     t0 = time.perf_counter()

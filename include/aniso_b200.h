@@ -149,6 +149,11 @@ int aniso_synchronize(aniso_t* h);
 /* device buffer helpers for callers without a CUDA runtime of their own */
 int aniso_dev_alloc(aniso_t* h, size_t bytes, void** out);
 int aniso_dev_free(aniso_t* h, void* p);
+/* page-locked host buffers: vectors passed to aniso_mapping / aniso_gmres / aniso_to_slots / aniso_from_slots from such a
+ * buffer (or from any memory the caller registered with cudaHostRegister) are DMA'd directly, others are staged through
+ * the handle's own pinned buffer in 2 MB chunks */
+int aniso_host_alloc(aniso_t* h, size_t bytes, void** out);
+int aniso_host_free(aniso_t* h, void* p);
 int aniso_to_slots(aniso_t* h, const double* ref_order_host, double* slot_order_dev);   /* H2D + permute */
 int aniso_from_slots(aniso_t* h, const double* slot_order_dev, double* ref_order_host); /* permute + D2H (owned rows only
                                                                                             when sharded: others untouched) */
