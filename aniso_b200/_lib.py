@@ -54,6 +54,10 @@ SIGNATURES = {
     "aniso_singular_add_fast": (C.c_int, [_H, C.c_int, _dp, _dp]),
     "aniso_gmres": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
     "aniso_gmres_dev": (C.c_int, [_H, _V, _V, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
+    "aniso_block_forward": (C.c_int, [_H, _dp, C.c_int, _dp]),
+    "aniso_block_forward_dev": (C.c_int, [_H, _V, C.c_int, _V]),
+    "aniso_block_gmres": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
+    "aniso_block_gmres_dev": (C.c_int, [_H, _V, _V, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
     "aniso_line_integral": (C.c_int, [_H, C.c_int, _dp, _dp]),
     "aniso_kernel_eval": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, _dp, _dp]),
     "aniso_stream": (C.c_void_p, [_H]),

@@ -146,6 +146,32 @@ class Aniso:
                                            hist.size))
         return x, rc, it.value, hist[: it.value + 1]
 
+    # -- MATLAB application layer (aniso.m:121-172): multi-mode block operator ------------------------------------
+    def forward(self, u):
+        """aniso.m:121-136: rhs_i = sum_j mapping(u_|j|, |i-j|); u, rhs: K*N, mode-major."""
+        n = self.kernelSize // 2 + 1
+        out = np.zeros(n * self.numberOfNodes)
+        _lib.check(self.L.aniso_block_forward(self.h, _vec(u, n * self.numberOfNodes, "u"), 0, out))
+        return out
+
+    def mforward(self, u):
+        """aniso.m:138-156: rhs_i = sum_j chi_|j| mapping(sigma_s .* u_|j|, |i-j|), chi_a = (g^a - g^K)/(1 - g^K)."""
+        n = self.kernelSize // 2 + 1
+        out = np.zeros(n * self.numberOfNodes)
+        _lib.check(self.L.aniso_block_forward(self.h, _vec(u, n * self.numberOfNodes, "u"), 1, out))
+        return out
+
+    def solve(self, charge, m=400, max_iter=400, tol=1e-11):
+        """aniso.m:158-172 without preconditioner: rhs = forward(charge); (I - mforward) y = rhs by GMRES(400, 1e-11, 400)
+        (the reference's gmres.cpp; MATLAB's gmres is the caller there).  Returns (y, rc, iterations, residual history)."""
+        K = self.kernelSize // 2 + 1
+        rhs = self.forward(charge)
+        x = np.zeros(K * self.numberOfNodes)
+        it = C.c_int(0)
+        hist = np.zeros(max_iter + 2)
+        rc = _lib.check(self.L.aniso_block_gmres(self.h, rhs, x, int(m), int(max_iter), float(tol), C.byref(it), hist, hist.size))
+        return x, rc, it.value, hist[: it.value + 1]
+
     # -- probes / introspection ---------------------------------------------------------------------------------
     def line_integral(self, pts4):
         p = np.ascontiguousarray(np.asarray(pts4, np.float64).reshape(-1, 4))

@@ -69,6 +69,7 @@ struct aniso_handle {
     // work vectors
     double *d_f = nullptr, *d_q = nullptr, *d_mcharge = nullptr, *d_mpot = nullptr, *d_pot = nullptr;
     double *d_fmm = nullptr, *d_corr = nullptr, *d_a = nullptr, *d_b = nullptr, *d_xfull = nullptr, *d_stage = nullptr;
+    double *d_blk_full = nullptr, *d_blk_tmp = nullptr;  // block operator work space
     double* pinned = nullptr;  // 2N doubles
     std::map<std::pair<int, int>, OperatorCache> ops;
     std::map<int, StencilCache> stencils;
@@ -1035,6 +1036,35 @@ void forward_own(aniso_handle* h, const double* x_own, double* y_own) {
     mapping_slots(h, full, 0, h->d_sig_s, x_own, y_own, 1);
 }
 
+// Multi-mode block operator of the MATLAB application (aniso.m:121-156): K angular modes of n values,
+//   forward (weighted = false):  out_i = sum_{j=-(K-1)}^{K-1} mapping_{|i+j|}(u_|j|)
+//   mforward (weighted = true):  out_i = sum_j chi_|j| mapping_{|i+j|}(sigma_s .* u_|j|),  chi_a = (g^a - g^K)/(1 - g^K)
+// the only place the Henyey-Greenstein anisotropy g acts.  subtract: out = u - out (the GMRES operator of aniso.m:162).
+// u_own / out: K blocks of owned rows in slot order.  Loop and accumulation order are the reference's.
+void block_apply(aniso_handle* h, const double* u_own, double* out, bool weighted, bool subtract) {
+    const int K = h->plan.K, N = h->plan.N, n = h->nown;
+    if (!h->d_blk_tmp) h->d_blk_tmp = dalloc<double>(h, n);
+    const double* full = u_own;
+    if (h->nranks > 1) {
+        if (!h->d_blk_full) h->d_blk_full = dalloc<double>(h, (size_t)K * N);
+        for (int a = 0; a < K; ++a) allgather_slots(h, u_own + (size_t)a * n, h->d_blk_full + (size_t)a * N);
+        full = h->d_blk_full;
+    }
+    const double g = h->plan.g, gK = std::pow(g, K);
+    for (int i = -(K - 1); i <= 0; ++i) {
+        const int iid = -i;
+        double* acc = out + (size_t)iid * n;
+        CK(cudaMemsetAsync(acc, 0, sizeof(double) * n, h->st));
+        for (int j = -(K - 1); j <= K - 1; ++j) {
+            const int id = std::abs(j), k = std::abs(i - j);
+            mapping_slots(h, full + (size_t)id * N, k, weighted ? h->d_sig_s : nullptr, nullptr, h->d_blk_tmp, 0);
+            const double chi = weighted ? (std::pow(g, id) - gK) / (1.0 - gK) : 1.0;
+            LAUNCH(h, launch_axpy(n, chi, h->d_blk_tmp, acc, h->st));
+        }
+        if (subtract) LAUNCH(h, launch_sub(n, u_own + (size_t)iid * n, acc, acc, h->st));
+    }
+}
+
 // Update, gmres.cpp:12-24
 void gm_update(GmresWork& g, double* x, int k, const std::vector<double>& H, int ldh, const std::vector<double>& s) {
     std::vector<double> y(s.begin(), s.begin() + k + 1);
@@ -1045,11 +1075,11 @@ void gm_update(GmresWork& g, double* x, int k, const std::vector<double>& H, int
     for (int j = 0; j <= k; ++j) LAUNCH(g.h, launch_axpy(g.n, y[j], g.v(j), x, g.h->st));
 }
 
-int gmres_core(aniso_handle* h, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
+// A: y = A x on device vectors of length n (owned rows; for the block operator K blocks of owned rows)
+template <class Op>
+int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
                int hist_cap) {
-    const int n = h->nown, ldh = m + 1;
-    ensure_ops(h, 0, PART_BOTH);
-    ensure_stencils(h, 0);
+    const int ldh = m + 1;
     GmresWork g{h, n, m, nullptr, nullptr, nullptr};
     g.w = dalloc<double>(h, n);
     g.r = dalloc<double>(h, n);
@@ -1063,7 +1093,7 @@ int gmres_core(aniso_handle* h, const double* b, double* x, int m, int max_iter,
     *iters = 0;
     ddot_dev(h, n, b, b, dh, true);
     double normb = read_scalar(h, dh);
-    forward_own(h, x, g.w);
+    A(x, g.w);
     LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
     ddot_dev(h, n, g.r, g.r, dh, true);
     double beta = read_scalar(h, dh);
@@ -1079,7 +1109,7 @@ int gmres_core(aniso_handle* h, const double* b, double* x, int m, int max_iter,
         for (i = 0; i < m && j <= max_iter; ++i, ++j) {
             if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
             *iters = j;
-            forward_own(h, g.v(i), g.w);
+            A(g.v(i), g.w);
             // modified Gram-Schmidt, gmres.cpp:115-119: h_k = w . v_k; w -= h_k v_k.  The axpy of step k and the dot of
             // step k+1 (or the final norm) share one pass over w.
             ddot_dev(h, n, g.w, g.v(0), dh, false);
@@ -1105,7 +1135,7 @@ int gmres_core(aniso_handle* h, const double* b, double* x, int m, int max_iter,
         }
         if (done) break;
         gm_update(g, x, i - 1, H, ldh, s);
-        forward_own(h, x, g.w);
+        A(x, g.w);
         LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
         ddot_dev(h, n, g.r, g.r, dh, true);
         beta = read_scalar(h, dh);
@@ -1133,7 +1163,10 @@ int aniso_gmres_dev(aniso_t* h, const double* b, double* x, int m, int max_iter,
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede GMRES");
-    return gmres_core(h, b, x, m, max_iter, tol, iters, hist, hist_cap);
+    ensure_ops(h, 0, PART_BOTH);
+    ensure_stencils(h, 0);
+    return gmres_core(h, [h](const double* xx, double* yy) { forward_own(h, xx, yy); }, h->nown, b, x, m, max_iter, tol, iters,
+                      hist, hist_cap);
     API_END
 }
 
@@ -1148,8 +1181,87 @@ int aniso_gmres(aniso_t* h, const double* b, double* x, int m, int max_iter, dou
     double* dx = dalloc<double>(h, h->plan.N);
     to_slots(h, b, db);
     to_slots(h, x, dx);
-    const int rc = gmres_core(h, db + h->slot0, dx + h->slot0, m, max_iter, tol, iters, hist, hist_cap);
+    ensure_ops(h, 0, PART_BOTH);
+    ensure_stencils(h, 0);
+    const int rc = gmres_core(h, [h](const double* xx, double* yy) { forward_own(h, xx, yy); }, h->nown, db + h->slot0,
+                              dx + h->slot0, m, max_iter, tol, iters, hist, hist_cap);
     from_slots(h, dx + h->slot0, x);
+    dfree(h, db);
+    dfree(h, dx);
+    return rc;
+    API_END
+}
+
+int aniso_block_forward_dev(aniso_t* h, const double* u_dev, int weighted, double* out_dev) {
+    API_BEGIN
+    REQUIRE(h && u_dev && out_dev, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede the block operator");
+    block_apply(h, u_dev, out_dev, weighted != 0, false);
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_block_forward(aniso_t* h, const double* u, int weighted, double* out) {
+    API_BEGIN
+    REQUIRE(h && u && out, "null pointer");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede the block operator");
+    const int K = h->plan.K, N = h->plan.N, n = h->nown;
+    double* du = dalloc<double>(h, (size_t)K * N);
+    double* dow = dalloc<double>(h, (size_t)K * n);
+    double* down = dalloc<double>(h, (size_t)K * n);
+    for (int a = 0; a < K; ++a) {
+        to_slots(h, u + (size_t)a * N, du + (size_t)a * N);
+        CK(cudaMemcpyAsync(dow + (size_t)a * n, du + (size_t)a * N + h->slot0, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
+    }
+    block_apply(h, dow, down, weighted != 0, false);
+    for (int a = 0; a < K; ++a) from_slots(h, down + (size_t)a * n, out + (size_t)a * N);
+    dfree(h, du);
+    dfree(h, dow);
+    dfree(h, down);
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
+                          double* hist, int hist_cap) {
+    API_BEGIN
+    REQUIRE(h && rhs_dev && x_dev && iters && m >= 1 && max_iter >= 0, "bad arguments");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede GMRES");
+    for (int k = 0; k < h->plan.kernelSize; ++k) {
+        ensure_ops(h, k, PART_BOTH);
+        ensure_stencils(h, k);
+    }
+    return gmres_core(h, [h](const double* xx, double* yy) { block_apply(h, xx, yy, true, true); }, h->plan.K * h->nown, rhs_dev,
+                      x_dev, std::min(m, std::max(max_iter, 1)), max_iter, tol, iters, hist, hist_cap);
+    API_END
+}
+
+int aniso_block_gmres(aniso_t* h, const double* rhs, double* x, int m, int max_iter, double tol, int* iters, double* hist,
+                      int hist_cap) {
+    API_BEGIN
+    REQUIRE(h && rhs && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    const int K = h->plan.K, N = h->plan.N, n = h->nown;
+    double* tmp = dalloc<double>(h, N);
+    double* db = dalloc<double>(h, (size_t)K * n);
+    double* dx = dalloc<double>(h, (size_t)K * n);
+    for (int a = 0; a < K; ++a) {
+        to_slots(h, rhs + (size_t)a * N, tmp);
+        CK(cudaMemcpyAsync(db + (size_t)a * n, tmp + h->slot0, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
+        to_slots(h, x + (size_t)a * N, tmp);
+        CK(cudaMemcpyAsync(dx + (size_t)a * n, tmp + h->slot0, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
+    }
+    const int rc = aniso_block_gmres_dev(h, db, dx, m, max_iter, tol, iters, hist, hist_cap);
+    if (rc >= 0)
+        for (int a = 0; a < K; ++a) from_slots(h, dx + (size_t)a * n, x + (size_t)a * N);
+    dfree(h, tmp);
     dfree(h, db);
     dfree(h, dx);
     return rc;

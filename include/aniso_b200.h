@@ -136,6 +136,21 @@ int aniso_gmres(aniso_t* h, const double* b_host, double* x_host, int m, int max
 int aniso_gmres_dev(aniso_t* h, const double* b_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
                     double* resid_hist, int hist_cap);
 
+/* ---- multi-mode block operator (MATLAB application layer: aniso.m:121-156 forward / mforward, aniso.m:158-172 solve) ----
+ * Block vectors hold K = kernel_size angular modes of N values, mode-major: mode a at [a*N, (a+1)*N), reference node order.
+ *   weighted = 0  `forward`:  out_i = sum_{j=-(K-1)}^{K-1} mapping_{|i+j|}(u_|j|)                         (aniso.m:121-136)
+ *   weighted = 1  `mforward`: out_i = sum_j chi_|j| mapping_{|i+j|}(sigma_s .* u_|j|), chi_a = (g^a - g^K)/(1 - g^K)
+ *                                                                                                       (aniso.m:138-156)
+ * aniso_block_gmres solves (I - mforward) x = rhs with the reference's own GMRES (gmres.cpp:53-169; MATLAB's gmres is not
+ * available to the oracle either): aniso.m:165-169 uses restart 400, tol 1e-11, maxit 400.  The _dev forms take K blocks of
+ * OWNED rows in slot order (block a at [a*nown, (a+1)*nown)). */
+int aniso_block_forward(aniso_t* h, const double* u_host, int weighted, double* out_host);
+int aniso_block_forward_dev(aniso_t* h, const double* u_dev, int weighted, double* out_dev);
+int aniso_block_gmres(aniso_t* h, const double* rhs_host, double* x_host, int m, int max_iter, double tol, int* iters,
+                      double* resid_hist, int hist_cap);
+int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
+                          double* resid_hist, int hist_cap);
+
 /* ---- device probes (parity tests of K1/K2 pieces) ---------------------------------------------------------- */
 /* lineIntegral(x0,y0,x1,y1) KernelFactory.cpp:67-166 for n segments, pts4 = n x 4 host doubles */
 int aniso_line_integral(aniso_t* h, int n, const double* pts4_host, double* out_host);

@@ -62,3 +62,10 @@ CASES = {
     "c2": (128, 1, 5, 0.5, 10, 4, 20, "const"),     # BASELINE config 2
     "c1": (64, 3, 1, 0.95, 8, 4, 20, "main"),       # BASELINE config 1 (data.cfg)
 }
+
+# multi-mode block operator (aniso.m forward / mforward / solve): name -> same tuple
+BLOCK_CASES = {
+    "a16": CASES["a16"],                              # K 2, g 0.5
+    "k3h16": (16, 1, 3, 0.9, 10, 4, 20, "hetero"),    # K 3 (kernel ids 0..4), strong forward scattering, heterogeneous sigma
+    "b8d3": CASES["b8d3"],                            # deg 3
+}

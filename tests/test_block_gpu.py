@@ -1,0 +1,89 @@
+"""GPU parity of the multi-mode block operator (aniso.m:121-172 forward / mforward / solve) through the
+C-ABI (aniso_block_forward, aniso_block_gmres) against golden fixtures made with the compiled reference `mapping`
+(tests/golden/make_golden_block.py) and against the CPU oracle on a seeded input."""
+import numpy as np
+import pytest
+
+import cases
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def rel(a, b):
+    return np.linalg.norm(a - b) / np.linalg.norm(b)
+
+
+def make(name):
+    from aniso_b200 import Aniso
+
+    sz, deg, K, g, sr, np_, ml, kind = cases.BLOCK_CASES[name]
+    a = Aniso(sz, deg, K, g, sr, np_, ml)
+    x, y, w = a.nodes()
+    ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+    a.setCoeff(ss, st)
+    return a, K, g, ss, x.size
+
+
+@pytest.mark.parametrize("name", ["a16", "k3h16", "b8d3"])
+def test_forward_mforward_vs_reference_golden(golden, name):
+    g = golden(name + "_block")
+    a, K, gg, ss, n = make(name)
+    assert rel(a.forward(g["u"]), g["forward"]) < TOL
+    assert rel(a.mforward(g["u"]), g["mforward"]) < TOL
+    a.delete()
+
+
+def test_block_operator_vs_oracle_seeded():
+    from oracle import block_oracle, oracleapi
+
+    name = "k3h16"
+    a, K, gg, ss, n = make(name)
+    sz, deg, _, _, sr, np_, ml, kind = cases.BLOCK_CASES[name]
+    o = oracleapi.OracleAniso(sz, deg, K, gg, sr, np_, ml)
+    x, y, w = o.nodes()
+    o.set_coeff(*cases.sigma_fields(kind, x, y, sz, deg))
+    u = cases.random_source(K * n, 5)
+    assert rel(a.forward(u), block_oracle.forward(o, u, K, n)) < TOL
+    assert rel(a.mforward(u), block_oracle.mforward(o, u, K, n, gg, ss)) < TOL
+    # linearity of the block operator
+    v = cases.random_source(K * n, 6)
+    assert rel(a.mforward(2.0 * u - 3.0 * v), 2.0 * a.mforward(u) - 3.0 * a.mforward(v)) < 1e-12
+    a.delete()
+
+
+@pytest.mark.parametrize("name", ["a16", "k3h16", "b8d3"])
+def test_block_gmres_vs_reference_golden(golden, name):
+    g = golden(name + "_block")
+    a, K, gg, ss, n = make(name)
+    charge = g["u"]
+    xs, rc, it, hist = a.solve(charge)  # rhs = forward(charge); GMRES(400, 1e-11, 400) on I - mforward
+    ref_it = int(g["gm_iters"])
+    assert rc == int(g["gm_rc"]) == 0
+    assert abs(it - ref_it) <= 1, (it, ref_it, hist[-3:], g["gm_hist"][-3:])
+    assert rel(xs, g["gm_x"]) < 1e-8
+    m = min(it, ref_it) - 2
+    np.testing.assert_allclose(hist[:m], g["gm_hist"][:m], rtol=5e-3, atol=1e-8)
+    # the solution satisfies the block equation
+    assert rel(xs - a.mforward(xs), g["forward"]) < 1e-9
+    a.delete()
+
+
+def test_block_operator_at_c2():
+    """BASELINE config 2 (N = 2^14, K = 5, g = 0.5): properties only (the oracle needs minutes there): out_0 of forward with
+    the source in mode 0 contains mapping_0, and linearity."""
+    from aniso_b200 import Aniso
+
+    sz, deg, K, g, sr, np_, ml, kind = cases.CASES["c2"]
+    a = Aniso(sz, deg, K, g, sr, np_, ml)
+    x, y, w = a.nodes()
+    n = x.size
+    ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+    a.setCoeff(ss, st)
+    f = cases.gaussian_source(x, y)
+    u = np.zeros(K * n)
+    u[:n] = f  # demo.m:24-29
+    fw = a.forward(u)
+    for i in range(K):  # only j = 0 contributes: rhs_i = mapping(f, i)
+        assert rel(fw[i * n:(i + 1) * n], a.mapping(f, i)) < 1e-13
+    a.delete()
