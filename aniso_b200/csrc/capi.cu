@@ -1084,9 +1084,14 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     g.w = dalloc<double>(h, n);
     g.r = dalloc<double>(h, n);
     g.V = dalloc<double>(h, (size_t)(m + 1) * n);
-    double* dh = h->d_scal;  // device Hessenberg column, m+2 entries
-    if (m + 2 > 1024) throw std::invalid_argument("restart length m too large (max 1022)");
-    std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0), col(m + 2);
+    double* dh = h->d_scal;  // device Hessenberg column, m+2 entries (+ m+2 for the second CGS2 pass)
+    if (2 * (m + 2) > 1024) throw std::invalid_argument("restart length m too large (max 510)");
+    // orthogonalisation: the reference's modified Gram-Schmidt on one GPU; CGS2 when every dot costs an all-reduce
+    // (ANISO_GMRES_ORTHO=mgs|cgs2 overrides)
+    const char* oenv = getenv("ANISO_GMRES_ORTHO");
+    const bool cgs2 = oenv ? std::string(oenv) == "cgs2" : h->nranks > 1;
+    double* md_partial = cgs2 ? dalloc<double>(h, (size_t)(m + 1) * h->dot.blocks) : nullptr;
+    std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0), col(2 * m + 4);
     int rc = 1, j = 1, i = 0;
     bool done = false;
     double resid = 0;
@@ -1110,18 +1115,35 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
             if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
             *iters = j;
             A(g.v(i), g.w);
-            // modified Gram-Schmidt, gmres.cpp:115-119: h_k = w . v_k; w -= h_k v_k.  The axpy of step k and the dot of
-            // step k+1 (or the final norm) share one pass over w.
-            ddot_dev(h, n, g.w, g.v(0), dh, false);
-            for (int k = 0; k <= i; ++k) {
-                LAUNCH(h, launch_axpy_dot(n, dh + k, g.v(k), g.w, k < i ? g.v(k + 1) : nullptr, dh + k + 1, h->dot, h->st));
-                allreduce_scalars(h, dh + k + 1, 1);
+            if (!cgs2) {
+                // modified Gram-Schmidt, gmres.cpp:115-119: h_k = w . v_k; w -= h_k v_k.  The axpy of step k and the dot of
+                // step k+1 (or the final norm) share one pass over w.
+                ddot_dev(h, n, g.w, g.v(0), dh, false);
+                for (int k = 0; k <= i; ++k) {
+                    LAUNCH(h, launch_axpy_dot(n, dh + k, g.v(k), g.w, k < i ? g.v(k + 1) : nullptr, dh + k + 1, h->dot, h->st));
+                    allreduce_scalars(h, dh + k + 1, 1);
+                }
+            } else {
+                // classical Gram-Schmidt applied twice: the same projections to rounding (H(:,i) = h1 + h2), but all dots of
+                // a pass in one launch and ONE all-reduce, instead of i+1 dependent all-reduces
+                double* h2 = dh + m + 2;
+                for (int pass = 0; pass < 2; ++pass) {
+                    double* hp = pass ? h2 : dh;
+                    LAUNCH(h, launch_multi_dot(n, i + 1, g.w, g.V, (size_t)n, hp, md_partial, h->dot, h->st));
+                    ++h->launches;
+                    allreduce_scalars(h, hp, i + 1);
+                    LAUNCH(h, launch_multi_axpy(n, i + 1, hp, g.V, (size_t)n, g.w, pass ? dh + i + 1 : nullptr, md_partial, h->dot, h->st));
+                }
+                ++h->launches;
+                allreduce_scalars(h, dh + i + 1, 1);
             }
             LAUNCH(h, launch_sqrt1(dh + i + 1, h->st));
             LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), h->st));
-            CK(cudaMemcpyAsync(col.data(), dh, sizeof(double) * (i + 2), cudaMemcpyDeviceToHost, h->st));
+            CK(cudaMemcpyAsync(col.data(), dh, sizeof(double) * (cgs2 ? 2 * m + 4 : i + 2), cudaMemcpyDeviceToHost, h->st));
             CK(cudaStreamSynchronize(h->st));
             for (int k = 0; k <= i + 1; ++k) H[k + (size_t)i * ldh] = col[k];
+            if (cgs2)
+                for (int k = 0; k <= i; ++k) H[k + (size_t)i * ldh] += col[m + 2 + k];
             for (int k = 0; k < i; ++k) apply_rotation(H[k + (size_t)i * ldh], H[k + 1 + (size_t)i * ldh], cs[k], sn[k]);
             plane_rotation(H[i + (size_t)i * ldh], H[i + 1 + (size_t)i * ldh], cs[i], sn[i]);
             apply_rotation(H[i + (size_t)i * ldh], H[i + 1 + (size_t)i * ldh], cs[i], sn[i]);
@@ -1149,6 +1171,7 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     dfree(h, g.w);
     dfree(h, g.r);
     dfree(h, g.V);
+    dfree(h, md_partial);
     return rc;
 }
 

@@ -136,6 +136,12 @@ void launch_dot(int n, const double* a, const double* b, double* result, DotWork
 // w -= h[0] * v, then result = w . u (u == nullptr: w . w): one MGS step in one pass
 void launch_axpy_dot(int n, const double* h, const double* v, double* w, const double* u, double* result, DotWork& wk,
                      cudaStream_t st);
+// CGS2 pieces: out[k] = w . V_k for k < nv (V_k = V + k*ldv; partial: nv * wk.blocks doubles of scratch), and
+// w -= sum_k h[k] V_k with an optional ||w||^2 of the result
+void launch_multi_dot(int n, int nv, const double* w, const double* V, size_t ldv, double* out, double* partial, DotWork& wk,
+                      cudaStream_t st);
+void launch_multi_axpy(int n, int nv, const double* h, const double* V, size_t ldv, double* w, double* norm2_out, double* partial,
+                       DotWork& wk, cudaStream_t st);
 // w -= h[0] * v  (h read from device memory)
 void launch_axpy_neg_dev(int n, const double* h, const double* v, double* w, cudaStream_t st);
 void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t st);

@@ -184,25 +184,32 @@ __device__ __forceinline__ double cos_k_theta(int k, double c, double s) {  // R
     return cr;
 }
 
-__device__ double kernel_eval(const SigmaGrid& S, int id, int part, double ax, double ay, double bx, double by) {
+// D1: the deg-1 table path is known at compile time (keeps the general cell walk and its registers out of the kernel)
+template <bool D1>
+__device__ __forceinline__ double kernel_eval_t(const SigmaGrid& S, int id, int part, double ax, double ay, double bx, double by) {
     const double ddx = ax - bx, ddy = ay - by;
-    const double dist = sqrt(ddx * ddx + ddy * ddy);
-    if (dist == 0.0) return ((part & PART_IMAG) && id == 0) ? sigma_eval(S, ax, ay) : 0.0;
+    const double d2 = ddx * ddx + ddy * ddy;
+    if (d2 == 0.0) return ((part & PART_IMAG) && id == 0) ? sigma_eval(S, ax, ay) : 0.0;
+    const double dist = sqrt(d2);
     const double inv = 1.0 / dist;
     const double ck = id == 0 ? 1.0 : cos_k_theta(id, ddx * inv, ddy * inv);
     if (part == PART_REAL) return ck * inv;
-    const double tau = S.ty ? line_integral_d1(S, ax, ay, bx, by, dist) : line_integral(S, ax, ay, bx, by);
+    const double tau = D1 ? line_integral_d1(S, ax, ay, bx, by, dist) : line_integral(S, ax, ay, bx, by);
     const double e = exp(-tau);
     if (part == PART_IMAG) return (e - 1.0) * ck * inv;
     return e * ck * inv;
+}
+__device__ double kernel_eval(const SigmaGrid& S, int id, int part, double ax, double ay, double bx, double by) {
+    return S.ty ? kernel_eval_t<true>(S, id, part, ax, ay, bx, by) : kernel_eval_t<false>(S, id, part, ax, ay, bx, by);
 }
 
 // ------------------------------------------------------------------------------------------------
 // K1/K2 evaluator.  One CTA per operator block; threads stride over the block column-major in the target
 // index so the rays of one warp join neighbouring points of the same two boxes (similar step counts).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) fill_blocks_kernel(DevCSR m, DevTree T, DevGeom G, SigmaGrid S, int id, int part,
-                                                          int cheb, double* __restrict__ A) {
+template <bool D1>
+__global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, DevTree T, DevGeom G, SigmaGrid S, int id, int part,
+                                                                      int cheb, double* __restrict__ A) {
     const int e = blockIdx.x;
     const int tn = m.tgt_node[e], sn = m.src_node[e];
     const int np = T.np;
@@ -234,7 +241,7 @@ __global__ void __launch_bounds__(256) fill_blocks_kernel(DevCSR m, DevTree T, D
             bx = G.px[toff + t];
             by = G.py[toff + t];
         }
-        out[idx] = kernel_eval(S, id, part, ax, ay, bx, by);
+        out[idx] = kernel_eval_t<D1>(S, id, part, ax, ay, bx, by);
     }
 }
 
@@ -244,7 +251,8 @@ void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const Sigm
     int threads = 256;
     if (cheb && T.r <= 8) threads = 64;
     else if (cheb && T.r <= 11) threads = 128;
-    fill_blocks_kernel<<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    if (S.ty) fill_blocks_kernel<true><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    else fill_blocks_kernel<false><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
 }
 
 __global__ void probe_line_integral_kernel(SigmaGrid S, int n, const double* __restrict__ p, double* __restrict__ out) {

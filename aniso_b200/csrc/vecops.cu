@@ -139,4 +139,86 @@ void launch_sub(int n, const double* a, const double* b, double* out, cudaStream
     if (n) sub_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, a, b, out);
 }
 
+// ---- classical Gram-Schmidt with re-orthogonalisation (CGS2): all projections of one pass in two launches ----
+// multi_dot: partial[(k * gridDim.x) + b] = sum over block b's share of w . V_k, k = blockIdx.y * 8 + kk
+static constexpr int kMD = 8;
+__global__ void __launch_bounds__(kDotThreads) multi_dot_kernel(int n, int nv, const double* __restrict__ w, const double* __restrict__ V,
+                                                                size_t ldv, double* __restrict__ partial) {
+    __shared__ double warp_sum[kMD][kDotThreads / 32];
+    const int k0 = blockIdx.y * kMD;
+    double acc[kMD];
+#pragma unroll
+    for (int kk = 0; kk < kMD; ++kk) acc[kk] = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const double wi = w[i];
+#pragma unroll
+        for (int kk = 0; kk < kMD; ++kk)
+            if (k0 + kk < nv) acc[kk] = fma(wi, V[(size_t)(k0 + kk) * ldv + i], acc[kk]);
+    }
+#pragma unroll
+    for (int kk = 0; kk < kMD; ++kk) {
+        double a = acc[kk];
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_down_sync(0xffffffffu, a, o);
+        if ((threadIdx.x & 31) == 0) warp_sum[kk][threadIdx.x >> 5] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x < kMD && k0 + threadIdx.x < nv) {
+        double s = 0;
+        for (int q = 0; q < kDotThreads / 32; ++q) s += warp_sum[threadIdx.x][q];
+        partial[(size_t)(k0 + threadIdx.x) * gridDim.x + blockIdx.x] = s;
+    }
+}
+// out[k] = sum_b partial[k][b] in a fixed order (one warp per k)
+__global__ void reduce_partials_kernel(int nv, int nb, const double* __restrict__ partial, double* __restrict__ out) {
+    const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (k >= nv) return;
+    double s = 0;
+    for (int b = lane; b < nb; b += 32) s += partial[(size_t)k * nb + b];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if (lane == 0) out[k] = s;
+}
+int multi_dot_blocks(int n, const DotWork& wk) {
+    int blocks = (n + kDotThreads * 4 - 1) / (kDotThreads * 4);
+    return blocks < 1 ? 1 : blocks > wk.blocks ? wk.blocks : blocks;
+}
+void launch_multi_dot(int n, int nv, const double* w, const double* V, size_t ldv, double* out, double* partial, DotWork& wk,
+                      cudaStream_t st) {
+    const int nb = multi_dot_blocks(n, wk);
+    multi_dot_kernel<<<dim3(nb, (nv + kMD - 1) / kMD), kDotThreads, 0, st>>>(n, nv, w, V, ldv, partial);
+    reduce_partials_kernel<<<(nv + 7) / 8, 256, 0, st>>>(nv, nb, partial, out);
+}
+// w -= sum_k h[k] V_k; optionally partial[b] = block b's share of w . w (new w) for the norm
+__global__ void __launch_bounds__(kDotThreads) multi_axpy_kernel(int n, int nv, const double* __restrict__ h, const double* __restrict__ V,
+                                                                 size_t ldv, double* __restrict__ w, double* __restrict__ partial) {
+    __shared__ double warp_sum[kDotThreads / 32];
+    double acc = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        double a0 = w[i], a1 = 0;
+        int k = 0;
+        for (; k + 2 <= nv; k += 2) {
+            a0 = fma(-__ldg(h + k), V[(size_t)k * ldv + i], a0);
+            a1 = fma(-__ldg(h + k + 1), V[(size_t)(k + 1) * ldv + i], a1);
+        }
+        if (k < nv) a0 = fma(-__ldg(h + k), V[(size_t)k * ldv + i], a0);
+        const double wi = a0 + a1;
+        w[i] = wi;
+        acc = fma(wi, wi, acc);
+    }
+    if (!partial) return;
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int q = 0; q < kDotThreads / 32; ++q) s += warp_sum[q];
+        partial[blockIdx.x] = s;
+    }
+}
+void launch_multi_axpy(int n, int nv, const double* h, const double* V, size_t ldv, double* w, double* norm2_out, double* partial,
+                       DotWork& wk, cudaStream_t st) {
+    const int nb = multi_dot_blocks(n, wk);
+    multi_axpy_kernel<<<nb, kDotThreads, 0, st>>>(n, nv, h, V, ldv, w, norm2_out ? partial : nullptr);
+    if (norm2_out) reduce_partials_kernel<<<1, 32, 0, st>>>(1, nb, partial, norm2_out);
+}
+
 }  // namespace an
