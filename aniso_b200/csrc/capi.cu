@@ -53,6 +53,15 @@ struct aniso_handle {
     cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr;
     bool overlap = true;
     std::vector<cudaEvent_t> copy_ev;  // per-chunk events of the device -> host copy
+    // ANISO_PHASE_TIMES=1: events between the phases of every matvec on `st`, averages printed by aniso_destroy (development aid)
+    struct PhaseTimer {
+        bool on = false;
+        std::vector<cudaEvent_t> ev;
+        std::vector<const char*> name;
+        std::vector<double> sum;
+        int cur = 0, reps = 0;
+        bool closed = true;
+    } pt;
     int m2l_top_groups = 0;  // M2L groups of the first level that has V lists (a prefix: level-major numbering)
     int m2l_deep_g0 = 0;     // M2L groups [m2l_deep_g0, groups) belong to the deepest level and read only leaf multipoles
     bool subtree_ok = false;  // complete uniform tree: the sub-tree passes of subtree.cu replace the level-by-level ones
@@ -84,6 +93,34 @@ struct aniso_handle {
 };
 
 namespace {
+
+void phase_mark(aniso_handle* h, const char* name) {  // name == nullptr: start of a matvec
+    auto& t = h->pt;
+    if (!t.on) return;
+    if (name && (t.cur == 0 || t.cur >= 12 || t.closed)) return;  // only inside a matvec started by aniso_forward_dev
+    if (!name) {
+        t.closed = false;
+        if (t.cur > 1) {  // fold in the previous matvec (its events have completed by now or are waited for)
+            cudaEventSynchronize(t.ev[t.cur - 1]);
+            if (t.sum.size() < (size_t)t.cur) t.sum.resize(t.cur, 0.0);
+            for (int i = 1; i < t.cur; ++i) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, t.ev[i - 1], t.ev[i]);
+                t.sum[i] += ms;
+            }
+            ++t.reps;
+        }
+        t.cur = 0;
+    }
+    if ((int)t.ev.size() <= t.cur) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        t.ev.push_back(e);
+        t.name.push_back(name ? name : "start");
+    }
+    cudaEventRecord(t.ev[t.cur++], h->st);
+    if (name && std::string(name) == "down_leaf") t.closed = true;
+}
 
 template <class T>
 T* dalloc(aniso_handle* h, size_t n) {
@@ -161,6 +198,7 @@ void ensure_device(aniso_handle* h) {
     }
     for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
+    h->pt.on = getenv("ANISO_PHASE_TIMES") != nullptr;
     const HostPlan& p = h->plan;
     const int N = p.N, nn = (int)p.nodes.size(), r = p.rank;
     // geometry in slot order
@@ -395,6 +433,12 @@ int aniso_destroy(aniso_t* h) {
     if (h->dev_ready) {
         cudaSetDevice(h->device);
         cudaStreamSynchronize(h->st);
+        if (h->pt.on && h->pt.reps > 0) {
+            phase_mark(h, nullptr);
+            fprintf(stderr, "[aniso rank %d] phases over %d matvecs (us):", h->rank, h->pt.reps);
+            for (size_t i = 1; i < h->pt.sum.size(); ++i) fprintf(stderr, " %s %.1f", h->pt.name[i], 1e3 * h->pt.sum[i] / h->pt.reps);
+            fprintf(stderr, "\n");
+        }
         if (h->comm && h->nccl) h->nccl->CommDestroy(h->comm);
         for (void* p : h->allocs) cudaFree(p);
         if (h->pinned) cudaFreeHost(h->pinned);
@@ -613,16 +657,21 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     if (h->subtree_ok) {
         // complete uniform tree: each pass is ceil(levels/3) launches (subtree.cu)
         h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, h->overlap ? h->ev_leaf : nullptr);
+        phase_mark(h, "up");
         if (h->overlap) {
             CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
             if (gd < ng) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd, ng - gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, sb));
             CK(cudaEventRecord(h->ev_join, sb));
         }
         if (gd > 0) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, 0, gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
+        phase_mark(h, "m2l_shallow");
         h->launches += launch_down_mid_tree(T, h->m2l, sym_m, h->sub, L0, h->d_mpot, h->st);
+        phase_mark(h, "down_mid");
         if (h->overlap) CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
+        phase_mark(h, "join_bulk");
         h->launches += launch_down_leaf_tree(T, h->G, h->m2l, sym_m, h->p2p, sym_p, h->sub, L0, h->d_leaf_of_slot, h->slot0, h->nown,
                                              h->d_mpot, h->d_pot, stencil, f, x_own, out, mode, h->st);
+        phase_mark(h, "down_leaf");
         CK(cudaGetLastError());
         return;
     }
@@ -666,6 +715,17 @@ void allgather_slots(aniso_handle* h, const double* shard, double* full) {
         return;
     }
     NcclApi* a = h->nccl;
+    {
+        bool equal = true;
+        const int cnt = h->all_slot_end[0] - h->all_slot_begin[0];
+        for (int r = 0; r < h->nranks; ++r)
+            equal = equal && h->all_slot_end[r] - h->all_slot_begin[r] == cnt && h->all_slot_begin[r] == r * cnt;
+        if (equal) {  // one collective instead of nranks broadcasts
+            ncclResult_t rc = a->AllGather(shard, full, cnt, ncclDouble, h->comm, h->st);
+            if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather: ") + a->GetErrorString(rc));
+            return;
+        }
+    }
     a->GroupStart();
     for (int r = 0; r < h->nranks; ++r) {
         const int b = h->all_slot_begin[r], n = h->all_slot_end[r] - b;
@@ -694,6 +754,7 @@ void mapping_slots(aniso_handle* h, const double* f_full, int id, const double* 
     } else
         LAUNCH(h, launch_scale(h->plan.N, f_full, nullptr, h->G.pw, h->G.perm, h->d_f, h->d_q, h->st));
     f = h->d_f;  // unscaled source in reference node order
+    phase_mark(h, "scale");
     run_fmm(h, c, h->d_q, out, subtract ? 2 : 1, s.call, f, x_own);
 }
 
@@ -884,10 +945,12 @@ int aniso_forward_dev(aniso_t* h, const double* x_dev, double* y_dev) {
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     const double* full = x_dev;
+    phase_mark(h, nullptr);
     if (h->nranks > 1) {
         allgather_slots(h, x_dev, h->d_xfull);
         full = h->d_xfull;
     }
+    phase_mark(h, "allgather");
     mapping_slots(h, full, 0, h->d_sig_s, x_dev, y_dev, 1);
     return ANISO_OK;
     API_END

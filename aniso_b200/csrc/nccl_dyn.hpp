@@ -13,6 +13,7 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t);
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
     ncclResult_t (*GroupStart)();
     ncclResult_t (*GroupEnd)();
     const char* (*GetErrorString)(ncclResult_t);
@@ -34,6 +35,7 @@ inline NcclApi* load_nccl() {
     ANISO_NCCL_SYM(CommDestroy, "ncclCommDestroy")
     ANISO_NCCL_SYM(AllReduce, "ncclAllReduce")
     ANISO_NCCL_SYM(Broadcast, "ncclBroadcast")
+    ANISO_NCCL_SYM(AllGather, "ncclAllGather")
     ANISO_NCCL_SYM(GroupStart, "ncclGroupStart")
     ANISO_NCCL_SYM(GroupEnd, "ncclGroupEnd")
     ANISO_NCCL_SYM(GetErrorString, "ncclGetErrorString")

@@ -627,6 +627,19 @@ void partition_leaves(const HostPlan& p, int nranks, std::vector<int>& begin, st
     }
     begin.assign(nranks, 0);
     end.assign(nranks, 0);
+    {
+        // uniform leaves that divide evenly: equal shares (the per-leaf cost differs only along the domain boundary), so
+        // that every rank owns the same number of slots and the per-matvec exchange is one ncclAllGather
+        bool same = nl > 0 && nl % nranks == 0;
+        for (int q = 1; same && q < nl; ++q) same = p.nodes[p.leaves[q]].npts == p.nodes[p.leaves[0]].npts;
+        if (same) {
+            for (int rk = 0; rk < nranks; ++rk) {
+                begin[rk] = rk * (nl / nranks);
+                end[rk] = (rk + 1) * (nl / nranks);
+            }
+            return;
+        }
+    }
     int k = 0;
     double acc = 0;
     for (int rk = 0; rk < nranks; ++rk) {
