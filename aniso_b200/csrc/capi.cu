@@ -304,8 +304,10 @@ void ensure_device(aniso_handle* h) {
     S.sz = p.sz; S.deg = p.deg; S.c2 = p.c2; S.h = p.dx;  // cell edge k sits at k*dx (KernelFactory.cpp:71-72: k / (1/dx))
     S.chat = h->d_chat; S.glx = upload(h, p.glx); S.glw = upload(h, p.glw);
     if (p.deg == 1 && !getenv("ANISO_CELL_WALK")) {  // line-integral tables of the deg-1 fast path, filled by setCoeff
-        S.ty = dalloc<double2>(h, N);
-        S.tx = dalloc<double2>(h, N);
+        S.ty = dalloc<double2>(h, (size_t)N + 1);  // + 1: see magic_floor_inner
+        S.tx = dalloc<double2>(h, (size_t)N + 1);
+        CK(cudaMemsetAsync(const_cast<double2*>(S.ty), 0, sizeof(double2) * ((size_t)N + 1), h->st));
+        CK(cudaMemsetAsync(const_cast<double2*>(S.tx), 0, sizeof(double2) * ((size_t)N + 1), h->st));
     }
     // work space
     h->d_f = dalloc<double>(h, N); h->d_q = dalloc<double>(h, N); h->d_pot = dalloc<double>(h, N);

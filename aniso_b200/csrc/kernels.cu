@@ -125,6 +125,15 @@ __device__ __forceinline__ double magic_floor(double v, double szd, double top, 
     return t - MAGIC;
 }
 
+// crossing points lie between the two (clamped) end points: no clamp needed (the tables carry one entry of padding for the
+// one-ulp case v == 1)
+__device__ __forceinline__ double magic_floor_inner(double v, double szd, int& j) {
+    const double MAGIC = 6755399441055744.0;
+    const double t = fma(v, szd, -0.5) + MAGIC;
+    j = __double2loint(t);
+    return t - MAGIC;
+}
+
 __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0, double y0, double x1, double y1, double len) {
     const double ddx = x1 - x0, ddy = y1 - y0;
     const bool steep = fabs(ddy) >= fabs(ddx);
@@ -140,7 +149,7 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
     const double2 e0 = __ldg(tab + (size_t)c0 * sz + j0), e1 = __ldg(tab + (size_t)c1 * sz + j1);
     double acc = (e1.x - e0.x) + (fma(e1.y, fma(-jd1, h, v1), -e0.y * fma(-jd0, h, v0)));
     if (c0 != c1) {
-        const double slope = dv / du;
+        const double slope = dv * __drcp_rn(du);  // crossing positions tolerate the extra ulp
         const int sgn = c1 > c0 ? 1 : -1, ncross = abs(c1 - c0);
         double bd = (double)(c1 > c0 ? c0 + 1 : c0);
         const double sd = (double)sgn;
@@ -151,7 +160,7 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
         for (; k + 2 <= ncross; k += 2) {  // two crossings per trip: four independent table reads in flight
             const double vb0 = fma(fma(bd, h, -u0), slope, v0), vb1 = fma(fma(bd + sd, h, -u0), slope, v0);
             int ja, jb;
-            const double jda = magic_floor(vb0, szd, top, ja), jdb = magic_floor(vb1, szd, top, jb);
+            const double jda = magic_floor_inner(vb0, szd, ja), jdb = magic_floor_inner(vb1, szd, jb);
             const double2 a0 = __ldg(row + ja), a1 = __ldg(row + rstep + ja);
             const double2 b0 = __ldg(row + rstep + jb), b1 = __ldg(row + 2 * rstep + jb);
             acc = acc + ((a0.x - a1.x) + (a0.y - a1.y) * fma(-jda, h, vb0));
@@ -162,13 +171,13 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
         if (k < ncross) {
             const double vb0 = fma(fma(bd, h, -u0), slope, v0);
             int ja;
-            const double jda = magic_floor(vb0, szd, top, ja);
+            const double jda = magic_floor_inner(vb0, szd, ja);
             const double2 a0 = __ldg(row + ja), a1 = __ldg(row + rstep + ja);
             acc = acc + ((a0.x - a1.x) + (a0.y - a1.y) * fma(-jda, h, vb0));
         }
         acc += acc2;
     }
-    return acc * (len / dv);
+    return acc * (len * __drcp_rn(dv));
 }
 
 // Kernel family of makeKernels (KernelFactory.cpp:240-267): a = source, b = target (Q8).
@@ -190,8 +199,15 @@ __device__ __forceinline__ double kernel_eval_t(const SigmaGrid& S, int id, int 
     const double ddx = ax - bx, ddy = ay - by;
     const double d2 = ddx * ddx + ddy * ddy;
     if (d2 == 0.0) return ((part & PART_IMAG) && id == 0) ? sigma_eval(S, ax, ay) : 0.0;
-    const double dist = sqrt(d2);
-    const double inv = 1.0 / dist;
+    double dist, inv;
+    if (D1) {  // rsqrt + one Newton step on the product (<= 1 ulp from the IEEE pair, far inside the 1e-10 gate)
+        inv = rsqrt(d2);
+        dist = d2 * inv;
+        inv = fma(fma(-dist, inv, 1.0), inv, inv);
+    } else {
+        dist = sqrt(d2);
+        inv = 1.0 / dist;
+    }
     const double ck = id == 0 ? 1.0 : cos_k_theta(id, ddx * inv, ddy * inv);
     if (part == PART_REAL) return ck * inv;
     const double tau = D1 ? line_integral_d1(S, ax, ay, bx, by, dist) : line_integral(S, ax, ay, bx, by);
@@ -207,21 +223,22 @@ __device__ double kernel_eval(const SigmaGrid& S, int id, int part, double ax, d
 // K1/K2 evaluator.  One CTA per operator block; threads stride over the block column-major in the target
 // index so the rays of one warp join neighbouring points of the same two boxes (similar step counts).
 // ------------------------------------------------------------------------------------------------
-template <bool D1>
+// NR > 0: every block is NR x NR (index arithmetic by shifts)
+template <bool D1, int NR>
 __global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, DevTree T, DevGeom G, SigmaGrid S, int id, int part,
                                                                       int cheb, double* __restrict__ A) {
     const int e = blockIdx.x;
     const int tn = m.tgt_node[e], sn = m.src_node[e];
-    const int np = T.np;
+    const int np = NR == 16 ? 4 : T.np;
     int nrow, ncol, toff = 0, soff = 0;
     double tcx = 0, tcy = 0, trx = 0, try_ = 0, scx = 0, scy = 0, srx = 0, sry = 0;
     if (cheb) {
-        nrow = ncol = T.r;
+        nrow = ncol = NR ? NR : T.r;
         tcx = T.cx[tn]; tcy = T.cy[tn]; trx = T.rx[tn]; try_ = T.ry[tn];
         scx = T.cx[sn]; scy = T.cy[sn]; srx = T.rx[sn]; sry = T.ry[sn];
     } else {
-        nrow = T.npts[tn];
-        ncol = T.npts[sn];
+        nrow = NR ? NR : T.npts[tn];
+        ncol = NR ? NR : T.npts[sn];
         toff = T.pt_off[tn];
         soff = T.pt_off[sn];
     }
@@ -251,8 +268,9 @@ void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const Sigm
     int threads = 256;
     if (cheb && T.r <= 8) threads = 64;
     else if (cheb && T.r <= 11) threads = 128;
-    if (S.ty) fill_blocks_kernel<true><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
-    else fill_blocks_kernel<false><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    if (S.ty && m.uniform_block == 16) fill_blocks_kernel<true, 16><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    else if (S.ty) fill_blocks_kernel<true, 0><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    else fill_blocks_kernel<false, 0><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
 }
 
 __global__ void probe_line_integral_kernel(SigmaGrid S, int n, const double* __restrict__ p, double* __restrict__ out) {

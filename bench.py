@@ -32,6 +32,9 @@ import cases  # noqa: E402
 METRIC = "fmm_matvec_points_per_s"
 UNIT = "points/s"
 NP_ORDER, SING_RULE, G_ANISO, MAX_LEVEL = 4, 10, 0.9, 20
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the M2L stream kernel, from the committed `ncu --set full`
+# capture profiles/r01_final_ncu_raw.csv (cannot be measured live); keyed by (sz, n_gpus)
+NCU_TRAFFIC = {(1024, 1): 2403305000 + 115160000}
 
 
 def workload_name(sz):
@@ -303,7 +306,7 @@ def run_ours(args):
     m2l_alg = ab["m2l"] + 8 * r * tr["nodes"]  # stored blocks + scratch rows written + multipoles read
     peak, peak_src = measured_peak()
     roof = {"bound": "hbm", "kernel": "bsr_apply_sym_kernel<16> (M2L stream over the V/X blocks, symmetric storage)", "achieved": m2l_alg / (m2l_ms * 1e-3) / 1e9,
-            "peak": peak, "unit": "GB/s", "frac": m2l_alg / (m2l_ms * 1e-3) / 1e9 / peak, "traffic": None,
+            "peak": peak, "unit": "GB/s", "frac": m2l_alg / (m2l_ms * 1e-3) / 1e9 / peak, "traffic": NCU_TRAFFIC.get((sz, world)),
             "peak_source": peak_src, "algorithmic_bytes_per_launch": m2l_alg, "ms_per_launch": m2l_ms,
             "p2p_stream": {"algorithmic_bytes": ab["p2p"] + 8 * n, "ms_per_launch": p2p_ms,
                            "achieved": (ab["p2p"] + 8 * n) / (p2p_ms * 1e-3) / 1e9}}
