@@ -194,3 +194,55 @@ def test_large_properties(cfg):
     a.setCoeff(ss, st)  # invalidates and rebuilds the caches: same operator
     assert rel(a.mapping(f2, 0), y2) < 1e-14
     a.delete()
+
+
+PLAIN = {"ANISO_NO_SYM": "1", "ANISO_NO_SUBTREE": "1", "ANISO_NO_OVERLAP": "1", "ANISO_CELL_WALK": "1"}
+
+
+@pytest.mark.parametrize("cfg,kid", [
+    ((1024, 1, 1, 0.9, 10, 4, 20, "layers"), 0),   # C5: N = 2^20
+    ((512, 1, 1, 0.9, 10, 8, 20, "hetero"), 0),    # C4, np 8: 64 x 64 blocks, 64-point leaves
+    ((512, 1, 1, 0.9, 10, 5, 20, "hetero"), 0),    # C4, np 5 and 7: general-shape stream kernel + sub-tree passes
+    ((512, 1, 1, 0.9, 10, 7, 20, "hetero"), 0),
+    ((256, 1, 5, 0.9, 10, 6, 20, "hetero"), 3),    # C3: N = 2^16, np 6, a higher kernel id (odd: sign of the transposed blocks)
+    ((128, 1, 5, 0.5, 10, 4, 20, "const"), 8),     # C2, highest kernel id
+])
+def test_fast_paths_match_plain_paths_at_baseline_sizes(cfg, kid, monkeypatch):
+    """At the BASELINE sizes the reference cannot be run inside a test, so the optimised path (symmetric operator storage,
+    table line integral, sub-tree passes, two streams) is compared with the plain path of the same library (every block
+    stored, cell-walk line integral, level-by-level passes, one stream), which is the one validated against the reference
+    fixtures at the small sizes.  Same handle arguments, same inputs; only rounding may differ."""
+    from aniso_b200 import Aniso
+
+    sz, deg, K, g, sr, np_, ml, kind = cfg
+
+    def run(env):
+        for k in PLAIN:
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        a = Aniso(sz, deg, K, g, sr, np_, ml)
+        x, y, w = a.nodes()
+        ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+        a.setCoeff(ss, st)
+        a.cache(kid)
+        n = a.numberOfNodes
+        f = cases.random_source(n, 9) * cases.gaussian_source(x, y) + 0.1 * cases.tilted_source(x, y)
+        out = a.mapping(f, kid)
+        pin = a.pinned_empty(n)
+        pin[:] = f
+        out_pinned = a.mapping(pin, kid)  # page-locked input: direct DMA path
+        res = None
+        if kid == 0:
+            b = a.mapping(cases.gaussian_source(x, y), 0)
+            res = a.gmres(b)
+        a.delete()
+        return out, out_pinned, res
+
+    fast, fast_pinned, gm_fast = run({})
+    plain, _, gm_plain = run(PLAIN)
+    assert np.array_equal(fast, fast_pinned)
+    assert rel(fast, plain) < 1e-12
+    if gm_fast is not None:
+        assert gm_fast[1] == gm_plain[1] == 0 and gm_fast[2] == gm_plain[2]
+        assert rel(gm_fast[0], gm_plain[0]) < 1e-9
