@@ -266,6 +266,9 @@ void ensure_device(aniso_handle* h) {
                 for (int c = 1; c < 4; ++c)
                     if (n.child[c] != n.child[0] + c) throw std::runtime_error("internal: children not consecutive");
         }
+        T.uniform_npts = p.leaves.empty() ? 0 : p.nodes[p.leaves[0]].npts;
+        for (size_t k = 0; k < p.leaves.size(); ++k)
+            if (p.nodes[p.leaves[k]].npts != T.uniform_npts || p.nodes[p.leaves[k]].pt_off != (int)k * T.uniform_npts) T.uniform_npts = 0;
         T.leaf_info = upload(h, info); T.child0 = upload(h, child0);
         T.level_ptr = upload(h, p.level_ptr);
     }

@@ -47,6 +47,7 @@ struct DevTree {
     double* RT = nullptr;                                       // R transposed per child: [4][b][a]
     int* leaves = nullptr;                                      // all non-empty leaves (DFS order)
     int nleaves = 0, max_leaf = 0;
+    int uniform_npts = 0;                                       // > 0: every leaf holds this many points (slot = leaf * npts + k)
     int* level_ptr = nullptr;                                   // nodes of level L: [level_ptr[L], level_ptr[L+1])
     int4* leaf_info = nullptr;                                  // per leaf: node id, pt_off, npts, 0
     int* child0 = nullptr;                                      // first child (children are consecutive) or -1

@@ -68,6 +68,16 @@ __global__ void __launch_bounds__(256) up_leaf_kernel(DevTree T, DevGeom G, cons
     double* __restrict__ mult = sm;                                   // [lvoff(D+1)][r]
     double* __restrict__ ws = sm + (size_t)lvoff(D + 1) * r + (size_t)grp * LANES * stride;
     double* __restrict__ Rs = sm + (size_t)lvoff(D + 1) * r + (size_t)ngrp * LANES * stride;
+    const int n0 = T.uniform_npts;
+    // the point data of the first round is requested before the table loads and the barrier (uniform leaves: its address
+    // follows from the leaf index), so the DRAM round trip overlaps them
+    double pf_x = 0, pf_y = 0, pf_q = 0;
+    if (n0 && grp < nl && lane < n0) {
+        const int off = (m * nl + grp) * n0 + lane;
+        pf_x = G.sxn[off];
+        pf_y = G.syn[off];
+        pf_q = q[off];
+    }
     for (int i = threadIdx.x; i < np * np; i += blockDim.x) tn[i] = T.tnode[i];
     if (SMEM_R)
         for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.R + i);
@@ -76,8 +86,15 @@ __global__ void __launch_bounds__(256) up_leaf_kernel(DevTree T, DevGeom G, cons
     for (int j0 = 0; j0 < nl; j0 += ngrp) {
         const int j = j0 + grp;  // nl and ngrp are powers of two: a group is either fully inside or fully outside
         if (j >= nl) break;
-        const int4 info = T.leaf_info[(size_t)m * nl + j];  // id, pt_off, npts
-        const int id = info.x, off = info.y, n = info.z;
+        int id, off, n;
+        if (n0) {
+            id = lvoff(Ls + D) + m * nl + j;
+            off = (m * nl + j) * n0;
+            n = n0;
+        } else {
+            const int4 info = T.leaf_info[(size_t)m * nl + j];  // id, pt_off, npts
+            id = info.x; off = info.y; n = info.z;
+        }
         double acc[UMAX];
 #pragma unroll
         for (int u = 0; u < UMAX; ++u) acc[u] = 0;
@@ -85,12 +102,13 @@ __global__ void __launch_bounds__(256) up_leaf_kernel(DevTree T, DevGeom G, cons
             const int cnt = min(LANES, n - k0);
             if (lane < cnt) {
                 double w[2 * (NP ? NP : NP_MAX)];
-                cheb_weights<NP>(tn, np, G.sxn[off + k0 + lane], w);
-                cheb_weights<NP>(tn, np, G.syn[off + k0 + lane], w + np);
+                const bool pf = n0 && j0 == 0 && k0 == 0;
+                cheb_weights<NP>(tn, np, pf ? pf_x : G.sxn[off + k0 + lane], w);
+                cheb_weights<NP>(tn, np, pf ? pf_y : G.syn[off + k0 + lane], w + np);
 #pragma unroll
                 for (int mm = 0; mm < 2 * (NP ? NP : NP_MAX); ++mm)
                     if (mm < 2 * np) ws[lane * stride + mm] = w[mm];
-                ws[lane * stride + 2 * np] = q[off + k0 + lane];
+                ws[lane * stride + 2 * np] = pf ? pf_q : q[off + k0 + lane];
             }
             __syncwarp(mask);
 #pragma unroll
@@ -147,18 +165,29 @@ __device__ __forceinline__ double fold_node(const DevCSR& m, int node, int t) {
     return s;
 }
 
-// L2L inside shared memory: levels 0 .. D of the sub-tree rooted at node (Ls, m).  top: the root has no parent
-// contribution (first level with M2L lists), its local expansion is its own M2L sum.  FOLD: M2L sums are still spread
-// over scratch rows (symmetric storage), otherwise they sit in mpot.
-template <bool SMEM_R, bool FOLD>
-__device__ __forceinline__ void subtree_l2l(const DevTree& T, const DevCSR& m2l, int Ls, int m, int D, bool top, bool write_last,
-                                            double* __restrict__ sm, const double* __restrict__ RTs, double* __restrict__ mpot) {
-    const int r = T.r;
-    {
-        const int root = lvoff(Ls) + m;
-        for (int a = threadIdx.x; a < r; a += blockDim.x)
-            sm[a] = (FOLD && top) ? fold_node(m2l, root, a) : mpot[(size_t)root * r + a];
+// L2L inside shared memory: levels 0 .. D of the sub-tree rooted at node (Ls, m), in two steps.
+// subtree_own: every node's own contribution goes to sm[(lvoff(d) + g)*r + a] - for the root the finished local
+// expansion written by the chunk above (or, top: its own M2L sum, the first level with M2L lists has no parent term), for
+// the others their M2L sum.  FOLD: M2L sums are still spread over scratch rows (symmetric storage), otherwise they sit
+// in mpot.  None of these loads depends on another node, so they are all in flight together (no barrier inside).
+template <bool FOLD>
+__device__ __forceinline__ void subtree_own(const DevTree& T, const DevCSR& m2l, int Ls, int m, int D, bool top,
+                                            double* __restrict__ sm, const double* __restrict__ mpot) {
+    const int r = T.r, total = lvoff(D + 1) * r;
+    for (int o = threadIdx.x; o < total; o += blockDim.x) {
+        const int q = o / r, a = o - q * r;
+        int d = 0;
+        while (lvoff(d + 1) <= q) ++d;
+        const int id = lvoff(Ls + d) + (m << (2 * d)) + (q - lvoff(d));
+        sm[o] = (FOLD && (d > 0 || top)) ? fold_node(m2l, id, a) : mpot[(size_t)id * r + a];
     }
+}
+// subtree_l2l: child += R[index] * parent level by level (bbfmm.h:1070-1071), one block barrier per level; starts with
+// the barrier that publishes subtree_own's values.
+template <bool SMEM_R>
+__device__ __forceinline__ void subtree_l2l(const DevTree& T, int Ls, int m, int D, bool write_last, double* __restrict__ sm,
+                                            const double* __restrict__ RTs, double* __restrict__ mpot) {
+    const int r = T.r;
     __syncthreads();
     for (int d = 1; d <= D; ++d) {
         const int nb = 1 << (2 * d);
@@ -167,8 +196,6 @@ __device__ __forceinline__ void subtree_l2l(const DevTree& T, const DevCSR& m2l,
         const int first = lvoff(Ls + d) + (m << (2 * d));
         for (int o = threadIdx.x; o < nb * r; o += blockDim.x) {
             const int g = o / r, a = o - g * r;
-            const int id = first + g;
-            const double own = FOLD ? fold_node(m2l, id, a) : mpot[(size_t)id * r + a];
             const size_t roff = (size_t)(g & 3) * r * r + a;  // children are consecutive: sibling position = child index
             const double* __restrict__ RT = (SMEM_R ? RTs : T.RT) + roff;
             const double* __restrict__ src = pars + (size_t)(g >> 2) * r;
@@ -180,9 +207,9 @@ __device__ __forceinline__ void subtree_l2l(const DevTree& T, const DevCSR& m2l,
                 a1 = fma(SMEM_R ? RT[(size_t)(b + 1) * r] : __ldg(RT + (size_t)(b + 1) * r), src[b + 1], a1);
             }
             if (b < r) a0 = fma(SMEM_R ? RT[(size_t)b * r] : __ldg(RT + (size_t)b * r), src[b], a0);
-            const double v = own + (a0 + a1);
+            const double v = mine[o] + (a0 + a1);
             mine[o] = v;
-            if (write_last && d == D) mpot[(size_t)id * r + a] = v;
+            if (write_last && d == D) mpot[(size_t)(first + g) * r + a] = v;
         }
         __syncthreads();
     }
@@ -195,7 +222,8 @@ __global__ void __launch_bounds__(256) down_mid_kernel(DevTree T, DevCSR m2l, do
     double* __restrict__ RTs = sm + (size_t)lvoff(D + 1) * r;
     if (SMEM_R)
         for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) RTs[i] = __ldg(T.RT + i);
-    subtree_l2l<SMEM_R, FOLD>(T, m2l, Ls, blockIdx.x, D, top != 0, true, sm, RTs, mpot);  // starts with a barrier
+    subtree_own<FOLD>(T, m2l, Ls, blockIdx.x, D, top != 0, sm, mpot);
+    subtree_l2l<SMEM_R>(T, Ls, blockIdx.x, D, true, sm, RTs, mpot);
 }
 
 // L2L down to the leaves of one sub-tree, then per point of the sub-tree (one contiguous slot range)
@@ -213,7 +241,9 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
     __shared__ double tn[NP_MAX * NP_MAX];
     const int np = NP ? NP : T.np, r = np * np, m = blockIdx.x;
     const int root = lvoff(Ls) + m;
-    const int p_begin = max(T.pt_off[root], slot0), p_end = min(T.pt_off[root] + T.npts[root], slot0 + n);
+    const int n0 = T.uniform_npts;  // > 0: slot ranges follow from the leaf index, no table look-ups
+    const int rb = n0 ? (m << (2 * D)) * n0 : T.pt_off[root], rn = n0 ? n0 << (2 * D) : T.npts[root];
+    const int p_begin = max(rb, slot0), p_end = min(rb + rn, slot0 + n);
     if (p_begin >= p_end) return;  // no owned target below this root (multi-GPU partition)
     double* __restrict__ RTs = sm + (size_t)lvoff(D + 1) * r;
     for (int i = threadIdx.x; i < np * np; i += blockDim.x) tn[i] = T.tnode[i];
@@ -246,9 +276,9 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
                 for (int cs = 0; cs < 9; ++cs) P.corr = fma(cv[cs], fv[cs], P.corr);
             }
         }
-        const int id = leaf_of_slot[p];
+        const int id = n0 ? leaf0 + (p - rb) / n0 : leaf_of_slot[p];
         P.lo = id - leaf0;
-        P.near = fold_p2p ? fold_node(p2p, id, p - T.pt_off[id]) : pot[p];
+        P.near = fold_p2p ? fold_node(p2p, id, n0 ? (p - rb) % n0 : p - T.pt_off[id]) : pot[p];
         cheb_weights<NP>(tn, np, G.sxn[p], P.wx);
         cheb_weights<NP>(tn, np, G.syn[p], P.wy);
     };
@@ -276,8 +306,9 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
     __syncthreads();  // tn
     const int p_first = p_begin + threadIdx.x;
     Pre P0;
+    subtree_own<FOLD>(T, m2l, Ls, m, D, top != 0, sm, mpot);
     if (p_first < p_end) pre(p_first, P0);
-    subtree_l2l<SMEM_R, FOLD>(T, m2l, Ls, m, D, top != 0, false, sm, RTs, mpot);
+    subtree_l2l<SMEM_R>(T, Ls, m, D, false, sm, RTs, mpot);
     if (p_first < p_end) post(p_first, P0);
     for (int p = p_first + blockDim.x; p < p_end; p += blockDim.x) {
         Pre P;
