@@ -79,6 +79,9 @@ struct aniso_handle {
     double *d_f = nullptr, *d_q = nullptr, *d_mcharge = nullptr, *d_mpot = nullptr, *d_pot = nullptr;
     double *d_fmm = nullptr, *d_corr = nullptr, *d_a = nullptr, *d_b = nullptr, *d_xfull = nullptr, *d_stage = nullptr;
     double *d_blk_full = nullptr, *d_blk_tmp = nullptr;  // block operator work space
+    double* gm_buf = nullptr;   // Krylov work space, kept between solves ((m+3) vectors + CGS2 partials)
+    size_t gm_cap = 0;
+    double* pinned_small = nullptr;  // 2048 doubles: Hessenberg column read-back
     double* pinned = nullptr;  // 2N doubles
     std::map<std::pair<int, int>, OperatorCache> ops;
     std::map<int, StencilCache> stencils;
@@ -447,6 +450,7 @@ int aniso_destroy(aniso_t* h) {
         if (h->comm && h->nccl) h->nccl->CommDestroy(h->comm);
         for (void* p : h->allocs) cudaFree(p);
         if (h->pinned) cudaFreeHost(h->pinned);
+        if (h->pinned_small) cudaFreeHost(h->pinned_small);
         cudaStreamSynchronize(h->st_bulk);
         for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join})
             if (e) cudaEventDestroy(e);
@@ -1149,17 +1153,31 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
                int hist_cap) {
     const int ldh = m + 1;
     GmresWork g{h, n, m, nullptr, nullptr, nullptr};
-    g.w = dalloc<double>(h, n);
-    g.r = dalloc<double>(h, n);
-    g.V = dalloc<double>(h, (size_t)(m + 1) * n);
+    {
+        // one allocation, kept in the handle between solves (680 MB at C5, m = 80: cudaMalloc/cudaFree of that size cost
+        // milliseconds, a visible share of a 25 ms solve)
+        const size_t need = (size_t)(m + 3) * n + (size_t)(m + 1) * h->dot.blocks;
+        if (h->gm_cap < need) {
+            dfree(h, h->gm_buf);
+            h->gm_buf = nullptr;
+            h->gm_cap = 0;
+            h->gm_buf = dalloc<double>(h, need);
+            h->gm_cap = need;
+        }
+        if (!h->pinned_small) CK(cudaMallocHost(&h->pinned_small, 2048 * sizeof(double)));
+    }
+    g.w = h->gm_buf;
+    g.r = g.w + n;
+    g.V = g.r + n;
     double* dh = h->d_scal;  // device Hessenberg column, m+2 entries (+ m+2 for the second CGS2 pass)
     if (2 * (m + 2) > 1024) throw std::invalid_argument("restart length m too large (max 510)");
     // orthogonalisation: the reference's modified Gram-Schmidt on one GPU; CGS2 when every dot costs an all-reduce
     // (ANISO_GMRES_ORTHO=mgs|cgs2 overrides)
     const char* oenv = getenv("ANISO_GMRES_ORTHO");
     const bool cgs2 = oenv ? std::string(oenv) == "cgs2" : h->nranks > 1;
-    double* md_partial = cgs2 ? dalloc<double>(h, (size_t)(m + 1) * h->dot.blocks) : nullptr;
-    std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0), col(2 * m + 4);
+    double* md_partial = g.V + (size_t)(m + 1) * n;
+    double* col = h->pinned_small;
+    std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0);
     int rc = 1, j = 1, i = 0;
     bool done = false;
     double resid = 0;
@@ -1176,7 +1194,7 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
         done = true;
     }
     while (!done && j <= max_iter) {
-        LAUNCH(h, launch_scale_inv_dev(n, dh, g.r, g.v(0), h->st));  // dh[0] still holds beta
+        LAUNCH(h, launch_scale_inv_dev(n, dh, g.r, g.v(0), 0, h->st));  // dh[0] still holds beta
         std::fill(s.begin(), s.end(), 0.0);
         s[0] = beta;
         for (i = 0; i < m && j <= max_iter; ++i, ++j) {
@@ -1205,11 +1223,12 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
                 ++h->launches;
                 allreduce_scalars(h, dh + i + 1, 1);
             }
-            LAUNCH(h, launch_sqrt1(dh + i + 1, h->st));
-            LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), h->st));
-            CK(cudaMemcpyAsync(col.data(), dh, sizeof(double) * (cgs2 ? 2 * m + 4 : i + 2), cudaMemcpyDeviceToHost, h->st));
+            // dh[i+1] = w . w: the square root is taken inside the scaling kernel and, for H, on the host
+            LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), 1, h->st));
+            CK(cudaMemcpyAsync(col, dh, sizeof(double) * (cgs2 ? 2 * m + 4 : i + 2), cudaMemcpyDeviceToHost, h->st));
             CK(cudaStreamSynchronize(h->st));
-            for (int k = 0; k <= i + 1; ++k) H[k + (size_t)i * ldh] = col[k];
+            for (int k = 0; k <= i; ++k) H[k + (size_t)i * ldh] = col[k];
+            H[i + 1 + (size_t)i * ldh] = std::sqrt(col[i + 1]);
             if (cgs2)
                 for (int k = 0; k <= i; ++k) H[k + (size_t)i * ldh] += col[m + 2 + k];
             for (int k = 0; k < i; ++k) apply_rotation(H[k + (size_t)i * ldh], H[k + 1 + (size_t)i * ldh], cs[k], sn[k]);
@@ -1236,10 +1255,6 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     }
     if (hist && *iters < hist_cap) hist[*iters] = resid;
     CK(cudaStreamSynchronize(h->st));
-    dfree(h, g.w);
-    dfree(h, g.r);
-    dfree(h, g.V);
-    dfree(h, md_partial);
     return rc;
 }
 

@@ -1,6 +1,8 @@
 // K11: device-resident BLAS-1 pieces of the GMRES Arnoldi step (gmres.cpp:115-122, 12-24).  All scalars that
 // feed the next kernel (Hessenberg entries, norms) stay in device memory, so one Arnoldi step needs a single
 // host synchronisation (to read the new Hessenberg column for the Givens update).
+#include <cstdint>
+
 #include "device.cuh"
 
 namespace an {
@@ -48,6 +50,7 @@ __global__ void __launch_bounds__(kDotThreads) dot_kernel(int n, const double* _
 //   w -= h[0] * v          (h: the projection computed by the previous dot, still in device memory)
 //   result = w . u         (u = the next basis vector, or u == nullptr: w . w for the final norm)
 // Same deterministic two-stage reduction as dot_kernel.
+template <bool VEC>
 __global__ void __launch_bounds__(kDotThreads) axpy_dot_kernel(int n, const double* __restrict__ h, const double* __restrict__ v,
                                                                double* __restrict__ w, const double* __restrict__ u,
                                                                double* __restrict__ result, double* __restrict__ partial,
@@ -56,6 +59,34 @@ __global__ void __launch_bounds__(kDotThreads) axpy_dot_kernel(int n, const doub
     __shared__ bool last;
     const double alpha = -*h;
     double acc = 0;
+    if (VEC) {  // n even, 16-byte aligned vectors: two double2 per thread and trip in flight
+        const int n2 = n >> 1, stride = gridDim.x * blockDim.x;
+        const double2* __restrict__ v2 = reinterpret_cast<const double2*>(v);
+        const double2* __restrict__ u2 = reinterpret_cast<const double2*>(u);
+        double2* __restrict__ w2 = reinterpret_cast<double2*>(w);
+        double acc1 = 0;
+        int i = blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + stride < n2; i += 2 * stride) {
+            const double2 va = v2[i], vb = v2[i + stride];
+            double2 wa = w2[i], wb = w2[i + stride];
+            wa.x = fma(alpha, va.x, wa.x); wa.y = fma(alpha, va.y, wa.y);
+            wb.x = fma(alpha, vb.x, wb.x); wb.y = fma(alpha, vb.y, wb.y);
+            const double2 ua = u ? u2[i] : wa, ub = u ? u2[i + stride] : wb;
+            w2[i] = wa;
+            w2[i + stride] = wb;
+            acc = fma(wa.x, ua.x, acc); acc = fma(wa.y, ua.y, acc);
+            acc1 = fma(wb.x, ub.x, acc1); acc1 = fma(wb.y, ub.y, acc1);
+        }
+        if (i < n2) {
+            const double2 va = v2[i];
+            double2 wa = w2[i];
+            wa.x = fma(alpha, va.x, wa.x); wa.y = fma(alpha, va.y, wa.y);
+            const double2 ua = u ? u2[i] : wa;
+            w2[i] = wa;
+            acc = fma(wa.x, ua.x, acc); acc = fma(wa.y, ua.y, acc);
+        }
+        acc += acc1;
+    } else
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const double wi = fma(alpha, v[i], w[i]);
         w[i] = wi;
@@ -93,7 +124,9 @@ void launch_axpy_dot(int n, const double* h, const double* v, double* w, const d
     int blocks = (n + kDotThreads * 4 - 1) / (kDotThreads * 4);
     if (blocks < 1) blocks = 1;
     if (blocks > wk.blocks) blocks = wk.blocks;
-    axpy_dot_kernel<<<blocks, kDotThreads, 0, st>>>(n, h, v, w, u, result, wk.partial, wk.counter);
+    const bool vec = (n & 1) == 0 && ((reinterpret_cast<uintptr_t>(v) | reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(u)) & 15) == 0;
+    if (vec) axpy_dot_kernel<true><<<blocks, kDotThreads, 0, st>>>(n, h, v, w, u, result, wk.partial, wk.counter);
+    else axpy_dot_kernel<false><<<blocks, kDotThreads, 0, st>>>(n, h, v, w, u, result, wk.partial, wk.counter);
 }
 
 void launch_dot(int n, const double* a, const double* b, double* result, DotWork& wk, cudaStream_t st) {
@@ -119,13 +152,14 @@ void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t s
     if (n) axpy_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, alpha, x, y);
 }
 
-__global__ void scale_inv_dev_kernel(int n, const double* __restrict__ norm, const double* __restrict__ in, double* __restrict__ out) {
-    const double s = 1.0 / *norm;  // gmres.cpp:122 / 100: dscal(1.0 / h, v)
+__global__ void scale_inv_dev_kernel(int n, const double* __restrict__ norm, const double* __restrict__ in, double* __restrict__ out,
+                                     int squared) {
+    const double s = 1.0 / (squared ? sqrt(*norm) : *norm);  // gmres.cpp:122 / 100: dscal(1.0 / h, v)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = in[i] * s;
 }
-void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, cudaStream_t st) {
-    if (n) scale_inv_dev_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, norm, in, out);
+void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, int squared, cudaStream_t st) {
+    if (n) scale_inv_dev_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, norm, in, out, squared);
 }
 
 __global__ void sqrt1_kernel(double* v) { *v = sqrt(*v); }
@@ -168,12 +202,18 @@ __global__ void __launch_bounds__(kDotThreads) multi_dot_kernel(int n, int nv, c
         partial[(size_t)(k0 + threadIdx.x) * gridDim.x + blockIdx.x] = s;
     }
 }
-// out[k] = sum_b partial[k][b] in a fixed order (one warp per k)
+// out[k] = sum_b partial[k][b] in a fixed order (one warp per k); loads in independent batches of eight
 __global__ void reduce_partials_kernel(int nv, int nb, const double* __restrict__ partial, double* __restrict__ out) {
     const int k = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (k >= nv) return;
+    const double* __restrict__ row = partial + (size_t)k * nb;
     double s = 0;
-    for (int b = lane; b < nb; b += 32) s += partial[(size_t)k * nb + b];
+    for (int b = lane; b < nb; b += 32 * 8) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = b + 32 * u < nb ? row[b + 32 * u] : 0.0;
+        s += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+    }
     for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
     if (lane == 0) out[k] = s;
 }

@@ -321,13 +321,20 @@ def run_ours(args):
 
     it = ctypes.c_int(0)
     hist = np.zeros(402)
-    l1 = a.launch_count()
-    t0 = time.perf_counter()
-    rc = _lib.check(L.aniso_gmres_dev(a.h, b_own.data_ptr(), xs.data_ptr(), 80, 400, 1e-12, ctypes.byref(it), hist, hist.size))
-    a.synchronize()
-    barrier()
-    t_gmres = max_over_ranks(time.perf_counter() - t0)
-    gm_launches = a.launch_count() - l1
+    t_first = None
+    for rep in range(2):  # the first solve allocates the Krylov work space (kept in the handle); the second is reported
+        xs.zero_()
+        a.synchronize()
+        barrier()
+        l1 = a.launch_count()
+        t0 = time.perf_counter()
+        rc = _lib.check(L.aniso_gmres_dev(a.h, b_own.data_ptr(), xs.data_ptr(), 80, 400, 1e-12, ctypes.byref(it), hist, hist.size))
+        a.synchronize()
+        barrier()
+        t_gmres = max_over_ranks(time.perf_counter() - t0)
+        gm_launches = a.launch_count() - l1
+        if t_first is None:
+            t_first = t_gmres
 
     line = None
     if rank == 0:
@@ -344,7 +351,7 @@ def run_ours(args):
                           "m2l_fill_ms": m2l_fill_ms, "stencil_ms": ct["stencil_ms"],
                           "m2l_evals_per_s": all_m2l / (m2l_fill_ms * 1e-3) if m2l_fill_ms else None},
                 "gmres": {"rc": int(rc), "iters": int(it.value), "final_resid": float(hist[it.value]), "time_to_solve_s": t_gmres,
-                          "m": 80, "tol": 1e-12, "gpu_launches": int(gm_launches)},
+                          "first_call_s": t_first, "m": 80, "tol": 1e-12, "gpu_launches": int(gm_launches)},
                 "setup_s": t_setup}
         if world == 1 and not args.no_cpu:
             try:
