@@ -498,7 +498,7 @@ static void finish_csr(BlockCSR& b) {
 // Rewrites a uniform-block CSR into symmetric storage (see BlockCSR::symmetric).
 static void symmetrize(BlockCSR& b) {
     const int groups = (int)b.nrow.size(), R = b.uniform_block;
-    if (!groups || (R != 16 && R != 64) || getenv("ANISO_NO_SYM")) return;
+    if (!groups || R < 4 || R > 64 || getenv("ANISO_NO_SYM")) return;  // R = 16, 64: stream.cu bsr_apply_sym_kernel; else symg
     auto key = [](int t, int s) { return ((int64_t)t << 32) | (uint32_t)s; };
     std::unordered_map<int64_t, int> entry_of;  // (tgt, src) -> entry
     entry_of.reserve(b.col_off.size() * 2);

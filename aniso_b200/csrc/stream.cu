@@ -217,8 +217,8 @@ __global__ void __launch_bounds__(256, 4) bsr_apply_sym_kernel(DevCSR m, const d
     }
 }
 
-template <int R>
 __global__ void __launch_bounds__(256) bsr_reduce_kernel(DevCSR m, double* __restrict__ y) {
+    const int R = m.uniform_block;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int g = i / R, t = i - g * R;
     if (g >= m.groups) return;
@@ -231,6 +231,79 @@ __global__ void __launch_bounds__(256) bsr_reduce_kernel(DevCSR m, double* __res
     }
     if (r < r1) s0 += m.scratch[(size_t)r * R + t];
     y[m.row_off[g] + t] = s0 + s1;
+}
+
+// Symmetric storage for any uniform block size R <= 64 (np = 5, 6, 7: R = 25, 36, 49).  One warp per target; lane l
+// owns targets l and l + 32, so a block row (R consecutive doubles) is one or two coalesced 8-byte loads per lane and
+// eight rows are in flight per trip.  Forward product: acc[t] += A[s][t] x_B[s].  Transposed product for the partner:
+// z[s] = sign * sum_t A[s][t] x_A[t]; the eight per-lane partials of a trip are reduced across the warp with a butterfly
+// that halves the live values at each of its first three steps (4 + 2 + 1 + 1 + 1 shuffles instead of 8 x 5).
+// One trip of eight rows [s0, s0+8) of a block (FULL: all eight exist).
+template <int RC, bool FULL>
+__device__ __forceinline__ void symg_trip(const double* __restrict__ rowp, const double* __restrict__ xs, int s0, int R, int lane,
+                                          bool has0, bool has1, double xa0, double xa1, int mr, double sign, uint64_t pol,
+                                          double& acc0, double& acc1, double* __restrict__ scratch) {
+    constexpr bool TWO = RC == 0 || RC > 32;
+    const int Rr = RC ? RC : R;
+    double a0[8], a1[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const bool ok = FULL || s0 + j < Rr;
+        a0[j] = ok && has0 ? ld_stream(rowp + j * Rr, pol) : 0.0;
+        a1[j] = TWO && ok && has1 ? ld_stream(rowp + j * Rr + 32, pol) : 0.0;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const double xv = (FULL || s0 + j < Rr) ? __ldg(xs + j) : 0.0;
+        acc0 = fma(a0[j], xv, acc0);
+        if (TWO) acc1 = fma(a1[j], xv, acc1);
+    }
+    if (mr < 0) return;  // warp-uniform
+    double p[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) p[j] = TWO ? fma(a0[j], xa0, a1[j] * xa1) : a0[j] * xa0;
+    const bool b0 = lane & 1, b1 = lane & 2, b2 = lane & 4;
+    double q[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)  // lane bit 0 keeps rows {4..7} if set, else {0..3}
+        q[j] = (b0 ? p[4 + j] : p[j]) + __shfl_xor_sync(0xffffffffu, b0 ? p[j] : p[4 + j], 1);
+    const double w0 = (b1 ? q[2] : q[0]) + __shfl_xor_sync(0xffffffffu, b1 ? q[0] : q[2], 2);
+    const double w1 = (b1 ? q[3] : q[1]) + __shfl_xor_sync(0xffffffffu, b1 ? q[1] : q[3], 2);
+    double z = (b2 ? w1 : w0) + __shfl_xor_sync(0xffffffffu, b2 ? w0 : w1, 4);
+    z += __shfl_xor_sync(0xffffffffu, z, 8);
+    z += __shfl_xor_sync(0xffffffffu, z, 16);
+    // lane (low three bits b2 b1 b0 as read above) holds row 4*b0 + 2*b1 + b2 of this trip
+    const int row = s0 + (b0 ? 4 : 0) + (b1 ? 2 : 0) + (b2 ? 1 : 0);
+    if (lane < 8 && (FULL || row < Rr)) scratch[(size_t)mr * Rr + row] = sign * z;
+}
+
+template <int RC>  // RC: compile-time block size (25, 36, 49), or 0 = run-time m.uniform_block
+__global__ void __launch_bounds__(256, 3) bsr_apply_symg_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
+                                                                double sign) {
+    const int R = RC ? RC : m.uniform_block;
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (g >= m.groups) return;
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const uint64_t pol = stream_policy();
+    const double* __restrict__ blk = A + (ne ? m.blk_off[e0] : 0) + lane;
+    const int self = m.row_off[g];
+    const bool has0 = lane < R, has1 = lane + 32 < R;
+    const double xa0 = has0 ? __ldg(x + self + lane) : 0.0, xa1 = has1 ? __ldg(x + self + lane + 32) : 0.0;
+    double* __restrict__ scratch = m.scratch;
+    double acc0 = 0, acc1 = 0;
+    const int full = R & ~7;
+    for (int e = 0; e < ne; ++e, blk += R * R) {
+        const int mr = m.mirror_row[e0 + e];
+        const double* __restrict__ xs = x + m.col_off[e0 + e];
+        int s0 = 0;
+        for (; s0 < full; s0 += 8)
+            symg_trip<RC, true>(blk + s0 * R, xs + s0, s0, R, lane, has0, has1, xa0, xa1, mr, sign, pol, acc0, acc1, scratch);
+        if (s0 < R) symg_trip<RC, false>(blk + s0 * R, xs + s0, s0, R, lane, has0, has1, xa0, xa1, mr, sign, pol, acc0, acc1, scratch);
+    }
+    double* __restrict__ out = scratch + (size_t)m.srow_ptr[g] * R;
+    if (has0) out[lane] = acc0;
+    if (has1) out[lane + 32] = acc1;
 }
 
 __global__ void __launch_bounds__(128) bsr_apply_row_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
@@ -278,8 +351,7 @@ __global__ void __launch_bounds__(128) bsr_apply_row_kernel(DevCSR m, const doub
 void launch_bsr_reduce(const DevCSR& m, double* y, cudaStream_t st) {
     if (!m.symmetric || m.groups == 0) return;
     const unsigned rb = ((unsigned)m.groups * m.uniform_block + 255) / 256;
-    if (m.uniform_block == 16) bsr_reduce_kernel<16><<<rb, 256, 0, st>>>(m, y);
-    else bsr_reduce_kernel<64><<<rb, 256, 0, st>>>(m, y);
+    bsr_reduce_kernel<<<rb, 256, 0, st>>>(m, y);
 }
 
 void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, double sign, bool reduce, cudaStream_t st) {
@@ -287,7 +359,11 @@ void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double*
     const unsigned warps_per_cta = 8, ctas = (m.groups + warps_per_cta - 1) / warps_per_cta;
     if (m.symmetric) {
         if (m.uniform_block == 16) bsr_apply_sym_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, sign);
-        else bsr_apply_sym_kernel<64><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else if (m.uniform_block == 64) bsr_apply_sym_kernel<64><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else if (m.uniform_block == 25) bsr_apply_symg_kernel<25><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else if (m.uniform_block == 36) bsr_apply_symg_kernel<36><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else if (m.uniform_block == 49) bsr_apply_symg_kernel<49><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else bsr_apply_symg_kernel<0><<<ctas, 256, 0, st>>>(m, A, x, sign);
         if (reduce) launch_bsr_reduce(m, y, st);
         return;
     }
