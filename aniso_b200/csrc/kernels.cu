@@ -224,41 +224,59 @@ __device__ double kernel_eval(const SigmaGrid& S, int id, int part, double ax, d
 // index so the rays of one warp join neighbouring points of the same two boxes (similar step counts).
 // ------------------------------------------------------------------------------------------------
 // NR > 0: every block is NR x NR (index arithmetic by shifts)
+// A CTA evaluates EPC consecutive blocks.  The metadata of all of them (entry -> nodes -> box geometry or point offsets,
+// a chain of dependent global loads) is fetched once by the first EPC threads and parked in shared memory, so the chain
+// is paid once per EPC * 256 interactions instead of once per block.
+static constexpr int EPC = 8;
 template <bool D1, int NR>
 __global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, DevTree T, DevGeom G, SigmaGrid S, int id, int part,
                                                                       int cheb, double* __restrict__ A) {
-    const int e = blockIdx.x;
-    const int tn = m.tgt_node[e], sn = m.src_node[e];
+    __shared__ double s_geo[EPC][8];  // cheb: target cx, cy, rx, ry, source cx, cy, rx, ry
+    __shared__ int s_off[EPC][4];     // points: toff, soff, nrow, ncol
+    __shared__ int64_t s_blk[EPC];
+    __shared__ double s_cheb[16];
+    const int e_base = blockIdx.x * EPC, cnt = min(EPC, m.entries - e_base);
     const int np = NR == 16 ? 4 : T.np;
-    int nrow, ncol, toff = 0, soff = 0;
-    double tcx = 0, tcy = 0, trx = 0, try_ = 0, scx = 0, scy = 0, srx = 0, sry = 0;
-    if (cheb) {
-        nrow = ncol = NR ? NR : T.r;
-        tcx = T.cx[tn]; tcy = T.cy[tn]; trx = T.rx[tn]; try_ = T.ry[tn];
-        scx = T.cx[sn]; scy = T.cy[sn]; srx = T.rx[sn]; sry = T.ry[sn];
-    } else {
-        nrow = NR ? NR : T.npts[tn];
-        ncol = NR ? NR : T.npts[sn];
-        toff = T.pt_off[tn];
-        soff = T.pt_off[sn];
-    }
-    double* __restrict__ out = A + m.blk_off[e];
-    const int total = nrow * ncol;
-    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-        const int t = idx % nrow, s = idx / nrow;
-        double ax, ay, bx, by;
-        if (cheb) {  // flat = j*np + i, y slow (bbfmm.h:787-800)
-            ax = scx + srx * T.cheb[s % np];
-            ay = scy + sry * T.cheb[s / np];
-            bx = tcx + trx * T.cheb[t % np];
-            by = tcy + try_ * T.cheb[t / np];
+    if (threadIdx.x < cnt) {
+        const int e = e_base + threadIdx.x;
+        const int tn = m.tgt_node[e], sn = m.src_node[e];
+        s_blk[threadIdx.x] = m.blk_off[e];
+        if (cheb) {
+            const double g0 = T.cx[tn], g1 = T.cy[tn], g2 = T.rx[tn], g3 = T.ry[tn];
+            const double g4 = T.cx[sn], g5 = T.cy[sn], g6 = T.rx[sn], g7 = T.ry[sn];
+            double* __restrict__ gg = s_geo[threadIdx.x];
+            gg[0] = g0; gg[1] = g1; gg[2] = g2; gg[3] = g3; gg[4] = g4; gg[5] = g5; gg[6] = g6; gg[7] = g7;
+            s_off[threadIdx.x][2] = s_off[threadIdx.x][3] = NR ? NR : T.r;
         } else {
-            ax = G.px[soff + s];
-            ay = G.py[soff + s];
-            bx = G.px[toff + t];
-            by = G.py[toff + t];
+            const int o0 = T.pt_off[tn], o1 = T.pt_off[sn];
+            const int n0 = NR ? NR : T.npts[tn], n1 = NR ? NR : T.npts[sn];
+            s_off[threadIdx.x][0] = o0; s_off[threadIdx.x][1] = o1; s_off[threadIdx.x][2] = n0; s_off[threadIdx.x][3] = n1;
         }
-        out[idx] = kernel_eval_t<D1>(S, id, part, ax, ay, bx, by);
+    } else if (threadIdx.x >= 32 && threadIdx.x < 32 + np && cheb)
+        s_cheb[threadIdx.x - 32] = T.cheb[threadIdx.x - 32];
+    __syncthreads();
+    for (int j = 0; j < cnt; ++j) {
+        const int nrow = s_off[j][2], ncol = s_off[j][3];
+        double* __restrict__ out = A + s_blk[j];
+        const int total = nrow * ncol;
+        for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+            const int t = NR ? idx % NR : idx % nrow, s = NR ? idx / NR : idx / nrow;
+            double ax, ay, bx, by;
+            if (cheb) {  // flat = j*np + i, y slow (bbfmm.h:787-800)
+                const double* __restrict__ gg = s_geo[j];
+                ax = gg[4] + gg[6] * s_cheb[s % np];
+                ay = gg[5] + gg[7] * s_cheb[s / np];
+                bx = gg[0] + gg[2] * s_cheb[t % np];
+                by = gg[1] + gg[3] * s_cheb[t / np];
+            } else {
+                const int toff = s_off[j][0], soff = s_off[j][1];
+                ax = G.px[soff + s];
+                ay = G.py[soff + s];
+                bx = G.px[toff + t];
+                by = G.py[toff + t];
+            }
+            out[idx] = kernel_eval_t<D1>(S, id, part, ax, ay, bx, by);
+        }
     }
 }
 
@@ -268,9 +286,10 @@ void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const Sigm
     int threads = 256;
     if (cheb && T.r <= 8) threads = 64;
     else if (cheb && T.r <= 11) threads = 128;
-    if (S.ty && m.uniform_block == 16) fill_blocks_kernel<true, 16><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
-    else if (S.ty) fill_blocks_kernel<true, 0><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
-    else fill_blocks_kernel<false, 0><<<m.entries, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    const unsigned ctas = (m.entries + EPC - 1) / EPC;
+    if (S.ty && m.uniform_block == 16) fill_blocks_kernel<true, 16><<<ctas, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    else if (S.ty) fill_blocks_kernel<true, 0><<<ctas, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
+    else fill_blocks_kernel<false, 0><<<ctas, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
 }
 
 __global__ void probe_line_integral_kernel(SigmaGrid S, int n, const double* __restrict__ p, double* __restrict__ out) {
@@ -302,11 +321,12 @@ void launch_probe_kernel(const SigmaGrid& S, int id, int part, int n, const doub
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ double real_kernel(int id, double ax, double ay, double bx, double by) {
     const double ddx = ax - bx, ddy = ay - by;
-    const double dist = sqrt(ddx * ddx + ddy * ddy);
-    if (dist == 0.0) return 0.0;
-    if (id == 0) return 1 / dist;
-    const double inv = 1.0 / dist;
-    return cos_k_theta(id, ddx * inv, ddy * inv) / dist;
+    const double d2 = ddx * ddx + ddy * ddy;
+    if (d2 == 0.0) return 0.0;
+    double inv = rsqrt(d2);  // + one Newton step on the product: within an ulp of 1/sqrt(d2), 4x fewer instructions
+    inv = fma(fma(-d2 * inv, inv, 1.0), 0.5 * inv, inv);
+    if (id == 0) return inv;
+    return cos_k_theta(id, ddx * inv, ddy * inv) * inv;
 }
 
 __device__ __forceinline__ double legendre_tr1_dev(int l, double x) {
@@ -363,13 +383,28 @@ __global__ void __launch_bounds__(128) build_stencils_kernel(DevGeom G, int id, 
             const double* __restrict__ sW = G.singW + (size_t)tq * G.nsing;
             const int n = q / deg, kk = q - n * deg;
             const double nrm = G.lnorm[q];
+            const double xc = (0.5 + ti) * dx, yc = (0.5 + tj) * dx;
             double acc = 0;
-            for (int pp = 0; pp < G.nsing; ++pp) {
-                const double x = (0.5 + ti) * dx + 0.5 * (sX[pp]) * dx;
-                const double y = (0.5 + tj) * dx + 0.5 * (sY[pp]) * dx;
-                const double w = sW[pp] * (dx * dx) / 4.0;
-                const double inter = real_kernel(id, x, y, tx, ty) * w;
-                acc += (legendre_tr1_dev(n, x) * legendre_tr1_dev(kk, y) / nrm) * inter;
+            if (deg == 1) {  // P_0 = 1: the 8 sr^2 Duffy points only carry the kernel and the weight
+                double acc1 = 0;
+                int pp = 0;
+                for (; pp + 2 <= G.nsing; pp += 2) {
+                    const double x0 = xc + 0.5 * sX[pp] * dx, y0 = yc + 0.5 * sY[pp] * dx;
+                    const double x1 = xc + 0.5 * sX[pp + 1] * dx, y1 = yc + 0.5 * sY[pp + 1] * dx;
+                    acc += (1.0 / nrm) * (real_kernel(id, x0, y0, tx, ty) * (sW[pp] * (dx * dx) / 4.0));
+                    acc1 += (1.0 / nrm) * (real_kernel(id, x1, y1, tx, ty) * (sW[pp + 1] * (dx * dx) / 4.0));
+                }
+                for (; pp < G.nsing; ++pp)
+                    acc += (1.0 / nrm) * (real_kernel(id, xc + 0.5 * sX[pp] * dx, yc + 0.5 * sY[pp] * dx, tx, ty) * (sW[pp] * (dx * dx) / 4.0));
+                acc += acc1;
+            } else {
+                for (int pp = 0; pp < G.nsing; ++pp) {
+                    const double x = xc + 0.5 * (sX[pp]) * dx;
+                    const double y = yc + 0.5 * (sY[pp]) * dx;
+                    const double w = sW[pp] * (dx * dx) / 4.0;
+                    const double inter = real_kernel(id, x, y, tx, ty) * w;
+                    acc += (legendre_tr1_dev(n, x) * legendre_tr1_dev(kk, y) / nrm) * inter;
+                }
             }
             c9[(size_t)q * nown + k] = acc;
         }
