@@ -603,10 +603,15 @@ OperatorCache& ensure_ops(aniso_handle* h, int id, int part) {
     c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz);
     cudaEvent_t ev[3];
     for (auto& e : ev) CK(cudaEventCreate(&e));
+    // the optical depth is the same for every kernel id: ids > 0 of the fused operators are derived from id 0
+    const OperatorCache* base = nullptr;
+    if (id > 0 && part == PART_BOTH && !getenv("ANISO_NO_SHARED_TAU")) base = &ensure_ops(h, 0, PART_BOTH);
     CK(cudaEventRecord(ev[0], h->st));
-    LAUNCH(h, launch_fill(h->p2p, h->T, h->G, h->S, id, part, 0, c.p2p, h->st));
+    if (base) LAUNCH(h, launch_fill_from_base(h->p2p, h->T, h->G, id, 0, base->p2p, c.p2p, h->st));
+    else LAUNCH(h, launch_fill(h->p2p, h->T, h->G, h->S, id, part, 0, c.p2p, h->st));
     CK(cudaEventRecord(ev[1], h->st));
-    LAUNCH(h, launch_fill(h->m2l, h->T, h->G, h->S, id, part, 1, c.m2l, h->st));
+    if (base) LAUNCH(h, launch_fill_from_base(h->m2l, h->T, h->G, id, 1, base->m2l, c.m2l, h->st));
+    else LAUNCH(h, launch_fill(h->m2l, h->T, h->G, h->S, id, part, 1, c.m2l, h->st));
     CK(cudaEventRecord(ev[2], h->st));
     CK(cudaGetLastError());
     CK(cudaEventSynchronize(ev[2]));

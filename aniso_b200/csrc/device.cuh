@@ -68,6 +68,9 @@ struct DevGeom {
 // else the points of the two nodes (P2P).  A[blk_off[e] + s*nrow + t] = eval(source s, target t).
 void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const SigmaGrid& S, int id, int part, int cheb,
                  double* A, cudaStream_t st);
+// same for kernel id > 0, part BOTH, from the id-0 operators A0 (one multiply by cos(id * theta) per entry, no ray march)
+void launch_fill_from_base(const DevCSR& m, const DevTree& T, const DevGeom& G, int id, int cheb, const double* A0, double* A,
+                           cudaStream_t st);
 // y[row] (=) sum over entries: the HBM-streaming cached apply (K3 / K4)
 // sign = (-1)^id: parity of the kernel family under source<->target exchange (symmetric storage only)
 // reduce = false (symmetric storage only): leave the per-target sums in the scratch rows for the consumer to fold

@@ -280,6 +280,70 @@ __global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, 
     }
 }
 
+// Operators of kernel id k > 0 from those of id 0 (the optical depth does not depend on the id):
+//   K_k = exp(-tau) cos(k theta) / d = K_0 * cos(k theta),  diagonal 0 (makeKernels, KernelFactory.cpp:240-267),
+// one streaming pass over K_0 instead of a second ray march per entry.  Same CTA layout as fill_blocks_kernel.
+__global__ void __launch_bounds__(256) fill_from_base_kernel(DevCSR m, DevTree T, DevGeom G, int id, int cheb,
+                                                             const double* __restrict__ A0, double* __restrict__ A) {
+    __shared__ double s_geo[EPC][8];
+    __shared__ int s_off[EPC][4];
+    __shared__ int64_t s_blk[EPC];
+    __shared__ double s_cheb[16];
+    const int e_base = blockIdx.x * EPC, cnt = min(EPC, m.entries - e_base);
+    const int np = T.np;
+    if (threadIdx.x < cnt) {
+        const int e = e_base + threadIdx.x;
+        const int tn = m.tgt_node[e], sn = m.src_node[e];
+        s_blk[threadIdx.x] = m.blk_off[e];
+        if (cheb) {
+            double* __restrict__ gg = s_geo[threadIdx.x];
+            gg[0] = T.cx[tn]; gg[1] = T.cy[tn]; gg[2] = T.rx[tn]; gg[3] = T.ry[tn];
+            gg[4] = T.cx[sn]; gg[5] = T.cy[sn]; gg[6] = T.rx[sn]; gg[7] = T.ry[sn];
+            s_off[threadIdx.x][2] = s_off[threadIdx.x][3] = T.r;
+        } else {
+            s_off[threadIdx.x][0] = T.pt_off[tn]; s_off[threadIdx.x][1] = T.pt_off[sn];
+            s_off[threadIdx.x][2] = T.npts[tn]; s_off[threadIdx.x][3] = T.npts[sn];
+        }
+    } else if (threadIdx.x >= 32 && threadIdx.x < 32 + np && cheb)
+        s_cheb[threadIdx.x - 32] = T.cheb[threadIdx.x - 32];
+    __syncthreads();
+    for (int j = 0; j < cnt; ++j) {
+        const int nrow = s_off[j][2], ncol = s_off[j][3];
+        const double* __restrict__ in = A0 + s_blk[j];
+        double* __restrict__ out = A + s_blk[j];
+        const int total = nrow * ncol;
+        for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+            const double base = in[idx];
+            const int t = idx % nrow, s = idx / nrow;
+            double ax, ay, bx, by;
+            if (cheb) {
+                const double* __restrict__ gg = s_geo[j];
+                ax = gg[4] + gg[6] * s_cheb[s % np];
+                ay = gg[5] + gg[7] * s_cheb[s / np];
+                bx = gg[0] + gg[2] * s_cheb[t % np];
+                by = gg[1] + gg[3] * s_cheb[t / np];
+            } else {
+                const int toff = s_off[j][0], soff = s_off[j][1];
+                ax = G.px[soff + s]; ay = G.py[soff + s];
+                bx = G.px[toff + t]; by = G.py[toff + t];
+            }
+            const double ddx = ax - bx, ddy = ay - by, d2 = ddx * ddx + ddy * ddy;
+            double v = 0.0;
+            if (d2 != 0.0) {
+                double inv = rsqrt(d2);
+                inv = fma(fma(-d2 * inv, inv, 1.0), 0.5 * inv, inv);
+                v = base * cos_k_theta(id, ddx * inv, ddy * inv);
+            }
+            out[idx] = v;
+        }
+    }
+}
+void launch_fill_from_base(const DevCSR& m, const DevTree& T, const DevGeom& G, int id, int cheb, const double* A0, double* A,
+                           cudaStream_t st) {
+    if (m.entries == 0) return;
+    fill_from_base_kernel<<<(m.entries + EPC - 1) / EPC, 256, 0, st>>>(m, T, G, id, cheb, A0, A);
+}
+
 void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const SigmaGrid& S, int id, int part, int cheb,
                  double* A, cudaStream_t st) {
     if (m.entries == 0) return;
