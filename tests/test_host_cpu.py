@@ -162,3 +162,14 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".hpp", ".cuh", ".h")):
                 src = open(os.path.join(root, f)).read()
                 assert "oracle" not in src.lower(), os.path.join(root, f)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/mexplus"), reason="needs the reference's mexplus headers (build container only)")
+def test_mex_gateway_compiles_against_stub_mex():
+    """the MEX gateway rebuilt on the C-ABI (examples/AnisoWrapper_b200.cpp) compiles against a
+    declarations-only mex.h and the reference's own mexplus (MATLAB itself is not installed)."""
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run(["make", "-s", "-C", os.path.join(root, "oracle"), "mexcheck"], capture_output=True, text=True)
+    assert out.returncode == 0 and "mexcheck ok" in out.stdout, out.stderr[-2000:]
