@@ -79,6 +79,7 @@ struct aniso_handle {
     double *d_f = nullptr, *d_q = nullptr, *d_mcharge = nullptr, *d_mpot = nullptr, *d_pot = nullptr;
     double *d_fmm = nullptr, *d_corr = nullptr, *d_a = nullptr, *d_b = nullptr, *d_xfull = nullptr, *d_stage = nullptr;
     double *d_blk_full = nullptr, *d_blk_tmp = nullptr;  // block operator work space
+    double *d_blk_q = nullptr, *d_blk_f = nullptr, *d_blk_mc = nullptr, *d_blk_sm = nullptr, *d_blk_sp = nullptr;  // batched form
     double* gm_buf = nullptr;   // Krylov work space, kept between solves ((m+3) vectors + CGS2 partials)
     size_t gm_cap = 0;
     double* pinned_small = nullptr;  // 2048 doubles: Hessenberg column read-back
@@ -1118,6 +1119,59 @@ void forward_own(aniso_handle* h, const double* x_own, double* y_own) {
 //   mforward (weighted = true):  out_i = sum_j chi_|j| mapping_{|i+j|}(sigma_s .* u_|j|),  chi_a = (g^a - g^K)/(1 - g^K)
 // the only place the Henyey-Greenstein anisotropy g acts.  subtract: out = u - out (the GMRES operator of aniso.m:162).
 // u_own / out: K blocks of owned rows in slot order.  Loop and accumulation order are the reference's.
+// Batched form (complete uniform tree, symmetric 16x16 / 64x64 blocks): every cached operator is streamed ONCE per block
+// apply for all K input modes (launch_bsr_apply_multi), the upward pass runs once per input mode and the downward pass once
+// per output mode, folding the 2K-1 (kernel id, input mode) terms with their coefficients (FoldList).  2K-1 operator
+// streams instead of K(2K-1).
+bool block_multi_ok(const aniso_handle* h) {
+    const int K = h->plan.K;
+    auto ok = [](const DevCSR& m) { return m.symmetric && (m.uniform_block == 16 || m.uniform_block == 64); };
+    return h->subtree_ok && ok(h->m2l) && ok(h->p2p) && 2 * K - 1 <= FoldList::MAXF && !getenv("ANISO_BLOCK_LOOP");
+}
+
+void block_apply_multi(aniso_handle* h, const double* full, const double* u_own, double* out, bool weighted, bool subtract) {
+    const int K = h->plan.K, N = h->plan.N, n = h->nown, nk = 2 * K - 1;
+    const DevTree& T = h->T;
+    const size_t mc = (size_t)T.nnodes * T.r;
+    const size_t Sm = (size_t)h->m2l.scratch_rows * h->m2l.uniform_block, Sp = (size_t)h->p2p.scratch_rows * h->p2p.uniform_block;
+    if (!h->d_blk_q) {
+        h->d_blk_q = dalloc<double>(h, (size_t)K * N);
+        h->d_blk_f = dalloc<double>(h, (size_t)K * N);
+        h->d_blk_mc = dalloc<double>(h, (size_t)K * mc);
+        h->d_blk_sm = dalloc<double>(h, (size_t)nk * K * Sm);
+        h->d_blk_sp = dalloc<double>(h, (size_t)nk * K * Sp);
+    }
+    for (int a = 0; a < K; ++a) {
+        LAUNCH(h, launch_scale(N, full + (size_t)a * N, weighted ? h->d_sig_s : nullptr, h->G.pw, h->G.perm, h->d_blk_f + (size_t)a * N,
+                               h->d_blk_q + (size_t)a * N, h->st));
+        h->launches += launch_up_tree(T, h->G, h->sub, h->d_blk_q + (size_t)a * N, h->d_blk_mc + (size_t)a * mc, h->st, nullptr);
+    }
+    std::vector<const double*> stencil(nk);
+    for (int k = 0; k < nk; ++k) {
+        OperatorCache& c = ensure_ops(h, k, PART_BOTH);
+        stencil[k] = ensure_stencils(h, k).call;
+        h->launches += launch_bsr_apply_multi(h->m2l, c.m2l, h->d_blk_mc, mc, K, h->d_blk_sm + (size_t)k * K * Sm, Sm, c.sign, h->st);
+        h->launches += launch_bsr_apply_multi(h->p2p, c.p2p, h->d_blk_q, (size_t)N, K, h->d_blk_sp + (size_t)k * K * Sp, Sp, c.sign, h->st);
+    }
+    const double g = h->plan.g, gK = std::pow(g, K);
+    for (int iid = 0; iid < K; ++iid) {
+        FoldList fl;
+        for (int j = -(K - 1); j <= K - 1; ++j) {  // the reference's loop order (aniso.m:126, 143)
+            const int a = std::abs(j), k = std::abs(-iid - j), t = fl.n++;
+            fl.coef[t] = weighted ? (std::pow(g, a) - gK) / (1.0 - gK) : 1.0;
+            fl.m2l_scr[t] = h->d_blk_sm + ((size_t)k * K + a) * Sm;
+            fl.p2p_scr[t] = h->d_blk_sp + ((size_t)k * K + a) * Sp;
+            fl.C[t] = stencil[k];
+            fl.f[t] = h->d_blk_f + (size_t)a * N;
+        }
+        h->launches += launch_down_mid_tree(T, h->m2l, true, h->sub, h->first_m2l_level, h->d_mpot, h->st, &fl);
+        h->launches += launch_down_leaf_tree(T, h->G, h->m2l, true, h->p2p, true, h->sub, h->first_m2l_level, h->d_leaf_of_slot, h->slot0,
+                                             n, h->d_mpot, h->d_pot, nullptr, nullptr, u_own + (size_t)iid * n, out + (size_t)iid * n,
+                                             subtract ? 2 : 1, h->st, &fl);
+    }
+    CK(cudaGetLastError());
+}
+
 void block_apply(aniso_handle* h, const double* u_own, double* out, bool weighted, bool subtract) {
     const int K = h->plan.K, N = h->plan.N, n = h->nown;
     if (!h->d_blk_tmp) h->d_blk_tmp = dalloc<double>(h, n);
@@ -1126,6 +1180,10 @@ void block_apply(aniso_handle* h, const double* u_own, double* out, bool weighte
         if (!h->d_blk_full) h->d_blk_full = dalloc<double>(h, (size_t)K * N);
         for (int a = 0; a < K; ++a) allgather_slots(h, u_own + (size_t)a * n, h->d_blk_full + (size_t)a * N);
         full = h->d_blk_full;
+    }
+    if (block_multi_ok(h)) {
+        block_apply_multi(h, full, u_own, out, weighted, subtract);
+        return;
     }
     const double g = h->plan.g, gK = std::pow(g, K);
     for (int i = -(K - 1); i <= 0; ++i) {

@@ -76,6 +76,10 @@ void launch_fill_from_base(const DevCSR& m, const DevTree& T, const DevGeom& G, 
 // reduce = false (symmetric storage only): leave the per-target sums in the scratch rows for the consumer to fold
 void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, double sign, bool reduce, cudaStream_t st);
 void launch_bsr_reduce(const DevCSR& m, double* y, cudaStream_t st);
+// the same operator applied to nrhs vectors x + r*xstride in one pass (symmetric storage, 16x16 / 64x64 blocks); results
+// stay in the scratch sets scr + r*sstride (laid out like m.scratch).  Returns the number of launches.
+int launch_bsr_apply_multi(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
+                           double sign, cudaStream_t st);
 // q = f.*w, f = x or sig_s.*x; f_ref (optional) = f scattered into reference node order
 void launch_scale(int n, const double* x, const double* sig_s, const double* w, const int* perm, double* f_ref, double* q,
                   cudaStream_t st);
@@ -86,6 +90,19 @@ void launch_l2l(const DevTree& T, const DevCSR& m2l, bool fold, int first, int c
 // levels [Llo, Lhi] (at most 1024 nodes each) in one single-CTA launch
 void launch_m2m_top(const DevTree& T, int Lhi, int Llo, double* mcharge, cudaStream_t st);
 void launch_l2l_top(const DevTree& T, const DevCSR& m2l, bool fold, int Llo, int Lhi, double* mpot, cudaStream_t st);
+// The terms of one output mode of the multi-mode block operator (aniso.m:121-156): out = sum_j coef[j] * mapping_{k_j}(u_{a_j}).
+// The streams of (k_j, a_j) left their per-target sums in the scratch sets m2l_scr[j] / p2p_scr[j]; the downward pass folds
+// and combines them, so one downward pass serves all 2K-1 terms.
+struct FoldList {
+    static constexpr int MAXF = 16;
+    int n = 0;
+    double coef[MAXF];
+    const double* m2l_scr[MAXF];
+    const double* p2p_scr[MAXF];
+    const double* C[MAXF];  // fused correction stencil of kernel id k_j
+    const double* f[MAXF];  // unscaled source of input mode a_j, reference node order
+};
+
 // ---- sub-tree passes for complete uniform trees (subtree.cu) ----
 struct SubtreePlan {
     int leaf_Ls = 0, leaf_D = 0;          // sub-trees holding the leaves: roots at level leaf_Ls, leaf_D levels below
@@ -96,10 +113,13 @@ SubtreePlan make_subtree_plan(int first_m2l_level, int deepest, int r);
 // Return value: kernels launched.
 int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
                    cudaEvent_t leaf_done);
-int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st);
+// fl != nullptr: multi-term folds (block operator; needs fold == fold_p2p == true); C / f_ref / pot are then unused
+int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st,
+                         const FoldList* fl = nullptr);
 int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                           const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
-                          const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st);
+                          const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
+                          const FoldList* fl = nullptr);
 // L2P + tail of the matvec for slots [slot0, slot0+n):  fmm = pot[p] + L2P(p)
 //   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi   (C: fused stencil, f_ref: full unscaled source in reference order)
 void launch_l2p(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,

@@ -217,6 +217,92 @@ __global__ void __launch_bounds__(256, 4) bsr_apply_sym_kernel(DevCSR m, const d
     }
 }
 
+// Multi-mode block operator (aniso.m:121-156): the same operator block applied to NRHS right-hand sides in one pass over
+// the operator (x_r = x + r * xstride, scratch set r = scratch + r * sstride).  Same lane map and butterfly as
+// bsr_apply_sym_kernel; per 16-byte load the FP64 work grows NRHS-fold, which moves the kernel from the HBM roofline
+// towards the FP64 pipe (measured in profiles/).
+template <int R, int NRHS>
+__global__ void __launch_bounds__(256, 2) bsr_apply_sym_multi_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
+                                                                     size_t xstride, double* __restrict__ scr, size_t sstride,
+                                                                     double sign) {
+    constexpr int PAIRS = R * R / 2, ITERS = PAIRS / 32, CH = 4;
+    static_assert(64 % R == 0 && PAIRS % 32 == 0 && ITERS % CH == 0, "lane -> target pair must be loop invariant");
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (g >= m.groups) return;
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const uint64_t pol = stream_policy();
+    const double2* __restrict__ base = reinterpret_cast<const double2*>(A + (ne ? m.blk_off[e0] : 0));
+    const int s_lane = (2 * lane) / R, t0 = (2 * lane) % R;
+    const int self = m.row_off[g];
+    double xa0[NRHS], xa1[NRHS], acc0[NRHS], acc1[NRHS];
+#pragma unroll
+    for (int r = 0; r < NRHS; ++r) {
+        xa0[r] = __ldg(x + r * xstride + self + t0);
+        xa1[r] = __ldg(x + r * xstride + self + t0 + 1);
+        acc0[r] = acc1[r] = 0;
+    }
+    for (int eb = 0; eb < ne; eb += 32) {
+        const int cnt = min(32, ne - eb);
+        const int mycol = lane < cnt ? m.col_off[e0 + eb + lane] : 0;
+        const int mymir = lane < cnt ? m.mirror_row[e0 + eb + lane] : -1;
+        for (int j = 0; j < cnt; ++j) {
+            const int c0 = __shfl_sync(0xffffffffu, mycol, j) + s_lane;
+            const int m0 = __shfl_sync(0xffffffffu, mymir, j);
+            const double2* __restrict__ b0 = base + (size_t)(eb + j) * PAIRS + lane;
+#pragma unroll 1
+            for (int it0 = 0; it0 < ITERS; it0 += CH) {
+                double2 a0[CH];
+#pragma unroll
+                for (int u = 0; u < CH; ++u) a0[u] = ld_stream2(b0 + (it0 + u) * 32, pol);
+#pragma unroll
+                for (int r = 0; r < NRHS; ++r)
+                    sym_consume<R>(a0, it0, x + r * xstride + c0, xa0[r], xa1[r], m0, lane, s_lane, sign, acc0[r], acc1[r],
+                                   scr + r * sstride);
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < NRHS; ++r) {
+        double v0 = acc0[r], v1 = acc1[r];
+#pragma unroll
+        for (int off = 16; off >= R / 2; off >>= 1) {
+            v0 += __shfl_down_sync(0xffffffffu, v0, off);
+            v1 += __shfl_down_sync(0xffffffffu, v1, off);
+        }
+        if (lane < R / 2) {
+            double* __restrict__ out = scr + r * sstride + (size_t)m.srow_ptr[g] * R + 2 * lane;
+            out[0] = v0;
+            out[1] = v1;
+        }
+    }
+}
+
+template <int R>
+static void launch_multi_R(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
+                           double sign, cudaStream_t st) {
+    const unsigned ctas = (m.groups + 7) / 8;
+    int r = 0;
+    while (r < nrhs) {  // at most four right-hand sides per pass over the operator
+        const int c = nrhs - r >= 4 ? 4 : nrhs - r == 3 ? 3 : nrhs - r == 2 ? 2 : 1;
+        const double* xr = x + (size_t)r * xstride;
+        double* sr = scr + (size_t)r * sstride;
+        if (c == 4) bsr_apply_sym_multi_kernel<R, 4><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
+        else if (c == 3) bsr_apply_sym_multi_kernel<R, 3><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
+        else if (c == 2) bsr_apply_sym_multi_kernel<R, 2><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
+        else bsr_apply_sym_multi_kernel<R, 1><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
+        r += c;
+    }
+}
+// number of kernel launches is returned; requires m.symmetric and uniform 16 x 16 or 64 x 64 blocks
+int launch_bsr_apply_multi(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
+                           double sign, cudaStream_t st) {
+    if (m.groups == 0 || nrhs == 0) return 0;
+    if (m.uniform_block == 16) launch_multi_R<16>(m, A, x, xstride, nrhs, scr, sstride, sign, st);
+    else launch_multi_R<64>(m, A, x, xstride, nrhs, scr, sstride, sign, st);
+    return (nrhs + 3) / 4;
+}
+
 __global__ void __launch_bounds__(256) bsr_reduce_kernel(DevCSR m, double* __restrict__ y) {
     const int R = m.uniform_block;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

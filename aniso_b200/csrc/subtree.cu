@@ -151,10 +151,8 @@ __global__ void __launch_bounds__(256) up_mid_kernel(DevTree T, double* __restri
 }
 
 // Scratch rows of a tree node (symmetric storage) summed in their fixed order; node_rows[node] = [first, last) row.
-__device__ __forceinline__ double fold_node(const DevCSR& m, int node, int t) {
-    const int2 rr = m.node_rows[node];
-    const int R = m.uniform_block;
-    const double* __restrict__ base = m.scratch + t;
+__device__ __forceinline__ double fold_rows_at(const double* __restrict__ scratch, int2 rr, int R, int t) {
+    const double* __restrict__ base = scratch + t;
     double s = 0;
     for (int r = rr.x; r < rr.y; r += 8) {  // eight independent loads in flight per round
         double v[8];
@@ -164,14 +162,24 @@ __device__ __forceinline__ double fold_node(const DevCSR& m, int node, int t) {
     }
     return s;
 }
+__device__ __forceinline__ double fold_node(const DevCSR& m, int node, int t) {
+    return fold_rows_at(m.scratch, m.node_rows[node], m.uniform_block, t);
+}
+// block operator: the same fold over the scratch sets of all terms, combined with their coefficients
+__device__ __forceinline__ double fold_node_multi(const DevCSR& m, const FoldList& fl, const double* const* scr, int node, int t) {
+    const int2 rr = m.node_rows[node];
+    double s = 0;
+    for (int j = 0; j < fl.n; ++j) s = fma(fl.coef[j], fold_rows_at(scr[j], rr, m.uniform_block, t), s);
+    return s;
+}
 
 // L2L inside shared memory: levels 0 .. D of the sub-tree rooted at node (Ls, m), in two steps.
 // subtree_own: every node's own contribution goes to sm[(lvoff(d) + g)*r + a] - for the root the finished local
 // expansion written by the chunk above (or, top: its own M2L sum, the first level with M2L lists has no parent term), for
 // the others their M2L sum.  FOLD: M2L sums are still spread over scratch rows (symmetric storage), otherwise they sit
 // in mpot.  None of these loads depends on another node, so they are all in flight together (no barrier inside).
-template <bool FOLD>
-__device__ __forceinline__ void subtree_own(const DevTree& T, const DevCSR& m2l, int Ls, int m, int D, bool top,
+template <bool FOLD, bool MULTI>
+__device__ __forceinline__ void subtree_own(const DevTree& T, const DevCSR& m2l, const FoldList& fl, int Ls, int m, int D, bool top,
                                             double* __restrict__ sm, const double* __restrict__ mpot) {
     const int r = T.r, total = lvoff(D + 1) * r;
     for (int o = threadIdx.x; o < total; o += blockDim.x) {
@@ -179,7 +187,8 @@ __device__ __forceinline__ void subtree_own(const DevTree& T, const DevCSR& m2l,
         int d = 0;
         while (lvoff(d + 1) <= q) ++d;
         const int id = lvoff(Ls + d) + (m << (2 * d)) + (q - lvoff(d));
-        sm[o] = (FOLD && (d > 0 || top)) ? fold_node(m2l, id, a) : mpot[(size_t)id * r + a];
+        if (FOLD && (d > 0 || top)) sm[o] = MULTI ? fold_node_multi(m2l, fl, fl.m2l_scr, id, a) : fold_node(m2l, id, a);
+        else sm[o] = mpot[(size_t)id * r + a];
     }
 }
 // subtree_l2l: child += R[index] * parent level by level (bbfmm.h:1070-1071), one block barrier per level; starts with
@@ -215,14 +224,15 @@ __device__ __forceinline__ void subtree_l2l(const DevTree& T, int Ls, int m, int
     }
 }
 
-template <bool SMEM_R, bool FOLD>
-__global__ void __launch_bounds__(256) down_mid_kernel(DevTree T, DevCSR m2l, double* __restrict__ mpot, int Ls, int D, int top) {
+template <bool SMEM_R, bool FOLD, bool MULTI>
+__global__ void __launch_bounds__(256) down_mid_kernel(DevTree T, DevCSR m2l, double* __restrict__ mpot, int Ls, int D, int top,
+                                                       const __grid_constant__ FoldList fl) {
     extern __shared__ double sm[];
     const int r = T.r;
     double* __restrict__ RTs = sm + (size_t)lvoff(D + 1) * r;
     if (SMEM_R)
         for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) RTs[i] = __ldg(T.RT + i);
-    subtree_own<FOLD>(T, m2l, Ls, blockIdx.x, D, top != 0, sm, mpot);
+    subtree_own<FOLD, MULTI>(T, m2l, fl, Ls, blockIdx.x, D, top != 0, sm, mpot);
     subtree_l2l<SMEM_R>(T, Ls, blockIdx.x, D, true, sm, RTs, mpot);
 }
 
@@ -230,13 +240,13 @@ __global__ void __launch_bounds__(256) down_mid_kernel(DevTree T, DevCSR m2l, do
 //   fmm = near(p) + sum_{i,j} Sx(p,i) Sy(p,j) local[leaf][j*np+i]                 L2P, bbfmm.h:1104-1113
 //   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi
 // near(p): P2P sum, already reduced in pot or still spread over the leaf's scratch rows (fold_p2p).
-template <int NP, bool SMEM_R, bool FOLD>
+template <int NP, bool SMEM_R, bool FOLD, bool MULTI>
 __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree T, DevGeom G, DevCSR m2l, DevCSR p2p, int fold_p2p,
                                                         const int* __restrict__ leaf_of_slot, int slot0, int n,
                                                         double* __restrict__ mpot, const double* __restrict__ pot,
                                                         const double* __restrict__ C, const double* __restrict__ f_ref,
                                                         const double* __restrict__ x, double* __restrict__ out, int mode, int Ls,
-                                                        int D, int top) {
+                                                        int D, int top, const __grid_constant__ FoldList fl) {
     extern __shared__ double sm[];
     __shared__ double tn[NP_MAX * NP_MAX];
     const int np = NP ? NP : T.np, r = np * np, m = blockIdx.x;
@@ -263,22 +273,30 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
             const int c2 = G.c2, sz = G.sz;
             const int tc = G.perm[p] / c2;
             const int ti = tc / sz, tj = tc - ti * sz;
-            for (int qq = 0; qq < c2; ++qq) {  // the 18 loads of one Legendre mode are issued together
-                double cv[9], fv[9];
+            const int nterm = MULTI ? fl.n : 1;
+            for (int jt = 0; jt < nterm; ++jt) {
+                const double* __restrict__ Cj = MULTI ? fl.C[jt] : C;
+                const double* __restrict__ fj = MULTI ? fl.f[jt] : f_ref;
+                double cj = 0;
+                for (int qq = 0; qq < c2; ++qq) {  // the 18 loads of one Legendre mode are issued together
+                    double cv[9], fv[9];
 #pragma unroll
-                for (int cs = 0; cs < 9; ++cs) {
-                    const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
-                    const bool ok = si >= 0 && si < sz && sj >= 0 && sj < sz;
-                    cv[cs] = ok ? C[(size_t)(cs * c2 + qq) * n + k] : 0.0;
-                    fv[cs] = ok ? f_ref[(size_t)(si * sz + sj) * c2 + qq] : 0.0;
+                    for (int cs = 0; cs < 9; ++cs) {
+                        const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
+                        const bool ok = si >= 0 && si < sz && sj >= 0 && sj < sz;
+                        cv[cs] = ok ? Cj[(size_t)(cs * c2 + qq) * n + k] : 0.0;
+                        fv[cs] = ok ? fj[(size_t)(si * sz + sj) * c2 + qq] : 0.0;
+                    }
+#pragma unroll
+                    for (int cs = 0; cs < 9; ++cs) cj = fma(cv[cs], fv[cs], cj);
                 }
-#pragma unroll
-                for (int cs = 0; cs < 9; ++cs) P.corr = fma(cv[cs], fv[cs], P.corr);
+                P.corr = MULTI ? fma(fl.coef[jt], cj, P.corr) : cj;
             }
         }
         const int id = n0 ? leaf0 + (p - rb) / n0 : leaf_of_slot[p];
         P.lo = id - leaf0;
-        P.near = fold_p2p ? fold_node(p2p, id, n0 ? (p - rb) % n0 : p - T.pt_off[id]) : pot[p];
+        const int tl = n0 ? (p - rb) % n0 : p - T.pt_off[id];
+        P.near = MULTI ? fold_node_multi(p2p, fl, fl.p2p_scr, id, tl) : fold_p2p ? fold_node(p2p, id, tl) : pot[p];
         cheb_weights<NP>(tn, np, G.sxn[p], P.wx);
         cheb_weights<NP>(tn, np, G.syn[p], P.wy);
     };
@@ -306,7 +324,7 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
     __syncthreads();  // tn
     const int p_first = p_begin + threadIdx.x;
     Pre P0;
-    subtree_own<FOLD>(T, m2l, Ls, m, D, top != 0, sm, mpot);
+    subtree_own<FOLD, MULTI>(T, m2l, fl, Ls, m, D, top != 0, sm, mpot);
     if (p_first < p_end) pre(p_first, P0);
     subtree_l2l<SMEM_R>(T, Ls, m, D, false, sm, RTs, mpot);
     if (p_first < p_end) post(p_first, P0);
@@ -389,18 +407,27 @@ int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, co
     return 1 + sp.nmid;
 }
 
-int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st) {
+int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st,
+                         const FoldList* flp) {
     const int r = T.r;
     const bool sr = smem_R(r);
+    static const FoldList none = FoldList();
+    const FoldList& fl = flp ? *flp : none;
     for (int c = sp.nmid - 1; c >= 0; --c) {  // top-down
         const int D = sp.mid_D[c], Ls = sp.mid_Ls[c], ctas = 1 << (2 * Ls), top = Ls == L0;
         const size_t bytes = ((size_t)lvoff(D + 1) * r + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
-#define DOWN_MID(SR, FO)                                                          \
-    do {                                                                          \
-        want_smem(down_mid_kernel<SR, FO>, bytes);                                \
-        down_mid_kernel<SR, FO><<<ctas, 256, bytes, st>>>(T, m2l, mpot, Ls, D, top); \
+#define DOWN_MID(SR, FO)                                                                       \
+    do {                                                                                       \
+        want_smem(down_mid_kernel<SR, FO, false>, bytes);                                      \
+        down_mid_kernel<SR, FO, false><<<ctas, 256, bytes, st>>>(T, m2l, mpot, Ls, D, top, fl); \
     } while (0)
-        if (sr && fold) DOWN_MID(true, true);
+        if (flp && sr) {
+            want_smem(down_mid_kernel<true, true, true>, bytes);
+            down_mid_kernel<true, true, true><<<ctas, 256, bytes, st>>>(T, m2l, mpot, Ls, D, top, fl);
+        } else if (flp) {
+            want_smem(down_mid_kernel<false, true, true>, bytes);
+            down_mid_kernel<false, true, true><<<ctas, 256, bytes, st>>>(T, m2l, mpot, Ls, D, top, fl);
+        } else if (sr && fold) DOWN_MID(true, true);
         else if (sr) DOWN_MID(true, false);
         else if (fold) DOWN_MID(false, true);
         else DOWN_MID(false, false);
@@ -412,32 +439,38 @@ int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const S
 template <int NP>
 static void down_leaf_launch(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                              const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
-                             const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st) {
+                             const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
+                             const FoldList* flp) {
+    static const FoldList none = FoldList();
+    const FoldList& fl = flp ? *flp : none;
     const int r = T.r, D = sp.leaf_D, Ls = sp.leaf_Ls, ctas = 1 << (2 * Ls), top = Ls == L0;
     const bool sr = smem_R(r);
     const size_t bytes = ((size_t)lvoff(D + 1) * r + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
-#define DOWN_LEAF(SR, FO)                                                                                                       \
+#define DOWN_LEAF(SR, FO, MU)                                                                                                   \
     do {                                                                                                                        \
-        want_smem(down_leaf_kernel<NP, SR, FO>, bytes);                                                                         \
-        down_leaf_kernel<NP, SR, FO><<<ctas, 256, bytes, st>>>(T, G, m2l, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, C, \
-                                                               f_ref, x, out, mode, Ls, D, top);                                \
+        want_smem(down_leaf_kernel<NP, SR, FO, MU>, bytes);                                                                     \
+        down_leaf_kernel<NP, SR, FO, MU><<<ctas, 256, bytes, st>>>(T, G, m2l, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, \
+                                                                   C, f_ref, x, out, mode, Ls, D, top, fl);                     \
     } while (0)
-    if (sr && fold) DOWN_LEAF(true, true);
-    else if (sr) DOWN_LEAF(true, false);
-    else if (fold) DOWN_LEAF(false, true);
-    else DOWN_LEAF(false, false);
+    if (flp && sr) DOWN_LEAF(true, true, true);
+    else if (flp) DOWN_LEAF(false, true, true);
+    else if (sr && fold) DOWN_LEAF(true, true, false);
+    else if (sr) DOWN_LEAF(true, false, false);
+    else if (fold) DOWN_LEAF(false, true, false);
+    else DOWN_LEAF(false, false, false);
 #undef DOWN_LEAF
 }
 
 int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                           const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
-                          const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st) {
+                          const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
+                          const FoldList* fl) {
     if (n == 0) return 0;
     switch (T.np) {
-        case 4: down_leaf_launch<4>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st); break;
-        case 6: down_leaf_launch<6>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st); break;
-        case 8: down_leaf_launch<8>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st); break;
-        default: down_leaf_launch<0>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st);
+        case 4: down_leaf_launch<4>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl); break;
+        case 6: down_leaf_launch<6>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl); break;
+        case 8: down_leaf_launch<8>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl); break;
+        default: down_leaf_launch<0>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl);
     }
     return 1;
 }
