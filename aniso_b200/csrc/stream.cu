@@ -114,16 +114,15 @@ __global__ void __launch_bounds__(256) bsr_apply_warp_kernel(DevCSR m, const dou
 // over the LG lanes that share a source index with a butterfly that halves the live values at every step (2 + 1
 // shuffles over lane bits 0 and 1, then one shuffle per remaining lane bit), instead of 4 x log2(LG) full reductions.
 template <int R>
-__device__ __forceinline__ void sym_consume(const double2 (&a)[4], int it0, const double* __restrict__ xs_base, double xa0,
-                                            double xa1, int mr, int lane, int s_lane, double sign, double& acc0, double& acc1,
-                                            double* __restrict__ scratch) {
+__device__ __forceinline__ void sym_consume_x(const double2 (&a)[4], const double (&xs)[4], int it0, double xa0, double xa1, int mr,
+                                              int lane, int s_lane, double sign, double& acc0, double& acc1,
+                                              double* __restrict__ scratch) {
     constexpr int S_STEP = 64 / R, LG = R / 2 < 32 ? R / 2 : 32;
     static_assert(LG >= 4, "butterfly needs at least four lanes per source index");
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-        const double xs = __ldg(xs_base + (it0 + u) * S_STEP);
-        acc0 = fma(a[u].x, xs, acc0);
-        acc1 = fma(a[u].y, xs, acc1);
+        acc0 = fma(a[u].x, xs[u], acc0);
+        acc1 = fma(a[u].y, xs[u], acc1);
     }
     if (mr < 0) return;  // warp-uniform
     const double p0 = fma(a[0].x, xa0, a[0].y * xa1), p1 = fma(a[1].x, xa0, a[1].y * xa1);
@@ -143,6 +142,17 @@ __device__ __forceinline__ void sym_consume(const double2 (&a)[4], int it0, cons
         const int u = (b0 ? 2 : 0) + (b1 ? 1 : 0);
         scratch[(size_t)mr * R + (it0 + u) * S_STEP + s_lane] = sign * z;
     }
+}
+
+template <int R>
+__device__ __forceinline__ void sym_consume(const double2 (&a)[4], int it0, const double* __restrict__ xs_base, double xa0,
+                                            double xa1, int mr, int lane, int s_lane, double sign, double& acc0, double& acc1,
+                                            double* __restrict__ scratch) {
+    constexpr int S_STEP = 64 / R;
+    double xs[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) xs[u] = __ldg(xs_base + (it0 + u) * S_STEP);
+    sym_consume_x<R>(a, xs, it0, xa0, xa1, mr, lane, s_lane, sign, acc0, acc1, scratch);
 }
 
 // Symmetric storage: only one block of each (A,B)/(B,A) pair is in memory.  While a warp streams the blocks of its
@@ -222,9 +232,10 @@ __global__ void __launch_bounds__(256, 4) bsr_apply_sym_kernel(DevCSR m, const d
 // bsr_apply_sym_kernel; per 16-byte load the FP64 work grows NRHS-fold, which moves the kernel from the HBM roofline
 // towards the FP64 pipe (measured in profiles/).
 template <int R, int NRHS>
-__global__ void __launch_bounds__(256, 2) bsr_apply_sym_multi_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
-                                                                     size_t xstride, double* __restrict__ scr, size_t sstride,
-                                                                     double sign) {
+__global__ void __launch_bounds__(256, NRHS <= 2 ? 3 : 2) bsr_apply_sym_multi_kernel(DevCSR m, const double* __restrict__ A,
+                                                                                   const double* __restrict__ x, size_t xstride,
+                                                                                   double* __restrict__ scr, size_t sstride,
+                                                                                   double sign) {
     constexpr int PAIRS = R * R / 2, ITERS = PAIRS / 32, CH = 4;
     static_assert(64 % R == 0 && PAIRS % 32 == 0 && ITERS % CH == 0, "lane -> target pair must be loop invariant");
     const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -246,7 +257,31 @@ __global__ void __launch_bounds__(256, 2) bsr_apply_sym_multi_kernel(DevCSR m, c
         const int cnt = min(32, ne - eb);
         const int mycol = lane < cnt ? m.col_off[e0 + eb + lane] : 0;
         const int mymir = lane < cnt ? m.mirror_row[e0 + eb + lane] : -1;
-        for (int j = 0; j < cnt; ++j) {
+        int j = 0;
+        for (; j + 2 <= cnt; j += 2) {  // two blocks per trip: eight 16-byte loads in flight per lane, as in the single-RHS kernel
+            const int c0 = __shfl_sync(0xffffffffu, mycol, j) + s_lane, c1 = __shfl_sync(0xffffffffu, mycol, j + 1) + s_lane;
+            const int m0 = __shfl_sync(0xffffffffu, mymir, j), m1 = __shfl_sync(0xffffffffu, mymir, j + 1);
+            const double2* __restrict__ b0 = base + (size_t)(eb + j) * PAIRS + lane;
+            const double2* __restrict__ b1 = b0 + PAIRS;
+#pragma unroll 1
+            for (int it0 = 0; it0 < ITERS; it0 += CH) {
+                double2 a0[CH], a1[CH];
+#pragma unroll
+                for (int u = 0; u < CH; ++u) {
+                    a0[u] = ld_stream2(b0 + (it0 + u) * 32, pol);
+                    a1[u] = ld_stream2(b1 + (it0 + u) * 32, pol);
+                }
+#pragma unroll
+                for (int r = 0; r < NRHS; ++r)
+                    sym_consume<R>(a0, it0, x + r * xstride + c0, xa0[r], xa1[r], m0, lane, s_lane, sign, acc0[r], acc1[r],
+                                   scr + r * sstride);
+#pragma unroll
+                for (int r = 0; r < NRHS; ++r)
+                    sym_consume<R>(a1, it0, x + r * xstride + c1, xa0[r], xa1[r], m1, lane, s_lane, sign, acc0[r], acc1[r],
+                                   scr + r * sstride);
+            }
+        }
+        if (j < cnt) {
             const int c0 = __shfl_sync(0xffffffffu, mycol, j) + s_lane;
             const int m0 = __shfl_sync(0xffffffffu, mymir, j);
             const double2* __restrict__ b0 = base + (size_t)(eb + j) * PAIRS + lane;
@@ -278,6 +313,194 @@ __global__ void __launch_bounds__(256, 2) bsr_apply_sym_multi_kernel(DevCSR m, c
     }
 }
 
+// ---- the same symmetric stream fed by the TMA engine ---------------------------------------------------------------
+// The blocks of one target are one contiguous run of ne * R * R doubles, so a warp can have the copy engine fetch it in
+// 2 KB pieces (cp.async.bulk global -> shared, completion on an mbarrier) into a private ring of STAGES buffers and only
+// ever holds the four 16-byte values of the piece it is consuming in registers.  Bytes in flight per SM no longer depend
+// on the register budget (warps x STAGES x 2 KB), which is what the multi-RHS form needs: its FP64 / shuffle work per
+// byte is NRHS times that of the single-RHS kernel and it was latency-bound with register-held loads.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+        "l"(src), "r"(bytes), "r"(bar), "l"(pol)
+        : "memory");
+}
+
+__device__ __forceinline__ void bulk_g2s_keep(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+constexpr int RING_PIECE = 2048;  // bytes of operator per stage: four iterations of 32 lanes x 16 bytes
+constexpr int RING_COLS = 64;     // column offsets of a target's first blocks, kept in shared memory for the producer lane
+template <int R, int NRHS>
+__host__ __device__ constexpr int ring_stage_bytes() {  // operator piece + the 4 * (64 / R) source coefficients it multiplies, per right-hand side
+    return RING_PIECE + NRHS * 4 * (64 / R) * 8;
+}
+template <int R, int NRHS, int STAGES>
+constexpr int ring_smem_bytes() {
+    return 8 * (STAGES * ring_stage_bytes<R, NRHS>() + STAGES * 8 + RING_COLS * 4);
+}
+
+// One stage of the ring is filled by 1 + NRHS bulk copies that complete on the same mbarrier: 2 KB of operator and, for
+// every right-hand side, the slice of x_B that those 2 KB multiply.  The source coefficients travel with the operator
+// because a separate gather (L1 hit rate ~30 %) queues behind the ~190 KB of operator that each SM keeps in flight and
+// then costs more than the whole piece does.
+template <int R, int NRHS, int STAGES>
+__global__ void __launch_bounds__(256, 3) bsr_apply_sym_ring_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
+                                                                    size_t xstride, double* __restrict__ scr, size_t sstride,
+                                                                    double sign) {
+    constexpr int PAIRS = R * R / 2, ITERS = PAIRS / 32, CH = 4, PPB = ITERS / CH;  // pieces per block
+    constexpr int S_STEP = 64 / R, XB = CH * S_STEP * 8, STAGE = ring_stage_bytes<R, NRHS>();
+    constexpr bool LAZY = NRHS >= 3;
+    static_assert(64 % R == 0 && PAIRS % 32 == 0 && ITERS % CH == 0, "lane -> target pair must be loop invariant");
+    static_assert(XB % 16 == 0 && STAGE % 16 == 0, "bulk copies move multiples of 16 bytes");
+    extern __shared__ __align__(128) unsigned char ring_smem[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 8 + wid;
+    if (g >= m.groups) return;  // warps are independent: no CTA-wide barrier below
+    unsigned char* ring = ring_smem + (size_t)wid * STAGES * STAGE;
+    const uint32_t ring_a = smem_u32(ring);
+    const uint32_t bar_a = smem_u32(ring_smem + 8 * STAGES * STAGE + wid * STAGES * 8);
+    int* cols = reinterpret_cast<int*>(ring_smem + 8 * STAGES * STAGE + 8 * STAGES * 8) + wid * RING_COLS;
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const uint64_t pol = stream_policy();
+    const unsigned char* __restrict__ src = reinterpret_cast<const unsigned char*>(A + (ne ? m.blk_off[e0] : 0));
+    const int npieces = ne * PPB;
+#pragma unroll
+    for (int k = 0; k < RING_COLS; k += 32)
+        if (k + lane < ne) cols[k + lane] = m.col_off[e0 + k + lane];
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar_a + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    // producer (lane 0): piece q of this target -> stage q % STAGES
+    auto fill = [&](int q, int stage) {
+        const int e = q / PPB, it = (q - e * PPB) * CH;
+        const int col = e < RING_COLS ? cols[e] : m.col_off[e0 + e];
+        const uint32_t dst = ring_a + stage * STAGE, bar = bar_a + 8 * stage;
+        mbar_expect_tx(bar, STAGE);
+        bulk_g2s(dst, src + (size_t)q * RING_PIECE, RING_PIECE, bar, pol);
+#pragma unroll
+        for (int r = 0; r < NRHS; ++r) bulk_g2s_keep(dst + RING_PIECE + r * XB, x + r * xstride + col + it * S_STEP, XB, bar);
+    };
+    if (lane == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+            if (s < npieces) fill(s, s);
+    }
+    const int s_lane = (2 * lane) / R, t0 = (2 * lane) % R;
+    const int self = m.row_off[g];
+    double xa0[NRHS], xa1[NRHS], acc0[NRHS], acc1[NRHS];
+#pragma unroll
+    for (int r = 0; r < NRHS; ++r) {
+        xa0[r] = __ldg(x + r * xstride + self + t0);
+        xa1[r] = __ldg(x + r * xstride + self + t0 + 1);
+        acc0[r] = acc1[r] = 0;
+    }
+    int piece = 0, stage = 0;
+    uint32_t parity = 0;
+    for (int eb = 0; eb < ne; eb += 32) {
+        const int cnt = min(32, ne - eb);
+        const int mymir = lane < cnt ? m.mirror_row[e0 + eb + lane] : -1;
+        for (int j = 0; j < cnt; ++j) {
+            const int m0 = __shfl_sync(0xffffffffu, mymir, j);
+#pragma unroll 1
+            for (int it0 = 0; it0 < ITERS; it0 += CH, ++piece) {
+                mbar_wait(bar_a + 8 * stage, parity);
+                const unsigned char* sp = ring + stage * STAGE;
+                double2 a0[CH];
+#pragma unroll
+                for (int u = 0; u < CH; ++u) a0[u] = reinterpret_cast<const double2*>(sp)[u * 32 + lane];
+                auto refill = [&]() {
+                    __syncwarp();  // every lane has read what it needs from this stage
+                    if (lane == 0 && piece + STAGES < npieces) {
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        fill(piece + STAGES, stage);
+                    }
+                };
+                if (LAZY) {  // many right-hand sides: x_B is read from the stage as it is used, the stage is released afterwards
+#pragma unroll
+                    for (int r = 0; r < NRHS; ++r) {
+                        double xs[CH];
+#pragma unroll
+                        for (int u = 0; u < CH; ++u) xs[u] = reinterpret_cast<const double*>(sp + RING_PIECE + r * XB)[u * S_STEP + s_lane];
+                        sym_consume_x<R>(a0, xs, it0, xa0[r], xa1[r], m0, lane, s_lane, sign, acc0[r], acc1[r], scr + r * sstride);
+                    }
+                    refill();
+                } else {
+                    double xs[NRHS][CH];
+#pragma unroll
+                    for (int r = 0; r < NRHS; ++r)
+#pragma unroll
+                        for (int u = 0; u < CH; ++u)
+                            xs[r][u] = reinterpret_cast<const double*>(sp + RING_PIECE + r * XB)[u * S_STEP + s_lane];
+                    refill();
+#pragma unroll
+                    for (int r = 0; r < NRHS; ++r)
+                        sym_consume_x<R>(a0, xs[r], it0, xa0[r], xa1[r], m0, lane, s_lane, sign, acc0[r], acc1[r], scr + r * sstride);
+                }
+                if (++stage == STAGES) {
+                    stage = 0;
+                    parity ^= 1;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < NRHS; ++r) {
+        double v0 = acc0[r], v1 = acc1[r];
+#pragma unroll
+        for (int off = 16; off >= R / 2; off >>= 1) {
+            v0 += __shfl_down_sync(0xffffffffu, v0, off);
+            v1 += __shfl_down_sync(0xffffffffu, v1, off);
+        }
+        if (lane < R / 2) {
+            double* __restrict__ out = scr + r * sstride + (size_t)m.srow_ptr[g] * R + 2 * lane;
+            out[0] = v0;
+            out[1] = v1;
+        }
+    }
+}
+
+template <int R, int NRHS>
+static void launch_ring(const DevCSR& m, const double* A, const double* x, size_t xstride, double* scr, size_t sstride, double sign,
+                        cudaStream_t st) {
+    constexpr int STAGES = 3;  // 3 CTAs x (8 warps x 3 stages x ~2.3 KB) per SM
+    static bool once = false;  // per instantiation
+    if (!once) {
+        cudaFuncSetAttribute(bsr_apply_sym_ring_kernel<R, NRHS, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             ring_smem_bytes<R, NRHS, STAGES>());
+        once = true;
+    }
+    bsr_apply_sym_ring_kernel<R, NRHS, STAGES>
+        <<<(m.groups + 7) / 8, 256, ring_smem_bytes<R, NRHS, STAGES>(), st>>>(m, A, x, xstride, scr, sstride, sign);
+}
+
 template <int R>
 static void launch_multi_R(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
                            double sign, cudaStream_t st) {
@@ -287,7 +510,13 @@ static void launch_multi_R(const DevCSR& m, const double* A, const double* x, si
         const int c = nrhs - r >= 4 ? 4 : nrhs - r == 3 ? 3 : nrhs - r == 2 ? 2 : 1;
         const double* xr = x + (size_t)r * xstride;
         double* sr = scr + (size_t)r * sstride;
-        if (c == 4) bsr_apply_sym_multi_kernel<R, 4><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
+        static const bool regs = getenv("ANISO_STREAM_REGS") != nullptr;  // A/B switch: register-held loads instead of the TMA ring
+        if (!regs) {
+            if (c == 4) launch_ring<R, 4>(m, A, xr, xstride, sr, sstride, sign, st);
+            else if (c == 3) launch_ring<R, 3>(m, A, xr, xstride, sr, sstride, sign, st);
+            else if (c == 2) launch_ring<R, 2>(m, A, xr, xstride, sr, sstride, sign, st);
+            else launch_ring<R, 1>(m, A, xr, xstride, sr, sstride, sign, st);
+        } else if (c == 4) bsr_apply_sym_multi_kernel<R, 4><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
         else if (c == 3) bsr_apply_sym_multi_kernel<R, 3><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
         else if (c == 2) bsr_apply_sym_multi_kernel<R, 2><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
         else bsr_apply_sym_multi_kernel<R, 1><<<ctas, 256, 0, st>>>(m, A, xr, xstride, sr, sstride, sign);
@@ -444,7 +673,10 @@ void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double*
     if (m.nrows_total == 0) return;
     const unsigned warps_per_cta = 8, ctas = (m.groups + warps_per_cta - 1) / warps_per_cta;
     if (m.symmetric) {
-        if (m.uniform_block == 16) bsr_apply_sym_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        static const bool ring = getenv("ANISO_STREAM_TMA") != nullptr;  // A/B switch: TMA ring for the single-RHS stream too
+        if (ring && m.uniform_block == 16) launch_ring<16, 1>(m, A, x, 0, m.scratch, 0, sign, st);
+        else if (ring && m.uniform_block == 64) launch_ring<64, 1>(m, A, x, 0, m.scratch, 0, sign, st);
+        else if (m.uniform_block == 16) bsr_apply_sym_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, sign);
         else if (m.uniform_block == 64) bsr_apply_sym_kernel<64><<<ctas, 256, 0, st>>>(m, A, x, sign);
         else if (m.uniform_block == 25) bsr_apply_symg_kernel<25><<<ctas, 256, 0, st>>>(m, A, x, sign);
         else if (m.uniform_block == 36) bsr_apply_symg_kernel<36><<<ctas, 256, 0, st>>>(m, A, x, sign);
