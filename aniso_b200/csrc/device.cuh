@@ -31,6 +31,7 @@ struct DevCSR {
     int64_t* blk_off = nullptr;
     int *tgt_node = nullptr, *src_node = nullptr, *grow_ptr = nullptr, *row_group = nullptr;
     int symmetric = 0, scratch_rows = 0;                       // symmetric storage, see plan.hpp
+    int swz = 0;  // 16 x 16 blocks stored bank-swizzled: element (s, t) at s*16 + (t ^ 4*(s%4)), see stream.cu (DMMA kernel)
     int *mirror_row = nullptr, *srow_ptr = nullptr;
     int* group_of_node = nullptr;                              // tree node -> group (or -1)
     int2* node_rows = nullptr;                                 // tree node -> [first, last) scratch row (empty without a group)

@@ -260,7 +260,8 @@ __global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, 
         double* __restrict__ out = A + s_blk[j];
         const int total = nrow * ncol;
         for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-            const int t = NR ? idx % NR : idx % nrow, s = NR ? idx / NR : idx / nrow;
+            const int s = NR ? idx / NR : idx / nrow;
+            const int t = (NR ? idx % NR : idx % nrow) ^ (m.swz ? (s & 3) << 2 : 0);  // idx is the stored position
             double ax, ay, bx, by;
             if (cheb) {  // flat = j*np + i, y slow (bbfmm.h:787-800)
                 const double* __restrict__ gg = s_geo[j];
@@ -314,7 +315,7 @@ __global__ void __launch_bounds__(256) fill_from_base_kernel(DevCSR m, DevTree T
         const int total = nrow * ncol;
         for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
             const double base = in[idx];
-            const int t = idx % nrow, s = idx / nrow;
+            const int s = idx / nrow, t = (idx % nrow) ^ (m.swz ? (s & 3) << 2 : 0);
             double ax, ay, bx, by;
             if (cheb) {
                 const double* __restrict__ gg = s_geo[j];

@@ -109,6 +109,20 @@ __global__ void __launch_bounds__(256) bsr_apply_warp_kernel(DevCSR m, const dou
     }
 }
 
+// Swizzled storage of 16 x 16 blocks (DevCSR::swz): element (s, t) sits at s*16 + (t ^ 4*(s%4)), so that the 8 x 4 and
+// 4 x 8 fragment reads of the DMMA kernel below are free of shared-memory bank conflicts.  For the row-streaming kernels
+// this only renames the target pair a lane works on: lane (q = lane/8, c = lane%8) holds pair c ^ 2q in every iteration.
+template <int R>
+__device__ __forceinline__ int sym_t0(int lane, int swz) {
+    return R == 16 && swz ? 2 * ((lane & 7) ^ (2 * (lane >> 3))) : (2 * lane) % R;
+}
+// before the final reduction over the lanes of a target pair: bring pair c back to lane position c of each group of 8
+template <int R>
+__device__ __forceinline__ double sym_unswizzle(double v, int lane, int swz) {
+    if (R != 16 || !swz) return v;
+    return __shfl_sync(0xffffffffu, v, (lane & 24) | ((lane & 7) ^ (2 * (lane >> 3))));
+}
+
 // One block's worth of work for the symmetric kernel, iterations [it0, it0+4) already loaded into a[].
 // Forward part: acc += K x_B.  Transposed part (paired blocks): the four partial products of this chunk are reduced
 // over the LG lanes that share a source index with a butterfly that halves the live values at every step (2 + 1
@@ -173,7 +187,7 @@ __global__ void __launch_bounds__(256, 4) bsr_apply_sym_kernel(DevCSR m, const d
     const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
     const uint64_t pol = stream_policy();
     const double2* __restrict__ base = reinterpret_cast<const double2*>(A + (ne ? m.blk_off[e0] : 0));
-    const int s_lane = (2 * lane) / R, t0 = (2 * lane) % R;
+    const int s_lane = (2 * lane) / R, t0 = sym_t0<R>(lane, m.swz);
     const int self = m.row_off[g];
     const double xa0 = __ldg(x + self + t0), xa1 = __ldg(x + self + t0 + 1);
     double* __restrict__ scratch = m.scratch;
@@ -213,8 +227,8 @@ __global__ void __launch_bounds__(256, 4) bsr_apply_sym_kernel(DevCSR m, const d
             }
         }
     }
-    acc0 += acc2;
-    acc1 += acc3;
+    acc0 = sym_unswizzle<R>(acc0 + acc2, lane, m.swz);
+    acc1 = sym_unswizzle<R>(acc1 + acc3, lane, m.swz);
 #pragma unroll
     for (int off = 16; off >= R / 2; off >>= 1) {
         acc0 += __shfl_down_sync(0xffffffffu, acc0, off);
@@ -244,7 +258,7 @@ __global__ void __launch_bounds__(256, NRHS <= 2 ? 3 : 2) bsr_apply_sym_multi_ke
     const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
     const uint64_t pol = stream_policy();
     const double2* __restrict__ base = reinterpret_cast<const double2*>(A + (ne ? m.blk_off[e0] : 0));
-    const int s_lane = (2 * lane) / R, t0 = (2 * lane) % R;
+    const int s_lane = (2 * lane) / R, t0 = sym_t0<R>(lane, m.swz);
     const int self = m.row_off[g];
     double xa0[NRHS], xa1[NRHS], acc0[NRHS], acc1[NRHS];
 #pragma unroll
@@ -299,7 +313,7 @@ __global__ void __launch_bounds__(256, NRHS <= 2 ? 3 : 2) bsr_apply_sym_multi_ke
     }
 #pragma unroll
     for (int r = 0; r < NRHS; ++r) {
-        double v0 = acc0[r], v1 = acc1[r];
+        double v0 = sym_unswizzle<R>(acc0[r], lane, m.swz), v1 = sym_unswizzle<R>(acc1[r], lane, m.swz);
 #pragma unroll
         for (int off = 16; off >= R / 2; off >>= 1) {
             v0 += __shfl_down_sync(0xffffffffu, v0, off);
@@ -413,7 +427,7 @@ __global__ void __launch_bounds__(256, 3) bsr_apply_sym_ring_kernel(DevCSR m, co
         for (int s = 0; s < STAGES; ++s)
             if (s < npieces) fill(s, s);
     }
-    const int s_lane = (2 * lane) / R, t0 = (2 * lane) % R;
+    const int s_lane = (2 * lane) / R, t0 = sym_t0<R>(lane, m.swz);
     const int self = m.row_off[g];
     double xa0[NRHS], xa1[NRHS], acc0[NRHS], acc1[NRHS];
 #pragma unroll
@@ -473,7 +487,7 @@ __global__ void __launch_bounds__(256, 3) bsr_apply_sym_ring_kernel(DevCSR m, co
     }
 #pragma unroll
     for (int r = 0; r < NRHS; ++r) {
-        double v0 = acc0[r], v1 = acc1[r];
+        double v0 = sym_unswizzle<R>(acc0[r], lane, m.swz), v1 = sym_unswizzle<R>(acc1[r], lane, m.swz);
 #pragma unroll
         for (int off = 16; off >= R / 2; off >>= 1) {
             v0 += __shfl_down_sync(0xffffffffu, v0, off);
@@ -499,6 +513,186 @@ static void launch_ring(const DevCSR& m, const double* A, const double* x, size_
     }
     bsr_apply_sym_ring_kernel<R, NRHS, STAGES>
         <<<(m.groups + 7) / 8, 256, ring_smem_bytes<R, NRHS, STAGES>(), st>>>(m, A, x, xstride, scr, sstride, sign);
+}
+
+// ---- multi-RHS stream on the FP64 tensor cores (16 x 16 blocks, swizzled storage) -----------------------------------
+// With up to eight right-hand sides the two products of a block are small GEMMs,
+//   forward     Y[rhs][t] += sum_s X_B[rhs][s] * A[s][t]         (8 x 16) = (8 x 16)(16 x 16)
+//   transposed  Z[s][rhs]  = sum_t A[s][t]     * X_A[rhs][t]     (16 x 8) = (16 x 16)(16 x 8)
+// i.e. 8 + 8 mma.m8n8k4.f64 per 2 KB block whatever the number of right-hand sides, instead of ~55 instructions per block
+// AND right-hand side in the DFMA / butterfly form above.  The block is read from the ring stage twice, once as the
+// B operand (4 x 8 fragments: lane l holds A[s = 4 sb + l%4][t = 8 tb + l/4]) and once as the A operand (8 x 4 fragments:
+// lane l holds A[s = 8 sg + l/4][t = 4 tq + l%4]); the storage swizzle t ^ 4 (s%4) makes both reads conflict-free.
+// Results need no cross-lane reduction: the accumulator fragments are written straight to the scratch rows.
+__device__ __forceinline__ void dmma884(double2& c, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};" : "+d"(c.x), "+d"(c.y) : "d"(a), "d"(b));
+}
+
+constexpr int MMA_STAGE = RING_PIECE + 8 * 128;  // a block and the x_B slices of up to eight right-hand sides
+#define ANISO_PIN(v) asm volatile("" : "+r"(v))  // keep a lane-derived value in its register instead of recomputing it per block
+#define ANISO_PIN64(v) asm volatile("" : "+l"(v))
+
+template <int STAGES>
+__global__ void __launch_bounds__(256, 3) bsr_apply_sym_mma_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
+                                                                   size_t xstride, int nrhs, double* __restrict__ scr, size_t sstride,
+                                                                   double sign) {
+    constexpr int R = 16, STAGE = MMA_STAGE;
+    extern __shared__ __align__(128) unsigned char ring_smem[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 8 + wid;
+    if (g >= m.groups) return;  // warps are independent: no CTA-wide barrier below
+    unsigned char* ring = ring_smem + (size_t)wid * STAGES * STAGE;
+    uint32_t ring_a = smem_u32(ring);
+    uint32_t bar_a = smem_u32(ring_smem + 8 * STAGES * STAGE + wid * STAGES * 8);
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    // x_B area of a stage: [s-block sb][rhs 0..7][4 doubles], so that lane l reads doubles sb*32 + l (no bank conflicts,
+    // one base register).  Rows of right-hand sides >= nrhs are never written by a copy and stay zero.
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) reinterpret_cast<double*>(ring + s * STAGE + RING_PIECE)[k * 32 + lane] = 0.0;
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar_a + 8 * s, 33);  // lane 0's expect_tx + one cp.async arrival per lane
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+    // Producers: lane 0 has the copy engine fetch the 2 KB block (evict-first: it is never read again); the x_B slices the
+    // block multiplies (128 bytes per right-hand side) are fetched 16 bytes per lane with cp.async, whose completion arrives
+    // on the same mbarrier.  (One bulk copy per right-hand side costs ~15 serialised instructions each: UBLKCP takes its
+    // operands from uniform registers.)  A stage is refilled only after the DMMAs that consumed it were issued, i.e. after
+    // its shared-memory reads have returned, so no proxy fence is needed between the reads and the refill.
+    const unsigned char* __restrict__ src = reinterpret_cast<const unsigned char*>(A + (ne ? m.blk_off[e0] : 0));
+    const uint64_t pol = stream_policy();
+    // chunk c = lane (+ 32): rhs c / 8, doubles 2 (c % 8) .. + 1 of the slice, i.e. s-block (c % 8) / 2, half (c % 8) % 2
+    const double* __restrict__ xc0 = x + (size_t)(lane >> 3) * xstride + 2 * (lane & 7);
+    const double* __restrict__ xc1 = xc0 + 4 * xstride;
+    uint32_t xdst = RING_PIECE + ((lane & 7) >> 1) * 256 + (lane >> 3) * 32 + (lane & 1) * 16;  // second chunk: + 4 * 32
+    int c_ok = (lane < nrhs * 8 ? 1 : 0) | (lane + 32 < nrhs * 8 ? 2 : 0);
+    ANISO_PIN64(xc0); ANISO_PIN64(xc1); ANISO_PIN(xdst); ANISO_PIN(c_ok); ANISO_PIN(ring_a); ANISO_PIN(bar_a);
+    auto fill = [&](int q, int stage, int col) {  // block q of this target -> stage
+        const uint32_t dst = ring_a + stage * STAGE, bar = bar_a + 8 * stage;
+        if (lane == 0) {
+            mbar_expect_tx(bar, RING_PIECE);
+            bulk_g2s(dst, src + (size_t)q * RING_PIECE, RING_PIECE, bar, pol);
+        }
+        if (c_ok & 1) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + xdst), "l"(xc0 + col) : "memory");
+        if (c_ok & 2) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + xdst + 128), "l"(xc1 + col) : "memory");
+        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+    };
+    // column offsets / mirror rows of 32 blocks per lane-batch; the batch after the current one is loaded a batch early
+    int mycol = lane < ne ? m.col_off[e0 + lane] : 0;
+    int mycol_n = 32 + lane < ne ? m.col_off[e0 + 32 + lane] : 0;
+    int mymir = lane < ne ? m.mirror_row[e0 + lane] : -1;
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) {
+        const int col = __shfl_sync(0xffffffffu, mycol, s);
+        if (s < ne) fill(s, s, col);
+    }
+    const int lr = lane >> 2, lc = lane & 3;  // fragment row / column of this lane
+    const int self = m.row_off[g];
+    double xa[4];  // B operand of the transposed product: sign * X_A[rhs = lr][t = 4 tq + lc]
+#pragma unroll
+    for (int tq = 0; tq < 4; ++tq) xa[tq] = lr < nrhs ? sign * __ldg(x + lr * xstride + self + 4 * tq + lc) : 0.0;
+    double2 accf[2] = {make_double2(0, 0), make_double2(0, 0)};  // Y[rhs = lr][t = 8 tb + 2 lc + {0, 1}]
+    // byte offsets of this lane's fragment elements inside a stage (storage swizzle: t ^ 4 (s % 4))
+    uint32_t offb[2], offa[4];
+#pragma unroll
+    for (int tb = 0; tb < 2; ++tb) {  // + 512 sb: s = 4 sb + lc, t = 8 tb + lr
+        offb[tb] = 8 * (lc * 16 + ((8 * tb + lr) ^ (4 * lc)));
+        ANISO_PIN(offb[tb]);
+    }
+#pragma unroll
+    for (int tq = 0; tq < 4; ++tq) {  // + 1024 sg: s = 8 sg + lr, t = 4 tq + lc
+        offa[tq] = 8 * (lr * 16 + ((4 * tq + lc) ^ (4 * (lr & 3))));
+        ANISO_PIN(offa[tq]);
+    }
+    uint32_t offx = RING_PIECE + 8 * lane;
+    ANISO_PIN(offx);
+    // transposed-product accumulator fragment: Z[s = 8 sg + lr][rhs = 2 lc + {0, 1}]
+    double* z0 = scr + (size_t)(2 * lc) * sstride + lr;
+    double* z1 = z0 + sstride;
+    int z_ok = (2 * lc < nrhs ? 1 : 0) | (2 * lc + 1 < nrhs ? 2 : 0);
+    ANISO_PIN64(z0); ANISO_PIN64(z1); ANISO_PIN(z_ok);
+    int stage = 0;
+    uint32_t parity = 0;
+    for (int eb = 0; eb < ne; eb += 32) {
+        const int cnt = min(32, ne - eb);
+        if (eb) {
+            mycol = mycol_n;
+            mycol_n = eb + 32 + lane < ne ? m.col_off[e0 + eb + 32 + lane] : 0;
+            mymir = lane < cnt ? m.mirror_row[e0 + eb + lane] : -1;
+        }
+        for (int j = 0; j < cnt; ++j) {
+            const int q = eb + j;
+            const int m0 = __shfl_sync(0xffffffffu, mymir, j);
+            const int jn = j + STAGES;
+            const int c_a = __shfl_sync(0xffffffffu, mycol, jn & 31), c_b = __shfl_sync(0xffffffffu, mycol_n, jn & 31);
+            const int col = jn < 32 ? c_a : c_b;
+            mbar_wait(bar_a + 8 * stage, parity);
+            const unsigned char* __restrict__ sp = ring + stage * STAGE;
+            double xb[4], fb[4][2];
+#pragma unroll
+            for (int sb = 0; sb < 4; ++sb) {
+                xb[sb] = *reinterpret_cast<const double*>(sp + offx + 256 * sb);
+#pragma unroll
+                for (int tb = 0; tb < 2; ++tb) fb[sb][tb] = *reinterpret_cast<const double*>(sp + offb[tb] + 512 * sb);
+            }
+            if (m0 >= 0) {  // warp-uniform; four independent accumulator chains
+                double za[4][2];
+#pragma unroll
+                for (int tq = 0; tq < 4; ++tq)
+#pragma unroll
+                    for (int sg = 0; sg < 2; ++sg) za[tq][sg] = *reinterpret_cast<const double*>(sp + offa[tq] + 1024 * sg);
+                double2 z[2] = {make_double2(0, 0), make_double2(0, 0)};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    dmma884(accf[0], xb[k], fb[k][0]);
+                    dmma884(accf[1], xb[k], fb[k][1]);
+                    dmma884(z[0], za[k][0], xa[k]);
+                    dmma884(z[1], za[k][1], xa[k]);
+                }
+                const size_t zo = (size_t)m0 * R;
+                if (z_ok & 1) {
+                    z0[zo] = z[0].x;
+                    z0[zo + 8] = z[1].x;
+                }
+                if (z_ok & 2) {
+                    z1[zo] = z[0].y;
+                    z1[zo + 8] = z[1].y;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    dmma884(accf[0], xb[k], fb[k][0]);
+                    dmma884(accf[1], xb[k], fb[k][1]);
+                }
+            }
+            __syncwarp();  // every lane has read what it needs from this stage
+            if (q + STAGES < ne) fill(q + STAGES, stage, col);
+            if (++stage == STAGES) {
+                stage = 0;
+                parity ^= 1;
+            }
+        }
+    }
+    if (lr < nrhs) {
+        double* __restrict__ out = scr + lr * sstride + (size_t)m.srow_ptr[g] * R + 2 * lc;
+#pragma unroll
+        for (int tb = 0; tb < 2; ++tb) *reinterpret_cast<double2*>(out + 8 * tb) = accf[tb];
+    }
+}
+
+static void launch_mma(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
+                       double sign, cudaStream_t st) {
+    constexpr int STAGES = 3, SMEM = 8 * (STAGES * MMA_STAGE + STAGES * 8);
+    static bool once = false;
+    if (!once) {
+        cudaFuncSetAttribute(bsr_apply_sym_mma_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        once = true;
+    }
+    bsr_apply_sym_mma_kernel<STAGES><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, xstride, nrhs, scr, sstride, sign);
 }
 
 template <int R>
@@ -527,6 +721,17 @@ static void launch_multi_R(const DevCSR& m, const double* A, const double* x, si
 int launch_bsr_apply_multi(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
                            double sign, cudaStream_t st) {
     if (m.groups == 0 || nrhs == 0) return 0;
+    static const bool no_mma = getenv("ANISO_NO_DMMA") != nullptr;  // A/B switch: DFMA / butterfly form
+    if (m.uniform_block == 16 && m.swz && !no_mma) {  // tensor-core form: up to eight right-hand sides per pass
+        int launches = 0;
+        for (int r = 0; r < nrhs; r += 8, ++launches) {
+            const int c = nrhs - r < 8 ? nrhs - r : 8;
+            const double* xr = x + (size_t)r * xstride;
+            double* sr = scr + (size_t)r * sstride;
+            launch_mma(m, A, xr, xstride, c, sr, sstride, sign, st);
+        }
+        return launches;
+    }
     if (m.uniform_block == 16) launch_multi_R<16>(m, A, x, xstride, nrhs, scr, sstride, sign, st);
     else launch_multi_R<64>(m, A, x, xstride, nrhs, scr, sstride, sign, st);
     return (nrhs + 3) / 4;
