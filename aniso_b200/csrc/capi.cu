@@ -170,7 +170,7 @@ DevCSR upload_csr(aniso_handle* h, const BlockCSR& b) {
     d.grow_ptr = upload(h, b.grow_ptr);
     d.row_group = upload(h, b.row_group);
     d.symmetric = b.symmetric ? 1 : 0;
-    static const bool no_swz = getenv("ANISO_NO_SWIZZLE") != nullptr;  // A/B switch
+    const bool no_swz = getenv("ANISO_NO_SWIZZLE") != nullptr;  // A/B switch
     d.swz = b.symmetric && b.uniform_block == 16 && !no_swz;
     d.scratch_rows = b.scratch_rows;
     if (b.symmetric) {

@@ -704,7 +704,7 @@ static void launch_multi_R(const DevCSR& m, const double* A, const double* x, si
         const int c = nrhs - r >= 4 ? 4 : nrhs - r == 3 ? 3 : nrhs - r == 2 ? 2 : 1;
         const double* xr = x + (size_t)r * xstride;
         double* sr = scr + (size_t)r * sstride;
-        static const bool regs = getenv("ANISO_STREAM_REGS") != nullptr;  // A/B switch: register-held loads instead of the TMA ring
+        const bool regs = getenv("ANISO_STREAM_REGS") != nullptr;  // A/B switch: register-held loads instead of the TMA ring
         if (!regs) {
             if (c == 4) launch_ring<R, 4>(m, A, xr, xstride, sr, sstride, sign, st);
             else if (c == 3) launch_ring<R, 3>(m, A, xr, xstride, sr, sstride, sign, st);
@@ -721,7 +721,7 @@ static void launch_multi_R(const DevCSR& m, const double* A, const double* x, si
 int launch_bsr_apply_multi(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
                            double sign, cudaStream_t st) {
     if (m.groups == 0 || nrhs == 0) return 0;
-    static const bool no_mma = getenv("ANISO_NO_DMMA") != nullptr;  // A/B switch: DFMA / butterfly form
+    const bool no_mma = getenv("ANISO_NO_DMMA") != nullptr;  // A/B switch: DFMA / butterfly form
     if (m.uniform_block == 16 && m.swz && !no_mma) {  // tensor-core form: up to eight right-hand sides per pass
         int launches = 0;
         for (int r = 0; r < nrhs; r += 8, ++launches) {
@@ -878,7 +878,7 @@ void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double*
     if (m.nrows_total == 0) return;
     const unsigned warps_per_cta = 8, ctas = (m.groups + warps_per_cta - 1) / warps_per_cta;
     if (m.symmetric) {
-        static const bool ring = getenv("ANISO_STREAM_TMA") != nullptr;  // A/B switch: TMA ring for the single-RHS stream too
+        const bool ring = getenv("ANISO_STREAM_REGS") == nullptr;  // A/B switch: register-held loads instead of the TMA ring
         if (ring && m.uniform_block == 16) launch_ring<16, 1>(m, A, x, 0, m.scratch, 0, sign, st);
         else if (ring && m.uniform_block == 64) launch_ring<64, 1>(m, A, x, 0, m.scratch, 0, sign, st);
         else if (m.uniform_block == 16) bsr_apply_sym_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, sign);

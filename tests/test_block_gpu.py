@@ -115,4 +115,11 @@ def test_batched_block_operator_matches_the_loop(cfg, monkeypatch):
     launches_loop = a.launch_count() - launches_batched
     assert rel(fw, fw_loop) < 1e-12 and rel(mf, mf_loop) < 1e-12
     assert launches_loop > 2 * (launches_batched - 2 * (2 * K - 1) * 4)  # the batched form really is the shorter one
+    # 16 x 16 blocks: the batched form above ran on the FP64 tensor cores (mma.m8n8k4); the DFMA / butterfly form of the
+    # same multi-RHS stream must agree with it
+    monkeypatch.delenv("ANISO_BLOCK_LOOP", raising=False)
+    monkeypatch.setenv("ANISO_NO_DMMA", "1")
+    assert rel(a.forward(u), fw) < 1e-13 and rel(a.mforward(u), mf) < 1e-13
+    monkeypatch.setenv("ANISO_STREAM_REGS", "1")  # ... and with register-held loads instead of the TMA ring
+    assert rel(a.forward(u), fw) < 1e-13
     a.delete()

@@ -246,3 +246,38 @@ def test_fast_paths_match_plain_paths_at_baseline_sizes(cfg, kid, monkeypatch):
     if gm_fast is not None:
         assert gm_fast[1] == gm_plain[1] == 0 and gm_fast[2] == gm_plain[2]
         assert rel(gm_fast[0], gm_plain[0]) < 1e-9
+
+
+@pytest.mark.parametrize("cfg", [
+    (512, 1, 2, 0.9, 10, 4, 20, "layers"),    # 16 x 16 blocks: bank-swizzled storage
+    (256, 1, 2, 0.9, 10, 8, 20, "hetero"),    # 64 x 64 blocks
+])
+def test_stream_kernel_variants_agree(cfg, monkeypatch):
+    """The operator stream has three forms over the same symmetric storage: fed by the copy engine into a shared-memory ring
+    (default), with register-held loads (ANISO_STREAM_REGS), and, for 16 x 16 blocks, over the unswizzled block layout
+    (ANISO_NO_SWIZZLE, read when the operators are planned).  Same inputs, results equal up to summation order."""
+    from aniso_b200 import Aniso
+
+    sz, deg, K, g, sr, np_, ml, kind = cfg
+
+    def run(env):
+        for k in ("ANISO_STREAM_REGS", "ANISO_NO_SWIZZLE"):
+            monkeypatch.delenv(k, raising=False)
+        for k in env:
+            monkeypatch.setenv(k, "1")
+        a = Aniso(sz, deg, K, g, sr, np_, ml)
+        x, y, w = a.nodes()
+        ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+        a.setCoeff(ss, st)
+        f = cases.random_source(x.size, 5) * cases.gaussian_source(x, y) + 0.1 * cases.tilted_source(x, y)
+        out = []
+        for kid in (0, 1):
+            a.cache(kid)
+            out.append(a.mapping(f, kid))
+        a.delete()
+        return np.concatenate(out)
+
+    ring = run(())
+    assert rel(run(("ANISO_STREAM_REGS",)), ring) < 1e-13
+    assert rel(run(("ANISO_NO_SWIZZLE",)), ring) < 1e-13
+    assert rel(run(("ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS")), ring) < 1e-13
