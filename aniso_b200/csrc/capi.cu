@@ -80,6 +80,7 @@ struct aniso_handle {
     double *d_fmm = nullptr, *d_corr = nullptr, *d_a = nullptr, *d_b = nullptr, *d_xfull = nullptr, *d_stage = nullptr;
     double *d_blk_full = nullptr, *d_blk_tmp = nullptr;  // block operator work space
     double *d_blk_q = nullptr, *d_blk_f = nullptr, *d_blk_mc = nullptr, *d_blk_sm = nullptr, *d_blk_sp = nullptr;  // batched form
+    double *d_blk_wq = nullptr, *d_blk_wf = nullptr, *d_blk_wm = nullptr;  // regrouped form: inputs of the (kernel id, output mode) pairs
     double* gm_buf = nullptr;   // Krylov work space, kept between solves ((m+3) vectors + CGS2 partials)
     size_t gm_cap = 0;
     double* pinned_small = nullptr;  // 2048 doubles: Hessenberg column read-back
@@ -1149,13 +1150,90 @@ void block_apply_multi(aniso_handle* h, const double* full, const double* u_own,
         h->launches += launch_up_tree(T, h->G, h->sub, h->d_blk_q + (size_t)a * N, h->d_blk_mc + (size_t)a * mc, h->st, nullptr);
     }
     std::vector<const double*> stencil(nk);
+    const double g = h->plan.g, gK = std::pow(g, K);
+    if (h->m2l.swz && h->p2p.swz && K <= 8 && nk <= IdList::MAXI && !getenv("ANISO_NO_DMMA") && !getenv("ANISO_BLOCK_PER_ID")) {
+        // Regrouped by kernel id: out_i = sum_k [ FMM_k + C_k ] w^(i,k),  w^(i,k) = sum_{j: |i+j| = k} chi_|j| f_|j|  (at most two
+        // input modes).  The multipoles, charges and stencil sources of the w's are linear combinations of those of the K
+        // input modes; all kernel ids are then streamed by ONE launch per operator kind that accumulates over k on the fly
+        // (launch_bsr_apply_ids), so each output mode has a single scratch set and the downward pass folds one term.
+        if (!h->d_blk_wq) {
+            h->d_blk_wq = dalloc<double>(h, (size_t)nk * K * N);
+            h->d_blk_wf = dalloc<double>(h, (size_t)nk * K * N);
+            h->d_blk_wm = dalloc<double>(h, (size_t)nk * K * mc);
+            CK(cudaMemsetAsync(h->d_blk_wq, 0, sizeof(double) * nk * K * N, h->st));   // absent (k, i) pairs stay zero
+            CK(cudaMemsetAsync(h->d_blk_wf, 0, sizeof(double) * nk * K * N, h->st));
+            CK(cudaMemsetAsync(h->d_blk_wm, 0, sizeof(double) * nk * K * mc, h->st));
+        }
+        struct Term { int a[2]; double c[2]; int n = 0; };
+        std::vector<Term> W((size_t)nk * K);
+        for (int iid = 0; iid < K; ++iid)
+            for (int j = -(K - 1); j <= K - 1; ++j) {  // the reference's loop (aniso.m:126, 143)
+                const int a = std::abs(j), k = std::abs(-iid - j);
+                const double coef = weighted ? (std::pow(g, a) - gK) / (1.0 - gK) : 1.0;
+                Term& t = W[(size_t)k * K + iid];
+                if (t.n && t.a[0] == a) t.c[0] += coef;
+                else {
+                    t.a[t.n] = a;
+                    t.c[t.n++] = coef;
+                }
+            }
+        LinList Lq, Lf, Lm;
+        for (int k = 0; k < nk; ++k)
+            for (int iid = 0; iid < K; ++iid) {
+                const Term& t = W[(size_t)k * K + iid];
+                if (!t.n) continue;
+                const size_t w = (size_t)k * K + iid;
+                auto add = [&](LinList& L, double* dst, const double* base, size_t stride) {
+                    const int e = L.n++;
+                    L.dst[e] = dst;
+                    L.a[e] = base + t.a[0] * stride;
+                    L.ca[e] = t.c[0];
+                    L.b[e] = t.n > 1 ? base + t.a[1] * stride : nullptr;
+                    L.cb[e] = t.n > 1 ? t.c[1] : 0.0;
+                };
+                add(Lq, h->d_blk_wq + w * N, h->d_blk_q, (size_t)N);
+                add(Lf, h->d_blk_wf + w * N, h->d_blk_f, (size_t)N);
+                add(Lm, h->d_blk_wm + w * mc, h->d_blk_mc, mc);
+            }
+        LAUNCH(h, launch_lincomb(Lq, (size_t)N, h->st));
+        LAUNCH(h, launch_lincomb(Lf, (size_t)N, h->st));
+        LAUNCH(h, launch_lincomb(Lm, mc, h->st));
+        IdList im, ip;
+        for (int k = 0; k < nk; ++k) {
+            OperatorCache& c = ensure_ops(h, k, PART_BOTH);
+            stencil[k] = ensure_stencils(h, k).call;
+            im.A[k] = c.m2l; im.x[k] = h->d_blk_wm + (size_t)k * K * mc; im.sign[k] = c.sign;
+            ip.A[k] = c.p2p; ip.x[k] = h->d_blk_wq + (size_t)k * K * N; ip.sign[k] = c.sign;
+        }
+        im.n = ip.n = nk;
+        LAUNCH(h, launch_bsr_apply_ids(h->m2l, im, mc, K, h->d_blk_sm, Sm, h->st));
+        LAUNCH(h, launch_bsr_apply_ids(h->p2p, ip, (size_t)N, K, h->d_blk_sp, Sp, h->st));
+        for (int iid = 0; iid < K; ++iid) {
+            FoldList fl;
+            fl.nscr = 1;
+            for (int k = 0; k < nk; ++k) {
+                if (!W[(size_t)k * K + iid].n) continue;
+                const int t = fl.n++;
+                fl.coef[t] = 1.0;
+                fl.m2l_scr[t] = h->d_blk_sm + (size_t)iid * Sm;
+                fl.p2p_scr[t] = h->d_blk_sp + (size_t)iid * Sp;
+                fl.C[t] = stencil[k];
+                fl.f[t] = h->d_blk_wf + ((size_t)k * K + iid) * N;
+            }
+            h->launches += launch_down_mid_tree(T, h->m2l, true, h->sub, h->first_m2l_level, h->d_mpot, h->st, &fl);
+            h->launches += launch_down_leaf_tree(T, h->G, h->m2l, true, h->p2p, true, h->sub, h->first_m2l_level, h->d_leaf_of_slot,
+                                                 h->slot0, n, h->d_mpot, h->d_pot, nullptr, nullptr, u_own + (size_t)iid * n,
+                                                 out + (size_t)iid * n, subtract ? 2 : 1, h->st, &fl);
+        }
+        CK(cudaGetLastError());
+        return;
+    }
     for (int k = 0; k < nk; ++k) {
         OperatorCache& c = ensure_ops(h, k, PART_BOTH);
         stencil[k] = ensure_stencils(h, k).call;
         h->launches += launch_bsr_apply_multi(h->m2l, c.m2l, h->d_blk_mc, mc, K, h->d_blk_sm + (size_t)k * K * Sm, Sm, c.sign, h->st);
         h->launches += launch_bsr_apply_multi(h->p2p, c.p2p, h->d_blk_q, (size_t)N, K, h->d_blk_sp + (size_t)k * K * Sp, Sp, c.sign, h->st);
     }
-    const double g = h->plan.g, gK = std::pow(g, K);
     for (int iid = 0; iid < K; ++iid) {
         FoldList fl;
         for (int j = -(K - 1); j <= K - 1; ++j) {  // the reference's loop order (aniso.m:126, 143)

@@ -102,7 +102,31 @@ struct FoldList {
     const double* p2p_scr[MAXF];
     const double* C[MAXF];  // fused correction stencil of kernel id k_j
     const double* f[MAXF];  // unscaled source of input mode a_j, reference node order
+    int nscr = -1;          // terms that carry scratch sets (the first nscr; -1: all); the others only apply their stencil
 };
+
+// operators of several kernel ids applied in one pass (block operator on the tensor cores, stream.cu): id k multiplies the
+// nrhs vectors x[k] + r * xstride with A[k] (all ids share one block-CSR structure) and everything accumulates into the
+// nrhs result sets
+struct IdList {
+    static constexpr int MAXI = 15;
+    int n = 0;
+    const double* A[MAXI];
+    const double* x[MAXI];
+    double sign[MAXI];
+};
+// dst = ca * a + cb * b (b may be null), n entries of one length
+struct LinList {
+    static constexpr int MAXL = 96;
+    int n = 0;
+    double* dst[MAXL];
+    const double* a[MAXL];
+    const double* b[MAXL];
+    double ca[MAXL], cb[MAXL];
+};
+void launch_lincomb(const LinList& L, size_t len, cudaStream_t st);
+// requires m.swz (16 x 16 blocks, swizzled storage), nrhs <= 8; one launch
+void launch_bsr_apply_ids(const DevCSR& m, const IdList& ids, size_t xstride, int nrhs, double* scr, size_t sstride, cudaStream_t st);
 
 // ---- sub-tree passes for complete uniform trees (subtree.cu) ----
 struct SubtreePlan {

@@ -695,6 +695,180 @@ static void launch_mma(const DevCSR& m, const double* A, const double* x, size_t
     bsr_apply_sym_mma_kernel<STAGES><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, xstride, nrhs, scr, sstride, sign);
 }
 
+// ---- the same, for all kernel ids of a block apply in one launch ------------------------------------------------------
+// out_i = sum_k K_k w^(i,k) (aniso.m:121-156 regrouped by kernel id): the warp of a target walks the operators of all ids
+// one after the other (k-major), the forward accumulators live across the whole walk, and the transposed products of id k
+// are added onto those of the ids before it in the partner's scratch row: plain stores for the first id, red.add for the
+// others.  Each scratch element has exactly one writing thread, which issues its additions in id order, so the sums are
+// deterministic.  One scratch set per output mode instead of one per (id, input mode): K(2K-1) -> K sets written and read.
+template <int STAGES>
+__global__ void __launch_bounds__(256, 3) bsr_apply_sym_mma_ids_kernel(DevCSR m, const __grid_constant__ IdList ids, size_t xstride,
+                                                                       int nrhs, double* __restrict__ scr, size_t sstride) {
+    constexpr int R = 16, STAGE = MMA_STAGE, NCOL = 32;
+    extern __shared__ __align__(128) unsigned char ring_smem[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 8 + wid;
+    if (g >= m.groups) return;  // warps are independent: no CTA-wide barrier below
+    unsigned char* ring = ring_smem + (size_t)wid * STAGES * STAGE;
+    uint32_t ring_a = smem_u32(ring);
+    uint32_t bar_a = smem_u32(ring_smem + 8 * STAGES * STAGE + wid * STAGES * 8);
+    int* cols = reinterpret_cast<int*>(ring_smem + 8 * STAGES * STAGE + 8 * STAGES * 8) + wid * NCOL;
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const int nid = ids.n, npieces = nid * ne;
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) reinterpret_cast<double*>(ring + s * STAGE + RING_PIECE)[k * 32 + lane] = 0.0;
+    if (lane < ne) cols[lane] = m.col_off[e0 + lane];
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar_a + 8 * s, 33);  // lane 0's expect_tx + one cp.async arrival per lane
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+    const size_t blk0 = ne ? (size_t)m.blk_off[e0] : 0;
+    const uint64_t pol = stream_policy();
+    size_t xo0 = (size_t)(lane >> 3) * xstride + 2 * (lane & 7);  // chunk `lane` of the x_B slices (see the kernel above)
+    uint32_t xdst = RING_PIECE + ((lane & 7) >> 1) * 256 + (lane >> 3) * 32 + (lane & 1) * 16;
+    int c_ok = (lane < nrhs * 8 ? 1 : 0) | (lane + 32 < nrhs * 8 ? 2 : 0);
+    ANISO_PIN64(xo0); ANISO_PIN(xdst); ANISO_PIN(c_ok); ANISO_PIN(ring_a); ANISO_PIN(bar_a);
+    int fk = 0, fq = 0, fstage = 0;  // fill cursor: next piece to request = block fq of id fk, into stage fstage
+    auto fill = [&]() {
+        const int col = fq < NCOL ? cols[fq] : m.col_off[e0 + fq];
+        const uint32_t dst = ring_a + fstage * STAGE, bar = bar_a + 8 * fstage;
+        if (lane == 0) {
+            mbar_expect_tx(bar, RING_PIECE);
+            bulk_g2s(dst, reinterpret_cast<const unsigned char*>(ids.A[fk] + blk0) + (size_t)fq * RING_PIECE, RING_PIECE, bar, pol);
+        }
+        const double* __restrict__ xs = ids.x[fk] + xo0 + col;
+        if (c_ok & 1) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + xdst), "l"(xs) : "memory");
+        if (c_ok & 2) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + xdst + 128), "l"(xs + 4 * xstride) : "memory");
+        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+        if (++fq == ne) {
+            fq = 0;
+            ++fk;
+        }
+        if (++fstage == STAGES) fstage = 0;
+    };
+    for (int s = 0; s < STAGES && s < npieces; ++s) fill();
+    const int lr = lane >> 2, lc = lane & 3;  // fragment row / column of this lane
+    const int self = m.row_off[g];
+    double2 accf[2] = {make_double2(0, 0), make_double2(0, 0)};  // Y[rhs = lr][t = 8 tb + 2 lc + {0, 1}]
+    uint32_t offb[2], offa[4];
+#pragma unroll
+    for (int tb = 0; tb < 2; ++tb) {  // + 512 sb: s = 4 sb + lc, t = 8 tb + lr
+        offb[tb] = 8 * (lc * 16 + ((8 * tb + lr) ^ (4 * lc)));
+        ANISO_PIN(offb[tb]);
+    }
+#pragma unroll
+    for (int tq = 0; tq < 4; ++tq) {  // + 1024 sg: s = 8 sg + lr, t = 4 tq + lc
+        offa[tq] = 8 * (lr * 16 + ((4 * tq + lc) ^ (4 * (lr & 3))));
+        ANISO_PIN(offa[tq]);
+    }
+    uint32_t offx = RING_PIECE + 8 * lane;
+    ANISO_PIN(offx);
+    double* z0 = scr + (size_t)(2 * lc) * sstride + lr;  // transposed-product fragment: Z[s = 8 sg + lr][rhs = 2 lc + {0, 1}]
+    double* z1 = z0 + sstride;
+    int z_ok = (2 * lc < nrhs ? 1 : 0) | (2 * lc + 1 < nrhs ? 2 : 0);
+    ANISO_PIN64(z0); ANISO_PIN64(z1); ANISO_PIN(z_ok);
+    const size_t xa_off = (size_t)lr * xstride + self + lc;
+    double xa[4];  // B operand of the transposed product of the current id: sign_k * X_A[rhs = lr][t = 4 tq + lc]
+#pragma unroll
+    for (int tq = 0; tq < 4; ++tq) xa[tq] = lr < nrhs && nid ? ids.sign[0] * __ldg(ids.x[0] + xa_off + 4 * tq) : 0.0;
+    int mymir = lane < ne ? m.mirror_row[e0 + lane] : -1;
+    int stage = 0, piece = 0;
+    uint32_t parity = 0;
+    for (int k = 0; k < nid; ++k) {
+        double xan[4] = {0, 0, 0, 0};  // the next id's, fetched while this id streams
+        if (k + 1 < nid && lr < nrhs) {
+#pragma unroll
+            for (int tq = 0; tq < 4; ++tq) xan[tq] = ids.sign[k + 1] * __ldg(ids.x[k + 1] + xa_off + 4 * tq);
+        }
+        for (int eb = 0; eb < ne; eb += 32) {
+            const int cnt = min(32, ne - eb);
+            if (ne > 32) mymir = lane < cnt ? m.mirror_row[e0 + eb + lane] : -1;
+            for (int j = 0; j < cnt; ++j, ++piece) {
+                const int m0 = __shfl_sync(0xffffffffu, mymir, j);
+                mbar_wait(bar_a + 8 * stage, parity);
+                const unsigned char* __restrict__ sp = ring + stage * STAGE;
+                double xb[4], fb[4][2];
+#pragma unroll
+                for (int sb = 0; sb < 4; ++sb) {
+                    xb[sb] = *reinterpret_cast<const double*>(sp + offx + 256 * sb);
+#pragma unroll
+                    for (int tb = 0; tb < 2; ++tb) fb[sb][tb] = *reinterpret_cast<const double*>(sp + offb[tb] + 512 * sb);
+                }
+                if (m0 >= 0) {  // warp-uniform; four independent accumulator chains
+                    double za[4][2];
+#pragma unroll
+                    for (int tq = 0; tq < 4; ++tq)
+#pragma unroll
+                        for (int sg = 0; sg < 2; ++sg) za[tq][sg] = *reinterpret_cast<const double*>(sp + offa[tq] + 1024 * sg);
+                    double2 z[2] = {make_double2(0, 0), make_double2(0, 0)};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        dmma884(accf[0], xb[q], fb[q][0]);
+                        dmma884(accf[1], xb[q], fb[q][1]);
+                        dmma884(z[0], za[q][0], xa[q]);
+                        dmma884(z[1], za[q][1], xa[q]);
+                    }
+                    const size_t zo = (size_t)m0 * R;
+                    if (k == 0) {
+                        if (z_ok & 1) {
+                            z0[zo] = z[0].x;
+                            z0[zo + 8] = z[1].x;
+                        }
+                        if (z_ok & 2) {
+                            z1[zo] = z[0].y;
+                            z1[zo + 8] = z[1].y;
+                        }
+                    } else {
+                        if (z_ok & 1) {
+                            asm volatile("red.global.add.f64 [%0], %1;" ::"l"(z0 + zo), "d"(z[0].x) : "memory");
+                            asm volatile("red.global.add.f64 [%0], %1;" ::"l"(z0 + zo + 8), "d"(z[1].x) : "memory");
+                        }
+                        if (z_ok & 2) {
+                            asm volatile("red.global.add.f64 [%0], %1;" ::"l"(z1 + zo), "d"(z[0].y) : "memory");
+                            asm volatile("red.global.add.f64 [%0], %1;" ::"l"(z1 + zo + 8), "d"(z[1].y) : "memory");
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        dmma884(accf[0], xb[q], fb[q][0]);
+                        dmma884(accf[1], xb[q], fb[q][1]);
+                    }
+                }
+                __syncwarp();  // every lane has read what it needs from this stage
+                if (piece + STAGES < npieces) fill();
+                if (++stage == STAGES) {
+                    stage = 0;
+                    parity ^= 1;
+                }
+            }
+        }
+#pragma unroll
+        for (int tq = 0; tq < 4; ++tq) xa[tq] = xan[tq];
+    }
+    if (lr < nrhs) {
+        double* __restrict__ out = scr + lr * sstride + (size_t)m.srow_ptr[g] * R + 2 * lc;
+#pragma unroll
+        for (int tb = 0; tb < 2; ++tb) *reinterpret_cast<double2*>(out + 8 * tb) = accf[tb];
+    }
+}
+
+void launch_bsr_apply_ids(const DevCSR& m, const IdList& ids, size_t xstride, int nrhs, double* scr, size_t sstride, cudaStream_t st) {
+    if (m.groups == 0 || nrhs == 0 || ids.n == 0) return;
+    constexpr int STAGES = 3, SMEM = 8 * (STAGES * MMA_STAGE + STAGES * 8 + 32 * 4);
+    static bool once = false;
+    if (!once) {
+        cudaFuncSetAttribute(bsr_apply_sym_mma_ids_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        once = true;
+    }
+    bsr_apply_sym_mma_ids_kernel<STAGES><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, ids, xstride, nrhs, scr, sstride);
+}
+
 template <int R>
 static void launch_multi_R(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
                            double sign, cudaStream_t st) {

@@ -169,7 +169,8 @@ __device__ __forceinline__ double fold_node(const DevCSR& m, int node, int t) {
 __device__ __forceinline__ double fold_node_multi(const DevCSR& m, const FoldList& fl, const double* const* scr, int node, int t) {
     const int2 rr = m.node_rows[node];
     double s = 0;
-    for (int j = 0; j < fl.n; ++j) s = fma(fl.coef[j], fold_rows_at(scr[j], rr, m.uniform_block, t), s);
+    const int ns = fl.nscr < 0 ? fl.n : fl.nscr;
+    for (int j = 0; j < ns; ++j) s = fma(fl.coef[j], fold_rows_at(scr[j], rr, m.uniform_block, t), s);
     return s;
 }
 

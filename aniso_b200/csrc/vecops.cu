@@ -3,6 +3,8 @@
 // host synchronisation (to read the new Hessenberg column for the Givens update).
 #include <cstdint>
 
+#include <algorithm>
+
 #include "device.cuh"
 
 namespace an {
@@ -160,6 +162,22 @@ __global__ void scale_inv_dev_kernel(int n, const double* __restrict__ norm, con
 }
 void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, int squared, cudaStream_t st) {
     if (n) scale_inv_dev_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, norm, in, out, squared);
+}
+
+// block operator: the inputs of (kernel id, output mode) pairs are combinations of at most two scaled input modes
+__global__ void __launch_bounds__(256) lincomb_kernel(const __grid_constant__ LinList L, size_t len) {
+    const int e = blockIdx.y;
+    const double* __restrict__ a = L.a[e];
+    const double* __restrict__ b = L.b[e];
+    double* __restrict__ d = L.dst[e];
+    const double ca = L.ca[e], cb = L.cb[e];
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < len; i += (size_t)gridDim.x * blockDim.x)
+        d[i] = b ? fma(cb, b[i], ca * a[i]) : ca * a[i];
+}
+void launch_lincomb(const LinList& L, size_t len, cudaStream_t st) {
+    if (L.n == 0 || len == 0) return;
+    const unsigned gx = (unsigned)std::min<size_t>((len + 255) / 256, 1024);
+    lincomb_kernel<<<dim3(gx, L.n), 256, 0, st>>>(L, len);
 }
 
 __global__ void sqrt1_kernel(double* v) { *v = sqrt(*v); }
