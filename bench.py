@@ -34,7 +34,8 @@ UNIT = "points/s"
 NP_ORDER, SING_RULE, G_ANISO, MAX_LEVEL = 4, 10, 0.9, 20
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the M2L stream kernel, from the committed `ncu --set full`
 # capture profiles/r01_final_ncu_raw.csv (cannot be measured live); keyed by (sz, n_gpus)
-NCU_TRAFFIC = {(1024, 1): 2403305000 + 115160000}
+# (TMA-ring kernel: the two launches of a matvec, levels 2-7 and level 8, read 0.590 + 1.813 GB and write 0.007 + 0.077 GB)
+NCU_TRAFFIC = {(1024, 1): 590147000 + 1813174000 + 7098000 + 76844000}
 
 
 def workload_name(sz):
