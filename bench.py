@@ -186,6 +186,68 @@ def cpu_baseline(args):
     return out
 
 
+def block_section(sz, K=2):
+    """the multi-mode block operator of the MATLAB layer (aniso.m forward / mforward / solve) on the same
+    geometry with K = 2 angular modes (kernel ids 0..2, g = 0.9): device-resident mforward (regrouped tensor-core form and
+    the loop of K(2K-1) mappings) and the block GMRES of aniso.m:158-172 (restart 400, tol 1e-11) through the host API."""
+    import ctypes as C
+
+    from aniso_b200 import Aniso, _lib
+
+    a = Aniso(sz, 1, K, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
+    L = a.L
+    x, y, w = a.nodes()
+    n = x.size
+    ss, st = cases.sigma_fields("layers", x, y, sz, 1)
+    a.setCoeff(ss, st)
+    t0 = time.perf_counter()
+    for k in range(2 * K - 1):
+        a.cache(k)
+    a.synchronize()
+    t_cache = time.perf_counter() - t0
+    du, dout = C.c_void_p(), C.c_void_p()
+    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(du)))
+    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(dout)))
+    src = cases.gaussian_source(x, y)
+    for m in range(K):
+        _lib.check(L.aniso_to_slots(a.h, src, C.c_void_p(du.value + 8 * m * n)))
+    res = {"K": K, "kernel_ids": 2 * K - 1, "cache_all_ids_s": t_cache}
+    for key, env in (("mforward_ms", None), ("mforward_loop_ms", "1")):
+        if env:
+            os.environ["ANISO_BLOCK_LOOP"] = env
+        else:
+            os.environ.pop("ANISO_BLOCK_LOOP", None)
+        for _ in range(3):
+            _lib.check(L.aniso_block_forward_dev(a.h, du, 1, dout))
+        a.synchronize()
+        l0, t0, reps = a.launch_count(), time.perf_counter(), 10
+        for _ in range(reps):
+            _lib.check(L.aniso_block_forward_dev(a.h, du, 1, dout))
+        a.synchronize()
+        res[key] = (time.perf_counter() - t0) / reps * 1e3
+        res[key.replace("_ms", "_launches")] = (a.launch_count() - l0) // reps
+    os.environ.pop("ANISO_BLOCK_LOOP", None)
+    drhs, dx = C.c_void_p(), C.c_void_p()
+    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(drhs)))
+    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(dx)))
+    it = C.c_int(0)
+    hist = np.zeros(402)
+    zeros = np.zeros(n)
+    for _ in range(2):  # the first solve allocates the Krylov work space (restart 400: 403 vectors of K*N doubles)
+        for m in range(K):  # x0 = 0
+            _lib.check(L.aniso_to_slots(a.h, zeros, C.c_void_p(dx.value + 8 * m * n)))
+        a.synchronize()
+        t0 = time.perf_counter()
+        _lib.check(L.aniso_block_forward_dev(a.h, du, 0, drhs))  # rhs = forward(charge), aniso.m:160
+        rc = _lib.check(L.aniso_block_gmres_dev(a.h, drhs, dx, 400, 400, 1e-11, C.byref(it), hist, hist.size))
+        a.synchronize()
+        t_solve = time.perf_counter() - t0
+    res.update({"solve_s": t_solve, "solve_iters": int(it.value), "solve_rc": int(rc), "solve_final_resid": float(hist[it.value]),
+                "solve_note": "device-resident: rhs = forward(charge), then GMRES(400, 1e-11, 400) on I - mforward (aniso.m:158-172)"})
+    a.delete()
+    return res
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -354,6 +416,10 @@ def run_ours(args):
                 "gmres": {"rc": int(rc), "iters": int(it.value), "final_resid": float(hist[it.value]), "time_to_solve_s": t_gmres,
                           "first_call_s": t_first, "m": 80, "tol": 1e-12, "gpu_launches": int(gm_launches)},
                 "setup_s": t_setup}
+        if world == 1 and not args.no_block:
+            a.delete()
+            a = None
+            line["block_operator"] = block_section(sz)
         if world == 1 and not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_baseline(args)
@@ -361,7 +427,8 @@ def run_ours(args):
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_cores(), "kind": "reference",
                                         "sample": "failed: %r" % (e,)}
         print(json.dumps(line), flush=True)
-    a.delete()
+    if a is not None:
+        a.delete()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -376,6 +443,7 @@ def main():
     ap.add_argument("--sz", type=int, default=1024, help="cells per side (N = sz^2); 1024 = BASELINE C5")
     ap.add_argument("--ref-sz", type=int, default=0, help="sample size of the reference arm (0 = by core count)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-block", action="store_true", help="skip the multi-mode block operator section (N = 1 only)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
