@@ -603,8 +603,8 @@ OperatorCache& ensure_ops(aniso_handle* h, int id, int part) {
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede cache/mapping");
     OperatorCache c;
     c.sign = (id & 1) ? -1.0 : 1.0;
-    c.p2p = dalloc<double>(h, (size_t)h->p2p.nnz);
-    c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz);
+    c.p2p = dalloc<double>(h, (size_t)h->p2p.nnz + 2);  // + 16 bytes: the last bulk copy of a stream that starts on an odd
+    c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz + 2);  //   double rounds up to the next 16-byte boundary (stream.cu symg ring)
     cudaEvent_t ev[3];
     for (auto& e : ev) CK(cudaEventCreate(&e));
     // the optical depth is the same for every kernel id: ids > 0 of the fused operators are derived from id 0

@@ -1000,6 +1000,152 @@ __global__ void __launch_bounds__(256, 3) bsr_apply_symg_kernel(DevCSR m, const 
     if (has1) out[lane + 32] = acc1;
 }
 
+// ---- the same, fed by the TMA engine -------------------------------------------------------------------------------
+// The register-load form above holds 8 rows per warp in flight (24 warps x 8 x 8R bytes = 38 - 75 KB per SM) and ncu
+// shows it waiting on those loads (long-scoreboard stalls, 4.0 - 5.2 TB/s).  As for 16 x 16 blocks, the blocks of one
+// target are one contiguous run, here of ne * R rows of R doubles; the copy engine fetches it in pieces of EIGHT ROWS
+// (64 R bytes, a multiple of 16 for every R) into a private ring, so the bytes in flight (warps x STAGES x 64 R) no
+// longer depend on the register budget.  A piece may straddle two blocks: every row of a piece carries its own (block,
+// source index), i.e. its own x_B value and its own partner scratch row; the forward accumulators and x_A do not change
+// across the blocks of a target.  For odd R a target's run may start on an odd double: the ring copies from the 16-byte
+// boundary below it (`skew`), each stage holds 16 bytes more than a piece, and the operator allocation is padded by 16
+// bytes (capi.cu ensure_ops).
+template <int R, int STAGES, int MINB>
+__global__ void __launch_bounds__(256, MINB) bsr_apply_symg_ring_kernel(DevCSR m, const double* __restrict__ A,
+                                                                        const double* __restrict__ x, double sign) {
+    constexpr bool TWO = R > 32;
+    constexpr int PIECE = 64 * R, STAGE = PIECE + 16;
+    extern __shared__ __align__(128) unsigned char ring_smem[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 8 + wid;
+    if (g >= m.groups) return;  // warps are independent: no CTA-wide barrier below
+    unsigned char* ring = ring_smem + (size_t)wid * STAGES * STAGE;
+    const uint32_t ring_a = smem_u32(ring);
+    const uint32_t bar_a = smem_u32(ring_smem + 8 * STAGES * STAGE + wid * STAGES * 8);
+    double* __restrict__ xsh = reinterpret_cast<double*>(ring_smem + 8 * STAGES * STAGE + 8 * STAGES * 8) + wid * 8;
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const int64_t off0 = ne ? m.blk_off[e0] : 0;
+    const int skew = (int)(off0 & 1);
+    const unsigned char* __restrict__ src = reinterpret_cast<const unsigned char*>(A + (off0 - skew));
+    const int nrows = ne * R, npieces = (nrows + 7) >> 3;
+    const uint64_t pol = stream_policy();
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar_a + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    auto fill = [&](int q, int stage) {  // producer (lane 0): piece q -> stage
+        const int rows = min(8, nrows - 8 * q);
+        const uint32_t bytes = (uint32_t)(8 * (skew + rows * R) + 15) & ~15u;
+        const uint32_t bar = bar_a + 8 * stage;
+        mbar_expect_tx(bar, bytes);
+        bulk_g2s(ring_a + stage * STAGE, src + (size_t)q * PIECE, bytes, bar, pol);
+    };
+    if (lane == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+            if (s < npieces) fill(s, s);
+    }
+    const int self = m.row_off[g];
+    const bool has0 = lane < R, has1 = TWO && lane + 32 < R;
+    const double xa0 = has0 ? __ldg(x + self + lane) : 0.0, xa1 = has1 ? __ldg(x + self + lane + 32) : 0.0;
+    double* __restrict__ scratch = m.scratch;
+    const bool b0 = lane & 1, b1 = lane & 2, b2 = lane & 4;
+    const int l8 = lane & 7, rperm = (b0 ? 4 : 0) + (b1 ? 2 : 0) + (b2 ? 1 : 0);  // row of a piece whose z this lane ends up with
+    // per-row metadata of piece q, fetched one piece ahead: x_B of row l8 (natural order, published through xsh) and the
+    // partner scratch position of row rperm
+    auto meta = [&](int q, double& xv, int& mrow, int& srow) {
+        const int i = 8 * q + l8, ir = 8 * q + rperm;
+        xv = 0.0;
+        mrow = -1;
+        srow = 0;
+        if (i < nrows) {
+            const int e = i / R;
+            xv = __ldg(x + m.col_off[e0 + e] + (i - e * R));
+        }
+        if (ir < nrows) {
+            const int e = ir / R;
+            srow = ir - e * R;
+            mrow = m.mirror_row[e0 + e];
+        }
+    };
+    double xv_c, acc0 = 0, acc1 = 0;
+    int mr_c, sr_c;
+    meta(0, xv_c, mr_c, sr_c);
+    int stage = 0;
+    uint32_t parity = 0;
+#pragma unroll 1
+    for (int q = 0; q < npieces; ++q) {
+        double xv_n;
+        int mr_n, sr_n;
+        meta(q + 1, xv_n, mr_n, sr_n);
+        if (lane < 8) xsh[lane] = xv_c;
+        const int rows = min(8, nrows - 8 * q);
+        mbar_wait(bar_a + 8 * stage, parity);
+        __syncwarp();  // xsh
+        const double* __restrict__ sp = reinterpret_cast<const double*>(ring + stage * STAGE) + skew + lane;
+        double a0[8], a1[8], xs[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            a0[j] = has0 && j < rows ? sp[j * R] : 0.0;
+            a1[j] = has1 && j < rows ? sp[j * R + 32] : 0.0;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) {
+            const double2 v = reinterpret_cast<const double2*>(xsh)[j >> 1];
+            xs[j] = v.x;
+            xs[j + 1] = v.y;
+        }
+        __syncwarp();  // every lane has read what it needs from this stage (and from xsh)
+        if (lane == 0 && q + STAGES < npieces) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            fill(q + STAGES, stage);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            acc0 = fma(a0[j], xs[j], acc0);
+            if (TWO) acc1 = fma(a1[j], xs[j], acc1);
+        }
+        if (__any_sync(0xffffffffu, mr_c >= 0)) {
+            double p[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) p[j] = TWO ? fma(a0[j], xa0, a1[j] * xa1) : a0[j] * xa0;
+            double qq[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) qq[j] = (b0 ? p[4 + j] : p[j]) + __shfl_xor_sync(0xffffffffu, b0 ? p[j] : p[4 + j], 1);
+            const double w0 = (b1 ? qq[2] : qq[0]) + __shfl_xor_sync(0xffffffffu, b1 ? qq[0] : qq[2], 2);
+            const double w1 = (b1 ? qq[3] : qq[1]) + __shfl_xor_sync(0xffffffffu, b1 ? qq[1] : qq[3], 2);
+            double z = (b2 ? w1 : w0) + __shfl_xor_sync(0xffffffffu, b2 ? w0 : w1, 4);
+            z += __shfl_xor_sync(0xffffffffu, z, 8);
+            z += __shfl_xor_sync(0xffffffffu, z, 16);
+            if (lane < 8 && mr_c >= 0) scratch[(size_t)mr_c * R + sr_c] = sign * z;
+        }
+        xv_c = xv_n;
+        mr_c = mr_n;
+        sr_c = sr_n;
+        if (++stage == STAGES) {
+            stage = 0;
+            parity ^= 1;
+        }
+    }
+    double* __restrict__ out = scratch + (size_t)m.srow_ptr[g] * R;
+    if (has0) out[lane] = acc0;
+    if (has1) out[lane + 32] = acc1;
+}
+
+template <int R, int STAGES, int MINB>
+static void launch_symg_ring(const DevCSR& m, const double* A, const double* x, double sign, cudaStream_t st) {
+    constexpr int SMEM = 8 * STAGES * (64 * R + 16) + 8 * STAGES * 8 + 8 * 8 * 8;
+    static bool once = false;  // per instantiation
+    if (!once) {
+        cudaFuncSetAttribute(bsr_apply_symg_ring_kernel<R, STAGES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        once = true;
+    }
+    bsr_apply_symg_ring_kernel<R, STAGES, MINB><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, sign);
+}
+
 __global__ void __launch_bounds__(128) bsr_apply_row_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
                                                             double* __restrict__ y) {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1057,6 +1203,9 @@ void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double*
         else if (ring && m.uniform_block == 64) launch_ring<64, 1>(m, A, x, 0, m.scratch, 0, sign, st);
         else if (m.uniform_block == 16) bsr_apply_sym_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, sign);
         else if (m.uniform_block == 64) bsr_apply_sym_kernel<64><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else if (ring && m.uniform_block == 25) launch_symg_ring<25, 4, 4>(m, A, x, sign, st);
+        else if (ring && m.uniform_block == 36) launch_symg_ring<36, 3, 3>(m, A, x, sign, st);
+        else if (ring && m.uniform_block == 49) launch_symg_ring<49, 4, 2>(m, A, x, sign, st);
         else if (m.uniform_block == 25) bsr_apply_symg_kernel<25><<<ctas, 256, 0, st>>>(m, A, x, sign);
         else if (m.uniform_block == 36) bsr_apply_symg_kernel<36><<<ctas, 256, 0, st>>>(m, A, x, sign);
         else if (m.uniform_block == 49) bsr_apply_symg_kernel<49><<<ctas, 256, 0, st>>>(m, A, x, sign);

@@ -251,6 +251,9 @@ def test_fast_paths_match_plain_paths_at_baseline_sizes(cfg, kid, monkeypatch):
 @pytest.mark.parametrize("cfg", [
     (512, 1, 2, 0.9, 10, 4, 20, "layers"),    # 16 x 16 blocks: bank-swizzled storage
     (256, 1, 2, 0.9, 10, 8, 20, "hetero"),    # 64 x 64 blocks
+    (256, 1, 2, 0.9, 10, 5, 20, "hetero"),    # 25 x 25 blocks: eight-row pieces, streams starting on odd doubles
+    (256, 1, 2, 0.9, 10, 6, 20, "layers"),    # 36 x 36
+    (128, 1, 2, 0.5, 10, 7, 20, "hetero"),    # 49 x 49
 ])
 def test_stream_kernel_variants_agree(cfg, monkeypatch):
     """The operator stream has three forms over the same symmetric storage: fed by the copy engine into a shared-memory ring
