@@ -1146,6 +1146,169 @@ static void launch_symg_ring(const DevCSR& m, const double* A, const double* x, 
     bsr_apply_symg_ring_kernel<R, STAGES, MINB><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, sign);
 }
 
+// ---- eight-row pieces with the transposed product on the FP64 tensor cores -----------------------------------------
+// ncu of the kernel above at R = 25 / 36: issue slots 77 / 73 % busy, ~270 / 335 instructions per piece, a third of them
+// the butterfly (18 SHFL + 28 FSEL + DADD / DMUL) and much of the rest address arithmetic re-derived under register
+// pressure.  The transposed product of a piece, z[row] = sum_t P[row][t] x_A[t], is an (8 x R)(R x 1) product: as
+// ceil(R / 4) mma.m8n8k4.f64 with P read from the stage as the A operand (lane l: P[row l/4][4 kt + l%4]) and x_A
+// replicated over the eight columns of the B operand, lane 4 row of the accumulator fragment holds z[row] with no
+// cross-lane reduction at all.  The forward product stays on DFMA (lane = target; one LDS + one DFMA per row).  Rows are
+// tracked as (block, source index) pairs advanced by eight per piece instead of divided out.  The ring is zeroed before
+// the first copy so that the rows behind the end of a target's run (xs = 0, no partner row) multiply finite values.
+__device__ __forceinline__ double lds_f64(uint32_t a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double2 lds_v2f64(uint32_t a) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+
+template <int R, int STAGES, int MINB>
+__global__ void __launch_bounds__(256, MINB) bsr_apply_symg_mma_kernel(DevCSR m, const double* __restrict__ A,
+                                                                       const double* __restrict__ x, double sign) {
+    constexpr bool TWO = R > 32;
+    constexpr int PIECE = 64 * R, STAGE = PIECE + 16, KT = (R + 3) / 4;
+    extern __shared__ __align__(128) unsigned char ring_smem[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = blockIdx.x * 8 + wid;
+    if (g >= m.groups) return;  // warps are independent: no CTA-wide barrier below
+    unsigned char* ring = ring_smem + (size_t)wid * STAGES * STAGE;
+    uint32_t ring_a = smem_u32(ring);
+    uint32_t bar_a = smem_u32(ring_smem + 8 * STAGES * STAGE + wid * STAGES * 8);
+    uint32_t xsh_a = smem_u32(ring_smem + 8 * STAGES * STAGE + 8 * STAGES * 8 + wid * 64);
+    for (int o = lane * 16; o < STAGES * STAGE; o += 512) *reinterpret_cast<double2*>(ring + o) = make_double2(0.0, 0.0);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    const int e0 = m.ent_ptr[g], ne = m.ent_ptr[g + 1] - e0;
+    const int64_t off0 = ne ? m.blk_off[e0] : 0;
+    const int skew = (int)(off0 & 1);
+    const unsigned char* __restrict__ src = reinterpret_cast<const unsigned char*>(A + (off0 - skew));
+    const int nrows = ne * R, npieces = (nrows + 7) >> 3;
+    const uint64_t pol = stream_policy();
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(bar_a + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    // producer (lane 0): piece q -> the stage at shared address sa with barrier ba; every piece but the last has 8 rows
+    const uint32_t full_bytes = (uint32_t)(8 * (skew + 8 * R) + 15) & ~15u;
+    const uint32_t last_bytes = (uint32_t)(8 * (skew + (nrows - 8 * (npieces - 1)) * R) + 15) & ~15u;
+    auto fill = [&](int q, uint32_t sa, uint32_t ba) {
+        const uint32_t bytes = q == npieces - 1 ? last_bytes : full_bytes;
+        mbar_expect_tx(ba, bytes);
+        bulk_g2s(sa, src + (size_t)q * PIECE, bytes, ba, pol);
+    };
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s)
+            if (s < npieces) fill(s, ring_a + s * STAGE, bar_a + 8 * s);
+    }
+    const int self = m.row_off[g];
+    const int lr = lane >> 2, lc = lane & 3;
+    const bool has0 = lane < R, has1 = TWO && lane + 32 < R;
+    double xak[KT];  // B operand of the transposed product: sign * x_A[4 kt + lc], the same in all eight columns
+#pragma unroll
+    for (int kt = 0; kt < KT; ++kt) xak[kt] = 4 * kt + lc < R ? sign * __ldg(x + self + 4 * kt + lc) : 0.0;
+    double* __restrict__ scratch = m.scratch;
+    // Byte offsets of this lane inside a stage.  Lanes without a target / past the end of a row read a valid location
+    // instead of being predicated off (their products are multiplied by zero or never stored), so every load of the loop
+    // is base register + immediate.
+    uint32_t offf = 8 * (skew + min(lane, R - 1));                       // forward rows: lane = target
+    uint32_t offf1 = 8 * (skew + 32 + min(lane, TWO ? R - 33 : 0));      //   second half of a row (R > 32)
+    uint32_t offa = 8 * (skew + lr * R + lc);                            // A-operand fragment: row lr, column 4 kt + lc
+    uint32_t offa_last = 4 * (KT - 1) + lc < R ? offa + 32 * (KT - 1) : offa;  // R % 4 != 0: last k-step, lanes past the row
+    ANISO_PIN(offf); ANISO_PIN(offf1); ANISO_PIN(offa); ANISO_PIN(offa_last); ANISO_PIN(ring_a); ANISO_PIN(bar_a); ANISO_PIN(xsh_a);
+    // (block, source index) of the row whose x_B this lane gathers (row lane % 8 of the piece; lanes 0-7 publish it) and of
+    // the row whose z it ends up with (row lr; lanes lc == 0 write it)
+    int ex = 0, sx = lane & 7, ez = 0, sz = lr;
+    const int* __restrict__ colp = m.col_off + e0;
+    const int* __restrict__ mirp = m.mirror_row + e0;
+    double xv_c = ex < ne ? __ldg(x + colp[ex] + sx) : 0.0;
+    int mr_c = ez < ne ? mirp[ez] : -1;
+    double acc0 = 0, acc1 = 0;
+    uint32_t sa = ring_a, ba = bar_a, parity = 0;
+    int stage = 0;
+#pragma unroll 1
+    for (int q = 0; q < npieces; ++q) {
+        const int sz_c = sz;
+        sx += 8;
+        if (sx >= R) {
+            sx -= R;
+            ++ex;
+        }
+        sz += 8;
+        if (sz >= R) {
+            sz -= R;
+            ++ez;
+        }
+        const double xv_n = ex < ne ? __ldg(x + colp[ex] + sx) : 0.0;
+        const int mr_n = ez < ne ? mirp[ez] : -1;
+        if (lane < 8) asm volatile("st.shared.f64 [%0], %1;" ::"r"(xsh_a + 8 * lane), "d"(xv_c) : "memory");
+        mbar_wait(ba, parity);
+        __syncwarp();  // xsh
+        {
+            double a0[8], a1[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                a0[j] = lds_f64(sa + offf + 8 * j * R);
+                if (TWO) a1[j] = lds_f64(sa + offf1 + 8 * j * R);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+                const double2 v = lds_v2f64(xsh_a + 8 * j);
+                acc0 = fma(a0[j], v.x, acc0);
+                acc0 = fma(a0[j + 1], v.y, acc0);
+                if (TWO) {
+                    acc1 = fma(a1[j], v.x, acc1);
+                    acc1 = fma(a1[j + 1], v.y, acc1);
+                }
+            }
+        }
+        if (__any_sync(0xffffffffu, mr_c >= 0)) {
+            double2 z0 = make_double2(0.0, 0.0), z1 = make_double2(0.0, 0.0);
+#pragma unroll
+            for (int kt = 0; kt < KT; ++kt) {
+                const double a = lds_f64(kt == KT - 1 && (R & 3) ? sa + offa_last : sa + offa + 32 * kt);
+                if (kt & 1) dmma884(z1, a, xak[kt]);
+                else dmma884(z0, a, xak[kt]);
+            }
+            if (lc == 0 && mr_c >= 0) scratch[(size_t)mr_c * R + sz_c] = z0.x + z1.x;
+        }
+        __syncwarp();  // every lane's reads of this stage (and of xsh) have returned: the DFMA / DMMA above consumed them
+        if (lane == 0 && q + STAGES < npieces) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            fill(q + STAGES, sa, ba);
+        }
+        xv_c = xv_n;
+        mr_c = mr_n;
+        sa += STAGE;
+        ba += 8;
+        if (++stage == STAGES) {
+            stage = 0;
+            sa = ring_a;
+            ba = bar_a;
+            parity ^= 1;
+        }
+    }
+    double* __restrict__ out = scratch + (size_t)m.srow_ptr[g] * R;
+    if (has0) out[lane] = acc0;
+    if (has1) out[lane + 32] = acc1;
+}
+
+template <int R, int STAGES, int MINB>
+static void launch_symg_mma(const DevCSR& m, const double* A, const double* x, double sign, cudaStream_t st) {
+    constexpr int SMEM = 8 * STAGES * (64 * R + 16) + 8 * STAGES * 8 + 8 * 8 * 8;
+    static bool once = false;  // per instantiation
+    if (!once) {
+        cudaFuncSetAttribute(bsr_apply_symg_mma_kernel<R, STAGES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        once = true;
+    }
+    bsr_apply_symg_mma_kernel<R, STAGES, MINB><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, sign);
+}
+
 __global__ void __launch_bounds__(128) bsr_apply_row_kernel(DevCSR m, const double* __restrict__ A, const double* __restrict__ x,
                                                             double* __restrict__ y) {
     const int row = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1203,6 +1366,8 @@ void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double*
         else if (ring && m.uniform_block == 64) launch_ring<64, 1>(m, A, x, 0, m.scratch, 0, sign, st);
         else if (m.uniform_block == 16) bsr_apply_sym_kernel<16><<<ctas, 256, 0, st>>>(m, A, x, sign);
         else if (m.uniform_block == 64) bsr_apply_sym_kernel<64><<<ctas, 256, 0, st>>>(m, A, x, sign);
+        else if (ring && m.uniform_block == 25 && !getenv("ANISO_SYMG_NO_DMMA")) launch_symg_mma<25, 4, 4>(m, A, x, sign, st);
+        else if (ring && m.uniform_block == 36 && !getenv("ANISO_SYMG_NO_DMMA")) launch_symg_mma<36, 3, 3>(m, A, x, sign, st);
         else if (ring && m.uniform_block == 25) launch_symg_ring<25, 4, 4>(m, A, x, sign, st);
         else if (ring && m.uniform_block == 36) launch_symg_ring<36, 3, 3>(m, A, x, sign, st);
         else if (ring && m.uniform_block == 49) launch_symg_ring<49, 4, 2>(m, A, x, sign, st);

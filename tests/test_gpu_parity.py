@@ -264,7 +264,7 @@ def test_stream_kernel_variants_agree(cfg, monkeypatch):
     sz, deg, K, g, sr, np_, ml, kind = cfg
 
     def run(env):
-        for k in ("ANISO_STREAM_REGS", "ANISO_NO_SWIZZLE"):
+        for k in ("ANISO_STREAM_REGS", "ANISO_NO_SWIZZLE", "ANISO_SYMG_NO_DMMA"):
             monkeypatch.delenv(k, raising=False)
         for k in env:
             monkeypatch.setenv(k, "1")
@@ -284,3 +284,5 @@ def test_stream_kernel_variants_agree(cfg, monkeypatch):
     assert rel(run(("ANISO_STREAM_REGS",)), ring) < 1e-13
     assert rel(run(("ANISO_NO_SWIZZLE",)), ring) < 1e-13
     assert rel(run(("ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS")), ring) < 1e-13
+    if np_ in (5, 6):  # transposed product of a piece on the FP64 tensor cores (default) vs the shuffle butterfly
+        assert rel(run(("ANISO_SYMG_NO_DMMA",)), ring) < 1e-13
