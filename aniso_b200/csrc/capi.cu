@@ -3,6 +3,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -1314,10 +1315,13 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     g.V = g.r + n;
     double* dh = h->d_scal;  // device Hessenberg column, m+2 entries (+ m+2 for the second CGS2 pass)
     if (2 * (m + 2) > 1024) throw std::invalid_argument("restart length m too large (max 510)");
-    // orthogonalisation: the reference's modified Gram-Schmidt on one GPU; CGS2 when every dot costs an all-reduce
-    // (ANISO_GMRES_ORTHO=mgs|cgs2 overrides)
+    // orthogonalisation: classical Gram-Schmidt applied twice in three fused passes over the basis (default; same
+    // projections to rounding and the same iteration counts as the reference's modified Gram-Schmidt on every fixture, one
+    // launch and one all-reduce per pass instead of i+1 dependent ones).  ANISO_GMRES_ORTHO=mgs: the reference's MGS
+    // (gmres.cpp:115-119); cgs2_unfused: the two-launch form
     const char* oenv = getenv("ANISO_GMRES_ORTHO");
-    const bool cgs2 = oenv ? std::string(oenv) == "cgs2" : h->nranks > 1;
+    const bool cgs2 = oenv ? std::string(oenv) == "cgs2" || std::string(oenv) == "cgs2_unfused" : true;
+    const bool cgs_fused = !(oenv && std::string(oenv) == "cgs2_unfused");
     double* md_partial = g.V + (size_t)(m + 1) * n;
     double* col = h->pinned_small;
     std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0);
@@ -1325,6 +1329,14 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     bool done = false;
     double resid = 0;
     *iters = 0;
+    // ANISO_GMRES_TIMES=1 (development aid): device time of the operator and of the orthogonalisation, summed over the
+    // Arnoldi steps, printed next to the wall time of the solve
+    const bool gt_on = getenv("ANISO_GMRES_TIMES") != nullptr;
+    cudaEvent_t gt_ev[3] = {nullptr, nullptr, nullptr};
+    double gt_ms[2] = {0, 0};
+    const auto gt_t0 = std::chrono::steady_clock::now();
+    if (gt_on)
+        for (auto& e : gt_ev) CK(cudaEventCreate(&e));
     ddot_dev(h, n, b, b, dh, true);
     double normb = read_scalar(h, dh);
     A(x, g.w);
@@ -1343,7 +1355,9 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
         for (i = 0; i < m && j <= max_iter; ++i, ++j) {
             if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
             *iters = j;
+            if (gt_on) CK(cudaEventRecord(gt_ev[0], h->st));
             A(g.v(i), g.w);
+            if (gt_on) CK(cudaEventRecord(gt_ev[1], h->st));
             if (!cgs2) {
                 // modified Gram-Schmidt, gmres.cpp:115-119: h_k = w . v_k; w -= h_k v_k.  The axpy of step k and the dot of
                 // step k+1 (or the final norm) share one pass over w.
@@ -1356,6 +1370,15 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
                 // classical Gram-Schmidt applied twice: the same projections to rounding (H(:,i) = h1 + h2), but all dots of
                 // a pass in one launch and ONE all-reduce, instead of i+1 dependent all-reduces
                 double* h2 = dh + m + 2;
+                if (cgs_fused && cgs_pass_ok(n, i + 1, g.V, (size_t)n, g.w)) {
+                    // three fused passes over the basis (vecops.cu cgs_pass_kernel): h1; w -= V h1 and h2; w -= V h2 and |w|^2
+                    LAUNCH(h, launch_cgs_pass(0, n, i + 1, nullptr, g.V, (size_t)n, g.w, dh, md_partial, h->dot, h->st));
+                    allreduce_scalars(h, dh, i + 1);
+                    LAUNCH(h, launch_cgs_pass(1, n, i + 1, dh, g.V, (size_t)n, g.w, h2, md_partial, h->dot, h->st));
+                    allreduce_scalars(h, h2, i + 1);
+                    LAUNCH(h, launch_cgs_pass(2, n, i + 1, h2, g.V, (size_t)n, g.w, dh + i + 1, md_partial, h->dot, h->st));
+                    --h->launches;  // no separate reduction launch for the norm (counted below for the two-launch form)
+                } else
                 for (int pass = 0; pass < 2; ++pass) {
                     double* hp = pass ? h2 : dh;
                     LAUNCH(h, launch_multi_dot(n, i + 1, g.w, g.V, (size_t)n, hp, md_partial, h->dot, h->st));
@@ -1369,7 +1392,15 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
             // dh[i+1] = w . w: the square root is taken inside the scaling kernel and, for H, on the host
             LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), 1, h->st));
             CK(cudaMemcpyAsync(col, dh, sizeof(double) * (cgs2 ? 2 * m + 4 : i + 2), cudaMemcpyDeviceToHost, h->st));
+            if (gt_on) CK(cudaEventRecord(gt_ev[2], h->st));
             CK(cudaStreamSynchronize(h->st));
+            if (gt_on) {
+                float a = 0, o = 0;
+                cudaEventElapsedTime(&a, gt_ev[0], gt_ev[1]);
+                cudaEventElapsedTime(&o, gt_ev[1], gt_ev[2]);
+                gt_ms[0] += a;
+                gt_ms[1] += o;
+            }
             for (int k = 0; k <= i; ++k) H[k + (size_t)i * ldh] = col[k];
             H[i + 1 + (size_t)i * ldh] = std::sqrt(col[i + 1]);
             if (cgs2)
@@ -1398,6 +1429,12 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     }
     if (hist && *iters < hist_cap) hist[*iters] = resid;
     CK(cudaStreamSynchronize(h->st));
+    if (gt_on) {
+        const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - gt_t0).count();
+        fprintf(stderr, "[aniso gmres] %d iterations: wall %.3f ms, operator %.3f ms, orthogonalisation %.3f ms (device, Arnoldi steps only)\n",
+                *iters, wall, gt_ms[0], gt_ms[1]);
+        for (auto& e : gt_ev) cudaEventDestroy(e);
+    }
     return rc;
 }
 

@@ -189,6 +189,9 @@ void launch_axpy_dot(int n, const double* h, const double* v, double* w, const d
 // w -= sum_k h[k] V_k with an optional ||w||^2 of the result
 void launch_multi_dot(int n, int nv, const double* w, const double* V, size_t ldv, double* out, double* partial, DotWork& wk,
                       cudaStream_t st);
+bool cgs_pass_ok(int n, int nv, const double* V, size_t ldv, const double* w);
+void launch_cgs_pass(int mode, int n, int nv, const double* h_in, const double* V, size_t ldv, double* w, double* out, double* partial,
+                     DotWork& wk, cudaStream_t st);
 void launch_multi_axpy(int n, int nv, const double* h, const double* V, size_t ldv, double* w, double* norm2_out, double* partial,
                        DotWork& wk, cudaStream_t st);
 // w -= h[0] * v  (h read from device memory)

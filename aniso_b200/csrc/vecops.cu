@@ -279,4 +279,135 @@ void launch_multi_axpy(int n, int nv, const double* h, const double* V, size_t l
     if (norm2_out) reduce_partials_kernel<<<1, 32, 0, st>>>(1, nb, partial, norm2_out);
 }
 
+
+// ---- CGS2 in three fused passes ---------------------------------------------------------------------------------------
+// The two-launch form above makes four passes over the Krylov basis per Arnoldi step (dots, axpys, dots, axpys), re-reads
+// w once per group of eight vectors and was measured at half the HBM roofline (148 us per step at N = 2^20, ~13 vectors).
+// Here one kernel serves all three steps of the twice-applied classical Gram-Schmidt:
+//   MODE 0   h1 = V^T w
+//   MODE 1   w -= V h1, then h2 = V^T w for the NEW w: the dot is a sum over elements, so a block can form it for the
+//            elements it has just updated; the basis is read once from HBM and once more while it is still in L2
+//   MODE 2   w -= V h2 and |w|^2
+// i.e. three passes over the basis instead of four.  A thread keeps eight elements of w in registers (four 16-byte
+// loads, coalesced across the warp) and walks the basis vectors with eight 16-byte loads in flight; per vector the warp
+// sum goes to a per-warp slot in shared memory, block sums to `partial`, and the last block to finish adds them in a fixed
+// order (deterministic, identical on every rank).
+template <int MODE>
+__global__ void __launch_bounds__(256, 3) cgs_pass_kernel(int n, int nv, const double* __restrict__ h_in, const double* __restrict__ V,
+                                                          size_t ldv, double* __restrict__ w, double* __restrict__ partial,
+                                                          double* __restrict__ out, unsigned int* __restrict__ counter) {
+    extern __shared__ double cg_sm[];  // hs[nv] | wpart[nout][8]
+    double* __restrict__ hs = cg_sm;
+    double* __restrict__ wpart = cg_sm + nv;
+    const int nout = MODE == 2 ? 1 : nv;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (MODE)
+        for (int k = threadIdx.x; k < nv; k += blockDim.x) hs[k] = h_in[k];
+    for (int k = threadIdx.x; k < nout * 8; k += blockDim.x) wpart[k] = 0.0;
+    __syncthreads();
+    const int npair = n >> 1;
+    const int per = (npair + gridDim.x - 1) / gridDim.x;
+    const int p0 = blockIdx.x * per, p1 = min(npair, p0 + per);
+    double2* __restrict__ w2 = reinterpret_cast<double2*>(w);
+    for (int c = p0; c < p1; c += 1024) {
+        int idx[4];
+        bool ok[4];
+        double2 a[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            idx[u] = c + u * 256 + threadIdx.x;
+            ok[u] = idx[u] < p1;
+            a[u] = ok[u] ? w2[idx[u]] : make_double2(0.0, 0.0);
+        }
+        if (MODE) {
+#pragma unroll 2
+            for (int k = 0; k < nv; ++k) {
+                const double2* __restrict__ Vk = reinterpret_cast<const double2*>(V + (size_t)k * ldv);
+                const double hk = -hs[k];
+                double2 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = ok[u] ? Vk[idx[u]] : make_double2(0.0, 0.0);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    a[u].x = fma(hk, v[u].x, a[u].x);
+                    a[u].y = fma(hk, v[u].y, a[u].y);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) w2[idx[u]] = a[u];
+        }
+        if (MODE == 2) {
+            double s = 0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) s = fma(a[u].x, a[u].x, fma(a[u].y, a[u].y, s));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (lane == 0) wpart[warp] += s;
+        } else {
+#pragma unroll 2
+            for (int k = 0; k < nv; ++k) {
+                const double2* __restrict__ Vk = reinterpret_cast<const double2*>(V + (size_t)k * ldv);
+                double2 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = ok[u] ? Vk[idx[u]] : make_double2(0.0, 0.0);
+                double s0 = 0, s1 = 0;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    s0 = fma(a[u].x, v[u].x, s0);
+                    s1 = fma(a[u].y, v[u].y, s1);
+                }
+                double s = s0 + s1;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+                if (lane == 0) wpart[k * 8 + warp] += s;
+            }
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < nout; k += blockDim.x) {
+        double s = 0;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) s += wpart[k * 8 + q];
+        partial[(size_t)k * gridDim.x + blockIdx.x] = s;
+    }
+    // the last block to finish adds the block sums in index order (as dot_kernel does): no separate reduction launch
+    __shared__ bool last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    for (int k = warp; k < nout; k += 8) {
+        const double* row = partial + (size_t)k * gridDim.x;
+        double s = 0;
+        for (int b = lane; b < (int)gridDim.x; b += 32 * 4) {  // four independent loads per trip, fixed order
+            double v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = b + 32 * u < (int)gridDim.x ? __ldcg(row + b + 32 * u) : 0.0;
+            s += (v[0] + v[1]) + (v[2] + v[3]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) out[k] = s;
+    }
+    if (threadIdx.x == 0) *counter = 0;
+}
+
+bool cgs_pass_ok(int n, int nv, const double* V, size_t ldv, const double* w) {
+    return n >= 2 && (n & 1) == 0 && (ldv & 1) == 0 && nv <= 512 && ((uintptr_t)V & 15) == 0 && ((uintptr_t)w & 15) == 0;
+}
+void launch_cgs_pass(int mode, int n, int nv, const double* h_in, const double* V, size_t ldv, double* w, double* out, double* partial,
+                     DotWork& wk, cudaStream_t st) {
+    const int npair = n >> 1;
+    int nb = std::min(std::min(444, wk.blocks), (npair + 1023) / 1024);  // 148 SMs x 3 resident CTAs: one balanced wave
+    if (nb < 1) nb = 1;
+    const int nout = mode == 2 ? 1 : nv;
+    const size_t smem = (size_t)(nv + 8 * nout) * sizeof(double);
+    if (mode == 0) cgs_pass_kernel<0><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
+    else if (mode == 1) cgs_pass_kernel<1><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
+    else cgs_pass_kernel<2><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
+}
+
 }  // namespace an

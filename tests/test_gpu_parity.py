@@ -119,6 +119,30 @@ def test_gmres_vs_reference_golden(golden, name):
     a.delete()
 
 
+@pytest.mark.parametrize("name", ["b8d3", "ml12d2"])
+def test_gmres_orthogonalisation_forms_agree(golden, name, monkeypatch):
+    """The Arnoldi orthogonalisation has three forms: classical Gram-Schmidt applied twice in three fused passes (default),
+    the same in two launches per pass, and the reference's modified Gram-Schmidt (gmres.cpp:115-119).  Same right-hand
+    side: the reference's iteration count from each, residual histories and solutions equal to rounding."""
+    g = golden(name)
+    runs = {}
+    for form in ("cgs2", "cgs2_unfused", "mgs"):
+        monkeypatch.setenv("ANISO_GMRES_ORTHO", form)
+        a, x, y, w = make(name)
+        a.cache(0)
+        b = g["gm_b"] if int(g["stride"]) == 1 else a.mapping(cases.gaussian_source(x, y), 0)
+        runs[form] = a.gmres(b, m=80, max_iter=400, tol=1e-12)
+        a.delete()
+    monkeypatch.delenv("ANISO_GMRES_ORTHO")
+    xs, rc, it, hist = runs["cgs2"]
+    assert rc == 0 and it == int(g["gm_iters"])
+    for form in ("cgs2_unfused", "mgs"):
+        xo, rco, ito, histo = runs[form]
+        assert rco == 0 and ito == it
+        assert rel(xo, xs) < 1e-10
+        np.testing.assert_allclose(histo[: it - 2], hist[: it - 2], rtol=1e-3, atol=1e-9)
+
+
 def test_gmres_count_sensitivity_of_the_oracle(golden):
     """Evidence for the tolerance above (CPU only, no device work): a 1e-15 relative perturbation of b changes the
     oracle's own iteration count on a16, because the residual stalls at 1e-12 = tol."""
