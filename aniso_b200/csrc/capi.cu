@@ -1337,12 +1337,23 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     const auto gt_t0 = std::chrono::steady_clock::now();
     if (gt_on)
         for (auto& e : gt_ev) CK(cudaEventCreate(&e));
-    ddot_dev(h, n, b, b, dh, true);
-    double normb = read_scalar(h, dh);
-    A(x, g.w);
-    LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
-    ddot_dev(h, n, g.r, g.r, dh, true);
-    double beta = read_scalar(h, dh);
+    // |b| and x0 . x0 come back in one read.  x0 = 0 (the usual start): A x0 = 0 exactly (the operator is linear and every
+    // kernel of it maps zeros to zeros), so r = b and the first operator application (gmres.cpp:86) is not launched.
+    ddot_dev(h, n, b, b, dh + 2, true);
+    ddot_dev(h, n, x, x, dh + 3, false);
+    CK(cudaMemcpyAsync(col, dh + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    double normb = col[0], beta;
+    if (col[1] == 0.0) {
+        CK(cudaMemcpyAsync(g.r, b, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
+        CK(cudaMemcpyAsync(dh, dh + 2, sizeof(double), cudaMemcpyDeviceToDevice, h->st));
+        beta = normb;
+    } else {
+        A(x, g.w);
+        LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
+        ddot_dev(h, n, g.r, g.r, dh, true);
+        beta = read_scalar(h, dh);
+    }
     if (normb == 0.0) normb = 1;
     if ((resid = beta / normb) <= tol) {  // gmres.cpp:90 (<= here, < below: Q11)
         rc = 0;

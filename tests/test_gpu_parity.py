@@ -143,6 +143,24 @@ def test_gmres_orthogonalisation_forms_agree(golden, name, monkeypatch):
         np.testing.assert_allclose(histo[: it - 2], hist[: it - 2], rtol=1e-3, atol=1e-9)
 
 
+def test_gmres_nonzero_start(golden):
+    """x0 = 0 skips the first operator application (A 0 = 0); a non-zero start takes r = b - A x0 (gmres.cpp:86-88) and must
+    reach the same solution, in fewer steps when x0 is already close."""
+    g = golden("b8d3")
+    a, x, y, w = make("b8d3")
+    a.cache(0)
+    b = g["gm_b"] if int(g["stride"]) == 1 else a.mapping(cases.gaussian_source(x, y), 0)
+    xs, rc, it, hist = a.gmres(b, m=80, max_iter=400, tol=1e-12)
+    pert = xs * (1 + 1e-3 * np.cos(7 * x) * np.sin(5 * y))
+    xs2, rc2, it2, hist2 = a.gmres(b, x0=pert, m=80, max_iter=400, tol=1e-12)
+    assert rc == rc2 == 0 and it2 < it
+    assert hist[0] == 1.0 and hist2[0] < 0.1
+    assert rel(xs2, xs) < 1e-10
+    xs3, rc3, it3, _ = a.gmres(b, x0=np.zeros_like(b), m=80, max_iter=400, tol=1e-12)
+    assert it3 == it and np.array_equal(xs3, xs)
+    a.delete()
+
+
 def test_gmres_count_sensitivity_of_the_oracle(golden):
     """Evidence for the tolerance above (CPU only, no device work): a 1e-15 relative perturbation of b changes the
     oracle's own iteration count on a16, because the residual stalls at 1e-12 = tol."""
