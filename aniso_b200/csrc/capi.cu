@@ -319,6 +319,10 @@ void ensure_device(aniso_handle* h) {
         S.tx = dalloc<double2>(h, (size_t)N + 1);
         CK(cudaMemsetAsync(const_cast<double2*>(S.ty), 0, sizeof(double2) * ((size_t)N + 1), h->st));
         CK(cudaMemsetAsync(const_cast<double2*>(S.tx), 0, sizeof(double2) * ((size_t)N + 1), h->st));
+        S.dty = dalloc<double2>(h, (size_t)N + 1);
+        S.dtx = dalloc<double2>(h, (size_t)N + 1);
+        CK(cudaMemsetAsync(const_cast<double2*>(S.dty), 0, sizeof(double2) * ((size_t)N + 1), h->st));
+        CK(cudaMemsetAsync(const_cast<double2*>(S.dtx), 0, sizeof(double2) * ((size_t)N + 1), h->st));
     }
     // work space
     h->d_f = dalloc<double>(h, N); h->d_q = dalloc<double>(h, N); h->d_pot = dalloc<double>(h, N);

@@ -21,6 +21,10 @@ struct SigmaGrid {
     //   tx[cy*sz + i] = { h * sum_{i' < i} sigma[i'][cy], sigma[i][cy] }     (along x inside row cy)
     const double2* ty = nullptr;
     const double2* tx = nullptr;
+    // differences of neighbouring lines, dty[cx*sz + j] = ty[cx*sz + j] - ty[(cx+1)*sz + j] (dtx alike): what a ray adds when
+    // it crosses from line cx to cx + 1
+    const double2* dty = nullptr;
+    const double2* dtx = nullptr;
 };
 
 // block-CSR operator (see plan.hpp BlockCSR); all pointers are device memory

@@ -149,22 +149,24 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
     const double2 e0 = __ldg(tab + (size_t)c0 * sz + j0), e1 = __ldg(tab + (size_t)c1 * sz + j1);
     double acc = (e1.x - e0.x) + (fma(e1.y, fma(-jd1, h, v1), -e0.y * fma(-jd0, h, v0)));
     if (c0 != c1) {
+        // Crossing from line c to c + 1 at v_b contributes F_c(v_b) - F_{c+1}(v_b) = D[c][j].x + D[c][j].y (v_b - j h) with the
+        // difference table D[c][j] = tab[c][j] - tab[c+1][j] (built with the tables): ONE 16-byte read per crossing.  Going
+        // down (c -> c - 1) the term is -D[c-1][j]; the sign is applied once to the sum.
         const double slope = dv * __drcp_rn(du);  // crossing positions tolerate the extra ulp
         const int sgn = c1 > c0 ? 1 : -1, ncross = abs(c1 - c0);
         double bd = (double)(c1 > c0 ? c0 + 1 : c0);
         const double sd = (double)sgn;
-        const double2* __restrict__ row = tab + (size_t)c0 * sz;
+        const double2* __restrict__ row = (steep ? S.dty : S.dtx) + (size_t)(c1 > c0 ? c0 : c0 - 1) * sz;
         const ptrdiff_t rstep = (ptrdiff_t)sgn * sz;
-        double acc2 = 0;
+        double cr0 = 0, cr1 = 0;
         int k = 0;
-        for (; k + 2 <= ncross; k += 2) {  // two crossings per trip: four independent table reads in flight
+        for (; k + 2 <= ncross; k += 2) {  // two crossings per trip: two independent table reads in flight
             const double vb0 = fma(fma(bd, h, -u0), slope, v0), vb1 = fma(fma(bd + sd, h, -u0), slope, v0);
             int ja, jb;
             const double jda = magic_floor_inner(vb0, szd, ja), jdb = magic_floor_inner(vb1, szd, jb);
-            const double2 a0 = __ldg(row + ja), a1 = __ldg(row + rstep + ja);
-            const double2 b0 = __ldg(row + rstep + jb), b1 = __ldg(row + 2 * rstep + jb);
-            acc = acc + ((a0.x - a1.x) + (a0.y - a1.y) * fma(-jda, h, vb0));
-            acc2 = acc2 + ((b0.x - b1.x) + (b0.y - b1.y) * fma(-jdb, h, vb1));
+            const double2 d0 = __ldg(row + ja), d1 = __ldg(row + rstep + jb);
+            cr0 += fma(d0.y, fma(-jda, h, vb0), d0.x);
+            cr1 += fma(d1.y, fma(-jdb, h, vb1), d1.x);
             bd += 2.0 * sd;
             row += 2 * rstep;
         }
@@ -172,10 +174,10 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
             const double vb0 = fma(fma(bd, h, -u0), slope, v0);
             int ja;
             const double jda = magic_floor_inner(vb0, szd, ja);
-            const double2 a0 = __ldg(row + ja), a1 = __ldg(row + rstep + ja);
-            acc = acc + ((a0.x - a1.x) + (a0.y - a1.y) * fma(-jda, h, vb0));
+            const double2 d0 = __ldg(row + ja);
+            cr0 += fma(d0.y, fma(-jda, h, vb0), d0.x);
         }
-        acc += acc2;
+        acc = fma(sd, cr0 + cr1, acc);
     }
     return acc * (len * __drcp_rn(dv));
 }
@@ -626,8 +628,22 @@ __global__ void sigma_prefix_kernel(SigmaGrid S, double2* __restrict__ ty, doubl
         }
     }
 }
+// Difference tables of neighbouring lines, D[c][j] = t[c][j] - t[c+1][j] (line sz-1 has no upper neighbour: zeros)
+__global__ void sigma_diff_kernel(int sz, const double2* __restrict__ ty, const double2* __restrict__ tx, double2* __restrict__ dty,
+                                  double2* __restrict__ dtx) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)sz * (sz - 1)) return;
+    const double2 a = ty[i], b = ty[i + sz], c = tx[i], d = tx[i + sz];
+    dty[i] = make_double2(a.x - b.x, a.y - b.y);
+    dtx[i] = make_double2(c.x - d.x, c.y - d.y);
+}
 void launch_sigma_prefix(const SigmaGrid& S, double2* ty, double2* tx, cudaStream_t st) {
     sigma_prefix_kernel<<<(2 * S.sz + 63) / 64, 64, 0, st>>>(S, ty, tx);
+    if (S.sz > 1) {
+        const size_t n = (size_t)S.sz * (S.sz - 1);
+        sigma_diff_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(S.sz, ty, tx, const_cast<double2*>(S.dty),
+                                                                      const_cast<double2*>(S.dtx));
+    }
 }
 
 }  // namespace an

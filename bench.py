@@ -57,7 +57,11 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc, self.t = index, [], None, None
+        self.index, self.rows, self.proc, self.t, self.start = index, [], None, None, 0
+
+    def mark(self):
+        """Rows before this point (sampler start-up, warm-up) are not part of the summary."""
+        self.start = len(self.rows)
 
     def _read(self):
         for line in self.proc.stdout:
@@ -84,7 +88,7 @@ class ClockSampler:
             self.t.join(timeout=5)
 
     def summary(self):
-        ok = [r for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        ok = [r for r in self.rows[self.start:] if len(r) >= 6 and r[0].replace(".", "").isdigit()]
         sm = [float(r[0]) for r in ok]
         mx = [float(r[1]) for r in ok if r[1].replace(".", "").isdigit()]
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
@@ -315,15 +319,16 @@ def run_ours(args):
         _lib.check(L.aniso_forward_dev(a.h, x_own.data_ptr(), y_own.data_ptr()))
 
     # ---- device-resident timed region ----
+    clk = ClockSampler(local)
+    clk.__enter__()  # started before the warm-up: nvidia-smi needs up to a second before its first row on an 8-GPU box
     for _ in range(max(args.warmup, 3)):
         step()
     a.synchronize()
     barrier()
     l0 = a.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    clk = ClockSampler(local)
-    clk.__enter__()
-    time.sleep(0.12)  # let the sampler produce its first rows
+    time.sleep(0.12)
+    clk.mark()
     e0.record(stream)
     for _ in range(args.steps):
         step()
@@ -361,9 +366,17 @@ def run_ours(args):
     tr = a.tree_stats()
     m2l_ms = max_over_ranks(a.time_kernel(0, 0, 50))
     p2p_ms = max_over_ranks(a.time_kernel(0, 1, 50))
-    for _ in range(200):  # keep the device under load long enough for the clock sampler to see it
-        step()
-    a.synchronize()
+    # keep the device under the same load until the sampler has seen it on every rank (a 30-step timed region is 6 - 20 ms,
+    # one sampler period is 50 ms); the number of extra steps is agreed between the ranks, step() holds a collective
+    for batch in range(300):
+        for _ in range(100):
+            step()
+        a.synchronize()
+        have = torch.tensor([len(clk.rows) - clk.start], dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.all_reduce(have, op=dist.ReduceOp.MIN)
+        if batch >= 1 and int(have.item()) >= 3:
+            break
     clk.__exit__()
     r = NP_ORDER * NP_ORDER
     m2l_alg = ab["m2l"] + 8 * r * tr["nodes"]  # stored blocks + scratch rows written + multipoles read
