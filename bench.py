@@ -108,14 +108,28 @@ def reference_sample_sz(cores):
     return 256 if cores >= 16 else 128
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm is one process that must use every host core.
+    The variable only matters until libgomp has read it, so the run-time call is made as well."""
+    import ctypes
+
+    cores = host_cores()
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(cores)
+    except OSError:
+        pass
+    return cores
+
+
 def run_reference(args):
     """The reference's own CPU implementation (compiled unmodified, its own -Ofast/-ffast-math flags, OpenMP on all
     host cores) on a bounded sample; rank 0 only."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
+    cores = use_all_host_threads()
     from oracle import refapi  # the one place bench.py executes oracle/ besides cpu_baseline
 
-    cores = host_cores()
     sz = args.ref_sz or reference_sample_sz(cores)
     kind = "reference" if refapi.available(fast=True) else "port"
     if kind == "reference":
@@ -125,6 +139,8 @@ def run_reference(args):
 
         r = oracleapi.OracleAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
         cores = 1
+    if kind == "reference":
+        cores = int(r.num_threads())  # the threads the reference's OpenMP regions actually get
     x, y, w = r.nodes()
     ss, st = cases.sigma_fields("layers", x, y, sz, 1)
     t0 = time.perf_counter()
