@@ -261,9 +261,25 @@ __global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, 
         const int nrow = s_off[j][2], ncol = s_off[j][3];
         double* __restrict__ out = A + s_blk[j];
         const int total = nrow * ncol;
-        for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-            const int s = NR ? idx / NR : idx / nrow;
-            const int t = (NR ? idx % NR : idx % nrow) ^ (m.swz ? (s & 3) << 2 : 0);  // idx is the stored position
+        for (int idx0 = threadIdx.x; idx0 < total; idx0 += blockDim.x) {
+            int idx = idx0;
+            int s = NR ? idx / NR : idx / nrow;
+            int t = (NR ? idx % NR : idx % nrow) ^ (m.swz ? (s & 3) << 2 : 0);  // idx is the stored position
+            if (NR == 16 && cheb) {
+                // 4 x 4 Chebyshev nodes per box: the number of grid lines a ray crosses along its minor axis - the trip count
+                // of the line integral - is fixed by the two node indices along that axis.  Give the 16 lanes of a half-warp
+                // the same pair of minor-axis indices (and all 16 pairs of major-axis indices), so that the lanes of a warp
+                // leave the crossing loop together; the minor axis is taken from the box centres.
+                const double* __restrict__ gg = s_geo[j];
+                const bool xmajor = fabs(gg[4] - gg[0]) >= fabs(gg[5] - gg[1]);
+                const int hi = (idx0 >> 4) & 15, lo = idx0 & 15;  // hi: constant over a half-warp
+                const int mn = xmajor ? hi : lo, mj = xmajor ? lo : hi;  // (source, target) index pairs along minor / major
+                const int sj = xmajor ? mn >> 2 : mj >> 2, tj = xmajor ? mn & 3 : mj & 3;  // y indices
+                const int si = xmajor ? mj >> 2 : mn >> 2, ti = xmajor ? mj & 3 : mn & 3;  // x indices
+                s = sj * 4 + si;
+                t = tj * 4 + ti;
+                idx = s * 16 + (t ^ (m.swz ? (s & 3) << 2 : 0));
+            }
             double ax, ay, bx, by;
             if (cheb) {  // flat = j*np + i, y slow (bbfmm.h:787-800)
                 const double* __restrict__ gg = s_geo[j];
