@@ -129,7 +129,10 @@ int aniso_singular_add_fast(aniso_t* h, int id, const double* fcoeff_host, doubl
 /* GMRES(A, x, b, m, max_iter, tol) gmres.cpp:53-169 with A = forwardOperator (main.cpp:123-136), device-resident
  * Arnoldi.  x_host: initial guess in, solution out.  Returns 0 converged / 1 not converged (like the reference) or a
  * negative error.  resid_hist[j-1] = relative residual the reference prints at iteration j, resid_hist[*iters] = the
- * final one (hist_cap entries available; may be NULL). */
+ * final one (hist_cap entries available; may be NULL).  The Krylov basis is orthogonalised by classical Gram-Schmidt
+ * applied twice (same Hessenberg entries to rounding and the same iteration counts as the reference's modified
+ * Gram-Schmidt, gmres.cpp:115-119, which ANISO_GMRES_ORTHO=mgs selects); a zero x_host skips the first operator
+ * application (r = b). */
 int aniso_gmres(aniso_t* h, const double* b_host, double* x_host, int m, int max_iter, double tol, int* iters,
                 double* resid_hist, int hist_cap);
 /* Same with device vectors in slot order (owned range), no host copies of vectors. */
