@@ -173,3 +173,31 @@ def test_mex_gateway_compiles_against_stub_mex():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = subprocess.run(["make", "-s", "-C", os.path.join(root, "oracle"), "mexcheck"], capture_output=True, text=True)
     assert out.returncode == 0 and "mexcheck ok" in out.stdout, out.stderr[-2000:]
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference`: runs on the host cores without a GPU, prints one JSON line with the contract
+    keys, uses every available core even when the launcher exported OMP_NUM_THREADS=1 (torchrun does), and only on rank 0."""
+    import json
+    import subprocess
+    import sys
+
+    from oracle import refapi
+
+    if not refapi.available(fast=True):
+        pytest.skip("oracle/_ref not built")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    cmd = [sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--ref-sz", "32"]
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600, cwd=root)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "config",
+                "cpu_baseline", "e2e"):
+        assert key in line
+    assert line["impl"] == "reference" and line["value"] > 0 and line["gpu_launches"] == 0
+    assert line["cpu_baseline"]["kind"] == "reference"
+    assert line["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["value"] == line["value"]
+    other = subprocess.run(cmd, env=dict(env, RANK="1", WORLD_SIZE="2"), capture_output=True, text=True, timeout=600, cwd=root)
+    assert other.returncode == 0 and other.stdout.strip() == ""
