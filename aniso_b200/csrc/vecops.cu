@@ -292,8 +292,16 @@ void launch_multi_axpy(int n, int nv, const double* h, const double* V, size_t l
 // loads, coalesced across the warp) and walks the basis vectors with eight 16-byte loads in flight; per vector the warp
 // sum goes to a per-warp slot in shared memory, block sums to `partial`, and the last block to finish adds them in a fixed
 // order (deterministic, identical on every rank).
+// CGS_U 16-byte elements of w per thread, CGS_KU basis vectors per trip of the walk (CGS_U * CGS_KU loads in flight per
+// thread), CGS_CTAS resident CTAs per SM
+#ifndef CGS_U
+#define CGS_U 2
+#define CGS_KU 4
+#define CGS_CTAS 4
+#endif
+static constexpr int kCgsKU = CGS_KU;
 template <int MODE>
-__global__ void __launch_bounds__(256, 3) cgs_pass_kernel(int n, int nv, const double* __restrict__ h_in, const double* __restrict__ V,
+__global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, const double* __restrict__ h_in, const double* __restrict__ V,
                                                           size_t ldv, double* __restrict__ w, double* __restrict__ partial,
                                                           double* __restrict__ out, unsigned int* __restrict__ counter) {
     extern __shared__ double cg_sm[];  // hs[nv] | wpart[nout][8]
@@ -309,51 +317,51 @@ __global__ void __launch_bounds__(256, 3) cgs_pass_kernel(int n, int nv, const d
     const int per = (npair + gridDim.x - 1) / gridDim.x;
     const int p0 = blockIdx.x * per, p1 = min(npair, p0 + per);
     double2* __restrict__ w2 = reinterpret_cast<double2*>(w);
-    for (int c = p0; c < p1; c += 1024) {
-        int idx[4];
-        bool ok[4];
-        double2 a[4];
+    for (int c = p0; c < p1; c += 256 * CGS_U) {
+        int idx[CGS_U];
+        bool ok[CGS_U];
+        double2 a[CGS_U];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < CGS_U; ++u) {
             idx[u] = c + u * 256 + threadIdx.x;
             ok[u] = idx[u] < p1;
             a[u] = ok[u] ? w2[idx[u]] : make_double2(0.0, 0.0);
         }
         if (MODE) {
-#pragma unroll 2
+#pragma unroll kCgsKU
             for (int k = 0; k < nv; ++k) {
                 const double2* __restrict__ Vk = reinterpret_cast<const double2*>(V + (size_t)k * ldv);
                 const double hk = -hs[k];
-                double2 v[4];
+                double2 v[CGS_U];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) v[u] = ok[u] ? Vk[idx[u]] : make_double2(0.0, 0.0);
+                for (int u = 0; u < CGS_U; ++u) v[u] = ok[u] ? Vk[idx[u]] : make_double2(0.0, 0.0);
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < CGS_U; ++u) {
                     a[u].x = fma(hk, v[u].x, a[u].x);
                     a[u].y = fma(hk, v[u].y, a[u].y);
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < CGS_U; ++u)
                 if (ok[u]) w2[idx[u]] = a[u];
         }
         if (MODE == 2) {
             double s = 0;
 #pragma unroll
-            for (int u = 0; u < 4; ++u) s = fma(a[u].x, a[u].x, fma(a[u].y, a[u].y, s));
+            for (int u = 0; u < CGS_U; ++u) s = fma(a[u].x, a[u].x, fma(a[u].y, a[u].y, s));
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
             if (lane == 0) wpart[warp] += s;
         } else {
-#pragma unroll 2
+#pragma unroll kCgsKU
             for (int k = 0; k < nv; ++k) {
                 const double2* __restrict__ Vk = reinterpret_cast<const double2*>(V + (size_t)k * ldv);
-                double2 v[4];
+                double2 v[CGS_U];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) v[u] = ok[u] ? Vk[idx[u]] : make_double2(0.0, 0.0);
+                for (int u = 0; u < CGS_U; ++u) v[u] = ok[u] ? Vk[idx[u]] : make_double2(0.0, 0.0);
                 double s0 = 0, s1 = 0;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < CGS_U; ++u) {
                     s0 = fma(a[u].x, v[u].x, s0);
                     s1 = fma(a[u].y, v[u].y, s1);
                 }
@@ -401,7 +409,7 @@ bool cgs_pass_ok(int n, int nv, const double* V, size_t ldv, const double* w) {
 void launch_cgs_pass(int mode, int n, int nv, const double* h_in, const double* V, size_t ldv, double* w, double* out, double* partial,
                      DotWork& wk, cudaStream_t st) {
     const int npair = n >> 1;
-    int nb = std::min(std::min(444, wk.blocks), (npair + 1023) / 1024);  // 148 SMs x 3 resident CTAs: one balanced wave
+    int nb = std::min(std::min(148 * CGS_CTAS, wk.blocks), (npair + 256 * CGS_U - 1) / (256 * CGS_U));  // one balanced wave of resident CTAs
     if (nb < 1) nb = 1;
     const int nout = mode == 2 ? 1 : nv;
     const size_t smem = (size_t)(nv + 8 * nout) * sizeof(double);
