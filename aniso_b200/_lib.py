@@ -15,6 +15,9 @@ _lp = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
 _H = C.c_void_p
 _V = C.c_void_p  # raw device pointer
 
+# host preconditioner callback of aniso_gmres_prec / aniso_block_gmres_prec: int (*)(void* ctx, int n, const double* r, double* z)
+PREC_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double))
+
 # name -> (restype, argtypes): exactly the symbols include/aniso_b200.h declares
 SIGNATURES = {
     "aniso_last_error": (C.c_char_p, []),
@@ -54,6 +57,9 @@ SIGNATURES = {
     "aniso_singular_add_fast": (C.c_int, [_H, C.c_int, _dp, _dp]),
     "aniso_gmres": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
     "aniso_gmres_dev": (C.c_int, [_H, _V, _V, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
+    "aniso_gmres_prec": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, PREC_FN, C.c_void_p, C.POINTER(C.c_int), _dp, C.c_int]),
+    "aniso_block_gmres_prec": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, PREC_FN, C.c_void_p, C.POINTER(C.c_int), _dp,
+                                          C.c_int]),
     "aniso_block_forward": (C.c_int, [_H, _dp, C.c_int, _dp]),
     "aniso_block_forward_dev": (C.c_int, [_H, _V, C.c_int, _V]),
     "aniso_block_gmres": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
@@ -72,6 +78,8 @@ SIGNATURES = {
     "aniso_launch_count": (C.c_int64, [_H]),
     "aniso_apply_bytes": (C.c_int, [_H, _lp]),
     "aniso_time_kernel": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "aniso_time_forward": (C.c_int, [_H, C.c_int, C.POINTER(C.c_double)]),
+    "aniso_get_config": (C.c_char_p, [_H]),
 }
 
 _lib = None

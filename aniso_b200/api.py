@@ -137,13 +137,34 @@ class Aniso:
         return {k: self.L.aniso_cache_bytes(self.h, k) / 1e6 for k in range(self.kernelSize)}
 
     # -- GMRES (gmres.cpp:53-169 with the operator of main.cpp:123-136) ---------------------------------------
-    def gmres(self, b, x0=None, m=80, max_iter=400, tol=1e-12):
+    @staticmethod
+    def _prec_callback(prec):
+        """Wraps prec(r) -> z (numpy vectors, reference node order) as the C callback of aniso_gmres_prec."""
+        def cb(ctx, n, r, z):
+            try:
+                out = np.asarray(prec(np.ctypeslib.as_array(r, shape=(n,)).copy()), dtype=np.float64).reshape(-1)
+                if out.size != n:
+                    return 2
+                np.ctypeslib.as_array(z, shape=(n,))[:] = out
+                return 0
+            except Exception:  # no exception may cross the C boundary
+                return 1
+        return _lib.PREC_FN(cb)
+
+    def gmres(self, b, x0=None, m=80, max_iter=400, tol=1e-12, prec=None):
+        """GMRES(A, x, b, m, max_iter, tol) of gmres.cpp:53-169 on the operator of main.cpp:123-136; prec: optional left
+        preconditioner r -> M^-1 r on host vectors (the hook aniso.m:165 hands to MATLAB's gmres)."""
         n = self.numberOfNodes
         x = np.zeros(n) if x0 is None else _vec(x0, n).copy()
         it = C.c_int(0)
         hist = np.zeros(max_iter + 2)
-        rc = _lib.check(self.L.aniso_gmres(self.h, _vec(b, n), x, int(m), int(max_iter), float(tol), C.byref(it), hist,
-                                           hist.size))
+        if prec is None:
+            rc = _lib.check(self.L.aniso_gmres(self.h, _vec(b, n), x, int(m), int(max_iter), float(tol), C.byref(it), hist,
+                                               hist.size))
+        else:
+            cb = self._prec_callback(prec)
+            rc = _lib.check(self.L.aniso_gmres_prec(self.h, _vec(b, n), x, int(m), int(max_iter), float(tol), cb, None,
+                                                    C.byref(it), hist, hist.size))
         return x, rc, it.value, hist[: it.value + 1]
 
     # -- MATLAB application layer (aniso.m:121-172): multi-mode block operator ------------------------------------
@@ -161,15 +182,23 @@ class Aniso:
         _lib.check(self.L.aniso_block_forward(self.h, _vec(u, n * self.numberOfNodes, "u"), 1, out))
         return out
 
-    def solve(self, charge, m=400, max_iter=400, tol=1e-11):
-        """aniso.m:158-172 without preconditioner: rhs = forward(charge); (I - mforward) y = rhs by GMRES(400, 1e-11, 400)
-        (the reference's gmres.cpp; MATLAB's gmres is the caller there).  Returns (y, rc, iterations, residual history)."""
+    def solve(self, charge, m=400, max_iter=400, tol=1e-11, prec=None):
+        """aniso.m:158-172: rhs = forward(charge); (I - mforward) y = rhs by GMRES(400, 1e-11, 400) (the reference's
+        gmres.cpp; MATLAB's gmres is the caller there); prec = the `pr == 1` branch (aniso.m:165), a callable r -> M^-1 r on
+        K*N host values.  max_iter counts Arnoldi steps in total (gmres.cpp semantics); MATLAB's gmres(restart 400, maxit 400)
+        would allow 400 outer cycles of 400 - a difference that only matters for solves that do not converge in 400 steps.
+        Returns (y, rc, iterations, residual history)."""
         K = self.kernelSize // 2 + 1
         rhs = self.forward(charge)
         x = np.zeros(K * self.numberOfNodes)
         it = C.c_int(0)
         hist = np.zeros(max_iter + 2)
-        rc = _lib.check(self.L.aniso_block_gmres(self.h, rhs, x, int(m), int(max_iter), float(tol), C.byref(it), hist, hist.size))
+        if prec is None:
+            rc = _lib.check(self.L.aniso_block_gmres(self.h, rhs, x, int(m), int(max_iter), float(tol), C.byref(it), hist, hist.size))
+        else:
+            cb = self._prec_callback(prec)
+            rc = _lib.check(self.L.aniso_block_gmres_prec(self.h, rhs, x, int(m), int(max_iter), float(tol), cb, None,
+                                                          C.byref(it), hist, hist.size))
         return x, rc, it.value, hist[: it.value + 1]
 
     # -- probes / introspection ---------------------------------------------------------------------------------
@@ -257,6 +286,15 @@ class Aniso:
         o = np.zeros(3)
         _lib.check(self.L.aniso_cache_times(self.h, o))
         return dict(p2p_fill_ms=float(o[0]), m2l_fill_ms=float(o[1]), stencil_ms=float(o[2]))
+
+    def time_forward(self, reps):
+        """average device milliseconds of one application of the GMRES operator (CUDA events on the handle's stream)"""
+        ms = C.c_double()
+        _lib.check(self.L.aniso_time_forward(self.h, int(reps), C.byref(ms)))
+        return ms.value
+
+    def config(self):
+        return self.L.aniso_get_config(self.h).decode()
 
     def time_kernel(self, kid, which, reps):
         ms = C.c_double()

@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <functional>
 #include <map>
 #include <stdexcept>
 #include <string>
@@ -82,10 +83,19 @@ struct aniso_handle {
     double *d_blk_full = nullptr, *d_blk_tmp = nullptr;  // block operator work space
     double *d_blk_q = nullptr, *d_blk_f = nullptr, *d_blk_mc = nullptr, *d_blk_sm = nullptr, *d_blk_sp = nullptr;  // batched form
     double *d_blk_wq = nullptr, *d_blk_wf = nullptr, *d_blk_wm = nullptr;  // regrouped form: inputs of the (kernel id, output mode) pairs
+    double *d_gm_b = nullptr, *d_gm_x = nullptr, *d_blk_gm = nullptr, *d_blk_io = nullptr;  // device copies of host right-hand sides / iterates
     double* gm_buf = nullptr;   // Krylov work space, kept between solves ((m+3) vectors + CGS2 partials)
     size_t gm_cap = 0;
-    double* pinned_small = nullptr;  // 2048 doubles: Hessenberg column read-back
+    double* pinned_small = nullptr;  // Hessenberg column / step report read-back (2m + 8 doubles)
+    size_t pinned_small_cap = 0;
+    cudaEvent_t gm_ev[2] = {nullptr, nullptr};  // pipelined Arnoldi: report of step i has arrived
     double* pinned = nullptr;  // 2N doubles
+    // sharded host path (nranks > 1): every rank moves 1/nranks of a host vector over PCIe, the rest travels over NVLink
+    double* d_stage_pad = nullptr;     // nranks * stage_chunk doubles: in-place all-gather of the uploaded pieces
+    int stage_chunk = 0;
+    int* d_own_sorted = nullptr;       // owned rows (relative slots) sorted by reference node index
+    struct Copy2D { size_t ref_start, stage_off, run, pitch, nruns; };
+    std::vector<Copy2D> own_copies;    // strided device -> host copies that put the owned rows at their reference positions
     std::map<std::pair<int, int>, OperatorCache> ops;
     std::map<int, StencilCache> stencils;
     int64_t launches = 0;
@@ -348,6 +358,34 @@ void ensure_device(aniso_handle* h) {
         ncclResult_t rc = h->nccl->CommInitRank(&h->comm, h->nranks, id, h->rank);
         if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclCommInitRank: ") + h->nccl->GetErrorString(rc));
     }
+    if (h->nranks > 1) {
+        // host path of the sharded handle: padded staging vector for the in-place all-gather of uploaded pieces, and the
+        // strided copies that return the owned rows to their places in a reference-order host vector
+        h->stage_chunk = (N + h->nranks - 1) / h->nranks;
+        h->d_stage_pad = dalloc<double>(h, (size_t)h->stage_chunk * h->nranks);
+        std::vector<std::pair<int, int>> own(h->nown);  // (reference index, relative slot)
+        for (int k = 0; k < h->nown; ++k) own[k] = {p.perm[h->slot0 + k], k};
+        std::sort(own.begin(), own.end());
+        std::vector<int> rel(h->nown);
+        for (int k = 0; k < h->nown; ++k) rel[k] = own[k].second;
+        h->d_own_sorted = upload(h, rel);
+        std::vector<std::pair<size_t, size_t>> runs;  // (reference start, length)
+        for (int k = 0; k < h->nown;) {
+            int e = k + 1;
+            while (e < h->nown && own[e].first == own[e - 1].first + 1) ++e;
+            runs.push_back({(size_t)own[k].first, (size_t)(e - k)});
+            k = e;
+        }
+        size_t off = 0;
+        for (size_t i = 0; i < runs.size();) {  // runs of one length at a constant pitch form one 2-D copy
+            size_t j = i + 1;
+            const size_t pitch = j < runs.size() ? runs[j].first - runs[i].first : runs[i].second;
+            while (j < runs.size() && runs[j].second == runs[i].second && runs[j].first - runs[j - 1].first == pitch) ++j;
+            h->own_copies.push_back({runs[i].first, off, runs[i].second, std::max(pitch, runs[i].second), j - i});
+            off += runs[i].second * (j - i);
+            i = j;
+        }
+    }
     CK(cudaStreamSynchronize(h->st));
     h->dev_ready = true;
 }
@@ -464,6 +502,8 @@ int aniso_destroy(aniso_t* h) {
         for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join})
             if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : h->copy_ev) cudaEventDestroy(e);
+        for (cudaEvent_t e : h->gm_ev)
+            if (e) cudaEventDestroy(e);
         cudaStreamDestroy(h->st_bulk);
         cudaStreamDestroy(h->st);
     }
@@ -594,6 +634,14 @@ void free_caches(aniso_handle* h) {
         dfree(h, kv.second.c7); dfree(h, kv.second.c8); dfree(h, kv.second.c9); dfree(h, kv.second.call);
     }
     h->stencils.clear();
+}
+
+// The probes evaluate the kernel family between arbitrary points.  Every point the matvec itself uses (nodes, Chebyshev
+// nodes of tree boxes) lies inside the unit square, where the table line integral needs no clamp of its crossing
+// indices; points outside it are rejected here instead of being extended by the reference's getRow/getCol clamp.
+void check_probe_points(int n, const double* pts4) {
+    for (int i = 0; i < 4 * n; ++i)
+        if (!(pts4[i] >= 0.0 && pts4[i] <= 1.0)) throw std::invalid_argument("probe point outside the unit square");
 }
 
 void check_id(const aniso_handle* h, int id) {
@@ -728,6 +776,7 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     join(deepest);
     LAUNCH(h, launch_l2p(T, h->G, h->p2p, sym_p, h->d_leaf_of_slot, h->slot0, h->nown, h->d_mpot, h->d_pot, stencil, f, x_own, out,
                          mode, h->st));
+    CK(cudaGetLastError());
 }
 
 // all-gather of the owned shards into a full slot-order vector; counts differ per rank, so this is a
@@ -792,25 +841,43 @@ bool is_pinned(const void* p) {
     }
     return a.type == cudaMemoryTypeHost;
 }
-void stage_h2d(aniso_handle* h, const double* host) {
-    const int N = h->plan.N;
+void stage_h2d_range(aniso_handle* h, const double* host, int lo, int cnt, double* dst) {  // host[lo, lo+cnt) -> dst[lo, lo+cnt)
+    if (cnt <= 0) return;
     if (is_pinned(host)) {  // caller's page-locked memory: one direct DMA
-        CK(cudaMemcpyAsync(h->d_stage, host, sizeof(double) * N, cudaMemcpyHostToDevice, h->st));
+        CK(cudaMemcpyAsync(dst + lo, host + lo, sizeof(double) * cnt, cudaMemcpyHostToDevice, h->st));
         return;
     }
     CK(cudaStreamSynchronize(h->st));
-    for (int off = 0; off < N; off += COPY_CHUNK) {
-        const int n = std::min(COPY_CHUNK, N - off);
+    for (int off = lo; off < lo + cnt; off += COPY_CHUNK) {
+        const int n = std::min(COPY_CHUNK, lo + cnt - off);
         std::memcpy(h->pinned + off, host + off, sizeof(double) * n);
-        CK(cudaMemcpyAsync(h->d_stage + off, h->pinned + off, sizeof(double) * n, cudaMemcpyHostToDevice, h->st));
+        CK(cudaMemcpyAsync(dst + off, h->pinned + off, sizeof(double) * n, cudaMemcpyHostToDevice, h->st));
     }
+}
+void stage_h2d(aniso_handle* h, const double* host) { stage_h2d_range(h, host, 0, h->plan.N, h->d_stage); }
+
+// A host vector every rank holds (reference order) -> the full vector on every device (reference order): each rank uploads
+// one contiguous 1/nranks piece and the pieces are all-gathered over NVLink, instead of nranks full copies through the
+// host's PCIe root.  Returns the device vector.  ANISO_HOST_FULL_COPY=1: the plain full upload (A/B switch).
+const double* stage_h2d_shared(aniso_handle* h, const double* host) {
+    static const bool full_copy = getenv("ANISO_HOST_FULL_COPY") != nullptr;
+    if (h->nranks == 1 || full_copy) {
+        stage_h2d(h, host);
+        return h->d_stage;
+    }
+    const int N = h->plan.N, lo = std::min(N, h->rank * h->stage_chunk), cnt = std::min(N, lo + h->stage_chunk) - lo;
+    stage_h2d_range(h, host, lo, cnt, h->d_stage_pad);
+    ncclResult_t rc = h->nccl->AllGather(h->d_stage_pad + (size_t)h->rank * h->stage_chunk, h->d_stage_pad, h->stage_chunk, ncclDouble,
+                                         h->comm, h->st);
+    if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather: ") + h->nccl->GetErrorString(rc));
+    return h->d_stage_pad;
 }
 
 // host (reference order) -> device slot order, full vector
 void to_slots(aniso_handle* h, const double* host, double* dev) {
     const int N = h->plan.N;
-    stage_h2d(h, host);
-    LAUNCH(h, launch_gather(N, h->d_stage, h->G.perm, dev, h->st));
+    const double* ref = stage_h2d_shared(h, host);
+    LAUNCH(h, launch_gather(N, ref, h->G.perm, dev, h->st));
 }
 // device owned rows (slot order) -> host reference order; rows owned by other ranks are left untouched
 void from_slots(aniso_handle* h, const double* dev_own, double* host) {
@@ -841,6 +908,16 @@ void from_slots(aniso_handle* h, const double* dev_own, double* host) {
             CK(cudaEventSynchronize(h->copy_ev[c]));
             std::memcpy(host + off, stage + off, sizeof(double) * n);
         }
+        return;
+    }
+    if (h->own_copies.size() <= 64 && !getenv("ANISO_HOST_FULL_COPY")) {
+        // owned rows sorted by reference index on the device, then one strided copy per group of equal runs (a quadtree
+        // box is sz/2^L runs of one length at pitch sz): no host-side scatter
+        LAUNCH(h, launch_gather(h->nown, dev_own, h->d_own_sorted, h->d_stage, h->st));
+        for (const auto& c : h->own_copies)
+            CK(cudaMemcpy2DAsync(host + c.ref_start, c.pitch * sizeof(double), h->d_stage + c.stage_off, c.run * sizeof(double),
+                                 c.run * sizeof(double), c.nruns, cudaMemcpyDeviceToHost, h->st));
+        CK(cudaStreamSynchronize(h->st));
         return;
     }
     CK(cudaMemcpyAsync(stage, dev_own, sizeof(double) * h->nown, cudaMemcpyDeviceToHost, h->st));
@@ -1037,6 +1114,7 @@ int aniso_line_integral(aniso_t* h, int n, const double* pts4, double* out) {
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede lineIntegral");
+    check_probe_points(n, pts4);
     double* d = dalloc<double>(h, (size_t)5 * n);
     CK(cudaMemcpyAsync(d, pts4, sizeof(double) * 4 * n, cudaMemcpyHostToDevice, h->st));
     LAUNCH(h, launch_probe_line_integral(h->S, n, d, d + 4 * (size_t)n, h->st));
@@ -1054,6 +1132,7 @@ int aniso_kernel_eval(aniso_t* h, int id, int part, int n, const double* pts4, d
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede kernel evaluation");
+    check_probe_points(n, pts4);
     double* d = dalloc<double>(h, (size_t)5 * n);
     CK(cudaMemcpyAsync(d, pts4, sizeof(double) * 4 * n, cudaMemcpyHostToDevice, h->st));
     LAUNCH(h, launch_probe_kernel(h->S, id, part, n, d, d + 4 * (size_t)n, h->st));
@@ -1295,16 +1374,58 @@ void gm_update(GmresWork& g, double* x, int k, const std::vector<double>& H, int
     for (int j = 0; j <= k; ++j) LAUNCH(g.h, launch_axpy(g.n, y[j], g.v(j), x, g.h->st));
 }
 
+// owned rows (slot order) of every rank -> the complete vector in reference order on this rank's host
+void slots_to_host_full(aniso_handle* h, const double* dev_own, double* host) {
+    if (h->nranks == 1) {
+        from_slots(h, dev_own, host);
+        return;
+    }
+    allgather_slots(h, dev_own, h->d_xfull);
+    LAUNCH(h, launch_scatter(h->plan.N, h->d_xfull, h->G.perm, h->d_stage, h->st));
+    CK(cudaMemcpyAsync(host, h->d_stage, sizeof(double) * h->plan.N, cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+}
+
+// Host preconditioner callback (aniso.m:111-119 `prec`, handed to MATLAB's gmres at aniso.m:165) as a device operator:
+// the vector goes to the host in reference node order (all `blocks` modes, complete on every rank), the callback maps
+// r -> z = M^-1 r, and z comes back.  On a sharded handle every rank runs the callback on the same data.
+struct HostPrec {
+    aniso_handle* h;
+    aniso_prec_fn fn;
+    void* ctx;
+    int blocks;
+    std::vector<double> r, z;
+    void operator()(double* v_own) {
+        const int N = h->plan.N, n = h->nown;
+        r.resize((size_t)blocks * N);
+        z.assign((size_t)blocks * N, 0.0);
+        for (int a = 0; a < blocks; ++a) slots_to_host_full(h, v_own + (size_t)a * n, r.data() + (size_t)a * N);
+        const int rc = fn(ctx, blocks * N, r.data(), z.data());
+        if (rc != 0) throw std::runtime_error("preconditioner callback returned " + std::to_string(rc));
+        for (int a = 0; a < blocks; ++a) {
+            to_slots(h, z.data() + (size_t)a * N, h->d_a);
+            CK(cudaMemcpyAsync(v_own + (size_t)a * n, h->d_a + h->slot0, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
+        }
+        CK(cudaStreamSynchronize(h->st));
+    }
+};
+
 // A: y = A x on device vectors of length n (owned rows; for the block operator K blocks of owned rows)
-template <class Op>
-int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
-               int hist_cap) {
+// P (optional): left preconditioner applied in place to a device vector, z = M^-1 r (MATLAB gmres(A, b, restart, tol, maxit, M1)
+// as called by aniso.m:165: the iteration runs on M^-1 A x = M^-1 b and the residual is measured in that norm)
+using DevOp = std::function<void(const double*, double*)>;
+using DevPrec = std::function<void(double*)>;
+
+int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* x, int m, int max_iter, double tol, int* iters,
+               double* hist, int hist_cap, const DevPrec* P = nullptr) {
     const int ldh = m + 1;
     GmresWork g{h, n, m, nullptr, nullptr, nullptr};
+    // device scalars of a solve: projections h1 / h2 (m + 2 each), then the state of the device-side Givens recurrence
+    const size_t nscal = (size_t)2 * (m + 2) + (size_t)ldh * m + (size_t)4 * (m + 1) + (size_t)2 * (m + 1) + 8;
     {
         // one allocation, kept in the handle between solves (680 MB at C5, m = 80: cudaMalloc/cudaFree of that size cost
         // milliseconds, a visible share of a 25 ms solve)
-        const size_t need = (size_t)(m + 3) * n + (size_t)(m + 1) * h->dot.blocks;
+        const size_t need = (size_t)(m + 4) * n + (size_t)(m + 1) * h->dot.blocks + nscal;
         if (h->gm_cap < need) {
             dfree(h, h->gm_buf);
             h->gm_buf = nullptr;
@@ -1312,13 +1433,31 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
             h->gm_buf = dalloc<double>(h, need);
             h->gm_cap = need;
         }
-        if (!h->pinned_small) CK(cudaMallocHost(&h->pinned_small, 2048 * sizeof(double)));
+        const size_t pin = (size_t)2 * m + 8;
+        if (h->pinned_small_cap < pin) {
+            if (h->pinned_small) CK(cudaFreeHost(h->pinned_small));
+            h->pinned_small = nullptr;
+            h->pinned_small_cap = 0;
+            CK(cudaMallocHost(&h->pinned_small, pin * sizeof(double)));
+            h->pinned_small_cap = pin;
+        }
+        for (auto& e : h->gm_ev)
+            if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     }
     g.w = h->gm_buf;
     g.r = g.w + n;
-    g.V = g.r + n;
-    double* dh = h->d_scal;  // device Hessenberg column, m+2 entries (+ m+2 for the second CGS2 pass)
-    if (2 * (m + 2) > 1024) throw std::invalid_argument("restart length m too large (max 510)");
+    double* pb = g.r + n;  // M^-1 b of a preconditioned solve
+    g.V = pb + n;
+    double* md_partial = g.V + (size_t)(m + 1) * n;
+    double* dh = md_partial + (size_t)(m + 1) * h->dot.blocks;  // h1: m + 2 entries
+    double* h2 = dh + m + 2;
+    double* dH = h2 + m + 2;                 // (m + 1) x m, column-major: the rotated Hessenberg matrix (device Givens)
+    double* dcs = dH + (size_t)ldh * m;
+    double* dsn = dcs + m + 1;
+    double* ds = dsn + m + 1;
+    double* dy = ds + m + 1;
+    double* drep = dy + m + 1;               // 2 per step: residual, converged flag
+    double* dbeta = drep + 2 * (m + 1);      // beta, |b|, x0 . x0
     // orthogonalisation: classical Gram-Schmidt applied twice in three fused passes over the basis (default; same
     // projections to rounding and the same iteration counts as the reference's modified Gram-Schmidt on every fixture, one
     // launch and one all-reduce per pass instead of i+1 dependent ones).  ANISO_GMRES_ORTHO=mgs: the reference's MGS
@@ -1326,7 +1465,6 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     const char* oenv = getenv("ANISO_GMRES_ORTHO");
     const bool cgs2 = oenv ? std::string(oenv) == "cgs2" || std::string(oenv) == "cgs2_unfused" : true;
     const bool cgs_fused = !(oenv && std::string(oenv) == "cgs2_unfused");
-    double* md_partial = g.V + (size_t)(m + 1) * n;
     double* col = h->pinned_small;
     std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0);
     int rc = 1, j = 1, i = 0;
@@ -1341,37 +1479,102 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
     const auto gt_t0 = std::chrono::steady_clock::now();
     if (gt_on)
         for (auto& e : gt_ev) CK(cudaEventCreate(&e));
+    // Pipelined Arnoldi (default): Hessenberg column, Givens rotations and the stopping test stay on the device
+    // (givens_step_kernel); the host queues step i+1 and only then waits for the 16-byte report of step i, so the device
+    // never idles between steps.  When step i reports convergence exactly one surplus step has been queued - on every rank
+    // alike, since all ranks see the same all-reduced scalars - and its results are discarded.  The synchronous form (read the
+    // column back, rotate on the host like gmres.cpp:123-144) remains for MGS, the two-launch CGS2, a host preconditioner,
+    // the timers and ANISO_GMRES_SYNC=1.
+    const bool pipelined = cgs2 && cgs_fused && !P && !gt_on && !getenv("ANISO_GMRES_SYNC") && cgs_pass_ok(n, 1, g.V, (size_t)n, g.w);
+    const double* bb = b;  // right-hand side of the iteration: b or M^-1 b
+    if (P) {
+        CK(cudaMemcpyAsync(pb, b, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
+        (*P)(pb);
+        bb = pb;
+    }
     // |b| and x0 . x0 come back in one read.  x0 = 0 (the usual start): A x0 = 0 exactly (the operator is linear and every
     // kernel of it maps zeros to zeros), so r = b and the first operator application (gmres.cpp:86) is not launched.
-    ddot_dev(h, n, b, b, dh + 2, true);
-    ddot_dev(h, n, x, x, dh + 3, false);
-    CK(cudaMemcpyAsync(col, dh + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    ddot_dev(h, n, bb, bb, dbeta + 1, true);
+    ddot_dev(h, n, x, x, dbeta + 2, false);
+    CK(cudaMemcpyAsync(col, dbeta + 1, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     double normb = col[0], beta;
     if (col[1] == 0.0) {
-        CK(cudaMemcpyAsync(g.r, b, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
-        CK(cudaMemcpyAsync(dh, dh + 2, sizeof(double), cudaMemcpyDeviceToDevice, h->st));
+        CK(cudaMemcpyAsync(g.r, bb, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
+        CK(cudaMemcpyAsync(dbeta, dbeta + 1, sizeof(double), cudaMemcpyDeviceToDevice, h->st));
         beta = normb;
     } else {
         A(x, g.w);
         LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
-        ddot_dev(h, n, g.r, g.r, dh, true);
-        beta = read_scalar(h, dh);
+        if (P) (*P)(g.r);
+        ddot_dev(h, n, g.r, g.r, dbeta, true);
+        beta = read_scalar(h, dbeta);
     }
     if (normb == 0.0) normb = 1;
     if ((resid = beta / normb) <= tol) {  // gmres.cpp:90 (<= here, < below: Q11)
         rc = 0;
         done = true;
     }
+    // the orthogonalisation of Arnoldi step i (w against v_0 .. v_i) with CGS2; leaves h1 in dh, h2 in h2, w . w in dh[i + 1]
+    auto orthogonalise_cgs2 = [&](int i) {
+        if (cgs_fused && cgs_pass_ok(n, i + 1, g.V, (size_t)n, g.w)) {
+            // three fused passes over the basis (vecops.cu cgs_pass_kernel): h1; w -= V h1 and h2; w -= V h2 and |w|^2
+            LAUNCH(h, launch_cgs_pass(0, n, i + 1, nullptr, g.V, (size_t)n, g.w, dh, md_partial, h->dot, h->st));
+            allreduce_scalars(h, dh, i + 1);
+            LAUNCH(h, launch_cgs_pass(1, n, i + 1, dh, g.V, (size_t)n, g.w, h2, md_partial, h->dot, h->st));
+            allreduce_scalars(h, h2, i + 1);
+            LAUNCH(h, launch_cgs_pass(2, n, i + 1, h2, g.V, (size_t)n, g.w, dh + i + 1, md_partial, h->dot, h->st));
+        } else {
+            for (int pass = 0; pass < 2; ++pass) {
+                double* hp = pass ? h2 : dh;
+                LAUNCH(h, launch_multi_dot(n, i + 1, g.w, g.V, (size_t)n, hp, md_partial, h->dot, h->st));
+                ++h->launches;
+                allreduce_scalars(h, hp, i + 1);
+                LAUNCH(h, launch_multi_axpy(n, i + 1, hp, g.V, (size_t)n, g.w, pass ? dh + i + 1 : nullptr, md_partial, h->dot, h->st));
+            }
+            ++h->launches;
+        }
+        allreduce_scalars(h, dh + i + 1, 1);
+    };
+    // everything of Arnoldi step i that the pipelined form queues without looking at results
+    auto queue_step = [&](int i) {
+        A(g.v(i), g.w);
+        orthogonalise_cgs2(i);
+        LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), 1, h->st));
+        LAUNCH(h, launch_givens_step(i, dh, h2, dh + i + 1, dbeta, dH, ldh, dcs, dsn, ds, normb, tol, drep + 2 * i, h->st));
+        CK(cudaMemcpyAsync(col + 2 * (i & 1), drep + 2 * i, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+        CK(cudaEventRecord(h->gm_ev[i & 1], h->st));
+    };
     while (!done && j <= max_iter) {
-        LAUNCH(h, launch_scale_inv_dev(n, dh, g.r, g.v(0), 0, h->st));  // dh[0] still holds beta
+        LAUNCH(h, launch_scale_inv_dev(n, dbeta, g.r, g.v(0), 0, h->st));
         std::fill(s.begin(), s.end(), 0.0);
         s[0] = beta;
+        if (pipelined) {
+            queue_step(0);
+            for (i = 0; i < m && j <= max_iter; ++i, ++j) {
+                if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
+                *iters = j;
+                if (i + 1 < m && j + 1 <= max_iter) queue_step(i + 1);  // one step ahead of the report being waited for
+                CK(cudaEventSynchronize(h->gm_ev[i & 1]));
+                resid = col[2 * (i & 1)];
+                if (col[2 * (i & 1) + 1] != 0.0) {
+                    LAUNCH(h, launch_gm_solve(i, dH, ldh, ds, dy, h->st));
+                    LAUNCH(h, launch_multi_axpy(n, i + 1, dy, g.V, (size_t)n, x, nullptr, md_partial, h->dot, h->st));
+                    rc = 0;
+                    done = true;
+                    break;
+                }
+            }
+            if (done) break;
+            LAUNCH(h, launch_gm_solve(i - 1, dH, ldh, ds, dy, h->st));
+            LAUNCH(h, launch_multi_axpy(n, i, dy, g.V, (size_t)n, x, nullptr, md_partial, h->dot, h->st));
+        } else {
         for (i = 0; i < m && j <= max_iter; ++i, ++j) {
             if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
             *iters = j;
             if (gt_on) CK(cudaEventRecord(gt_ev[0], h->st));
             A(g.v(i), g.w);
+            if (P) (*P)(g.w);
             if (gt_on) CK(cudaEventRecord(gt_ev[1], h->st));
             if (!cgs2) {
                 // modified Gram-Schmidt, gmres.cpp:115-119: h_k = w . v_k; w -= h_k v_k.  The axpy of step k and the dot of
@@ -1384,25 +1587,7 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
             } else {
                 // classical Gram-Schmidt applied twice: the same projections to rounding (H(:,i) = h1 + h2), but all dots of
                 // a pass in one launch and ONE all-reduce, instead of i+1 dependent all-reduces
-                double* h2 = dh + m + 2;
-                if (cgs_fused && cgs_pass_ok(n, i + 1, g.V, (size_t)n, g.w)) {
-                    // three fused passes over the basis (vecops.cu cgs_pass_kernel): h1; w -= V h1 and h2; w -= V h2 and |w|^2
-                    LAUNCH(h, launch_cgs_pass(0, n, i + 1, nullptr, g.V, (size_t)n, g.w, dh, md_partial, h->dot, h->st));
-                    allreduce_scalars(h, dh, i + 1);
-                    LAUNCH(h, launch_cgs_pass(1, n, i + 1, dh, g.V, (size_t)n, g.w, h2, md_partial, h->dot, h->st));
-                    allreduce_scalars(h, h2, i + 1);
-                    LAUNCH(h, launch_cgs_pass(2, n, i + 1, h2, g.V, (size_t)n, g.w, dh + i + 1, md_partial, h->dot, h->st));
-                    --h->launches;  // no separate reduction launch for the norm (counted below for the two-launch form)
-                } else
-                for (int pass = 0; pass < 2; ++pass) {
-                    double* hp = pass ? h2 : dh;
-                    LAUNCH(h, launch_multi_dot(n, i + 1, g.w, g.V, (size_t)n, hp, md_partial, h->dot, h->st));
-                    ++h->launches;
-                    allreduce_scalars(h, hp, i + 1);
-                    LAUNCH(h, launch_multi_axpy(n, i + 1, hp, g.V, (size_t)n, g.w, pass ? dh + i + 1 : nullptr, md_partial, h->dot, h->st));
-                }
-                ++h->launches;
-                allreduce_scalars(h, dh + i + 1, 1);
+                orthogonalise_cgs2(i);
             }
             // dh[i+1] = w . w: the square root is taken inside the scaling kernel and, for H, on the host
             LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), 1, h->st));
@@ -1433,10 +1618,12 @@ int gmres_core(aniso_handle* h, Op&& A, int n, const double* b, double* x, int m
         }
         if (done) break;
         gm_update(g, x, i - 1, H, ldh, s);
+        }
         A(x, g.w);
         LAUNCH(h, launch_sub(n, b, g.w, g.r, h->st));
-        ddot_dev(h, n, g.r, g.r, dh, true);
-        beta = read_scalar(h, dh);
+        if (P) (*P)(g.r);
+        ddot_dev(h, n, g.r, g.r, dbeta, true);
+        beta = read_scalar(h, dbeta);
         if ((resid = beta / normb) < tol) {
             rc = 0;
             done = true;
@@ -1471,26 +1658,34 @@ int aniso_gmres_dev(aniso_t* h, const double* b, double* x, int m, int max_iter,
     API_END
 }
 
-int aniso_gmres(aniso_t* h, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
-                int hist_cap) {
+int aniso_gmres_prec(aniso_t* h, const double* b, double* x, int m, int max_iter, double tol, aniso_prec_fn prec, void* ctx,
+                     int* iters, double* hist, int hist_cap) {
     API_BEGIN
     REQUIRE(h && b && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede GMRES");
-    double* db = dalloc<double>(h, h->plan.N);
-    double* dx = dalloc<double>(h, h->plan.N);
-    to_slots(h, b, db);
-    to_slots(h, x, dx);
     ensure_ops(h, 0, PART_BOTH);
     ensure_stencils(h, 0);
+    if (!h->d_gm_b) {  // right-hand side and iterate of the host-vector entry points, kept in the handle
+        h->d_gm_b = dalloc<double>(h, h->plan.N);
+        h->d_gm_x = dalloc<double>(h, h->plan.N);
+    }
+    double *db = h->d_gm_b, *dx = h->d_gm_x;
+    to_slots(h, b, db);
+    to_slots(h, x, dx);
+    HostPrec hp{h, prec, ctx, 1, {}, {}};
+    const DevPrec P = [&hp](double* v) { hp(v); };
     const int rc = gmres_core(h, [h](const double* xx, double* yy) { forward_own(h, xx, yy); }, h->nown, db + h->slot0,
-                              dx + h->slot0, m, max_iter, tol, iters, hist, hist_cap);
+                              dx + h->slot0, m, max_iter, tol, iters, hist, hist_cap, prec ? &P : nullptr);
     from_slots(h, dx + h->slot0, x);
-    dfree(h, db);
-    dfree(h, dx);
     return rc;
     API_END
+}
+
+int aniso_gmres(aniso_t* h, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
+                int hist_cap) {
+    return aniso_gmres_prec(h, b, x, m, max_iter, tol, nullptr, nullptr, iters, hist, hist_cap);
 }
 
 int aniso_block_forward_dev(aniso_t* h, const double* u_dev, int weighted, double* out_dev) {
@@ -1511,24 +1706,22 @@ int aniso_block_forward(aniso_t* h, const double* u, int weighted, double* out) 
     CK(cudaSetDevice(h->device));
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede the block operator");
     const int K = h->plan.K, N = h->plan.N, n = h->nown;
-    double* du = dalloc<double>(h, (size_t)K * N);
-    double* dow = dalloc<double>(h, (size_t)K * n);
-    double* down = dalloc<double>(h, (size_t)K * n);
+    if (!h->d_blk_io) h->d_blk_io = dalloc<double>(h, (size_t)K * N + 2 * (size_t)K * n);  // kept in the handle: no leak on a throw
+    double* du = h->d_blk_io;
+    double* dow = du + (size_t)K * N;
+    double* down = dow + (size_t)K * n;
     for (int a = 0; a < K; ++a) {
         to_slots(h, u + (size_t)a * N, du + (size_t)a * N);
         CK(cudaMemcpyAsync(dow + (size_t)a * n, du + (size_t)a * N + h->slot0, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
     }
     block_apply(h, dow, down, weighted != 0, false);
     for (int a = 0; a < K; ++a) from_slots(h, down + (size_t)a * n, out + (size_t)a * N);
-    dfree(h, du);
-    dfree(h, dow);
-    dfree(h, down);
     return ANISO_OK;
     API_END
 }
 
-int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
-                          double* hist, int hist_cap) {
+static int block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int m, int max_iter, double tol, aniso_prec_fn prec,
+                           void* ctx, int* iters, double* hist, int hist_cap) {
     API_BEGIN
     REQUIRE(h && rhs_dev && x_dev && iters && m >= 1 && max_iter >= 0, "bad arguments");
     ensure_device(h);
@@ -1538,35 +1731,46 @@ int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int 
         ensure_ops(h, k, PART_BOTH);
         ensure_stencils(h, k);
     }
+    HostPrec hp{h, prec, ctx, h->plan.K, {}, {}};
+    const DevPrec P = [&hp](double* v) { hp(v); };
     return gmres_core(h, [h](const double* xx, double* yy) { block_apply(h, xx, yy, true, true); }, h->plan.K * h->nown, rhs_dev,
-                      x_dev, std::min(m, std::max(max_iter, 1)), max_iter, tol, iters, hist, hist_cap);
+                      x_dev, std::min(m, std::max(max_iter, 1)), max_iter, tol, iters, hist, hist_cap, prec ? &P : nullptr);
     API_END
 }
 
-int aniso_block_gmres(aniso_t* h, const double* rhs, double* x, int m, int max_iter, double tol, int* iters, double* hist,
-                      int hist_cap) {
+int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
+                          double* hist, int hist_cap) {
+    return block_gmres_dev(h, rhs_dev, x_dev, m, max_iter, tol, nullptr, nullptr, iters, hist, hist_cap);
+}
+
+int aniso_block_gmres_prec(aniso_t* h, const double* rhs, double* x, int m, int max_iter, double tol, aniso_prec_fn prec, void* ctx,
+                           int* iters, double* hist, int hist_cap) {
     API_BEGIN
     REQUIRE(h && rhs && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
     ensure_device(h);
     CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede GMRES");
     const int K = h->plan.K, N = h->plan.N, n = h->nown;
-    double* tmp = dalloc<double>(h, N);
-    double* db = dalloc<double>(h, (size_t)K * n);
-    double* dx = dalloc<double>(h, (size_t)K * n);
+    if (!h->d_blk_gm) h->d_blk_gm = dalloc<double>(h, (size_t)N + 2 * (size_t)K * n);  // staging vector, rhs and iterate
+    double* tmp = h->d_blk_gm;
+    double* db = tmp + N;
+    double* dx = db + (size_t)K * n;
     for (int a = 0; a < K; ++a) {
         to_slots(h, rhs + (size_t)a * N, tmp);
         CK(cudaMemcpyAsync(db + (size_t)a * n, tmp + h->slot0, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
         to_slots(h, x + (size_t)a * N, tmp);
         CK(cudaMemcpyAsync(dx + (size_t)a * n, tmp + h->slot0, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
     }
-    const int rc = aniso_block_gmres_dev(h, db, dx, m, max_iter, tol, iters, hist, hist_cap);
+    const int rc = block_gmres_dev(h, db, dx, m, max_iter, tol, prec, ctx, iters, hist, hist_cap);
     if (rc >= 0)
         for (int a = 0; a < K; ++a) from_slots(h, dx + (size_t)a * n, x + (size_t)a * N);
-    dfree(h, tmp);
-    dfree(h, db);
-    dfree(h, dx);
     return rc;
     API_END
+}
+
+int aniso_block_gmres(aniso_t* h, const double* rhs, double* x, int m, int max_iter, double tol, int* iters, double* hist,
+                      int hist_cap) {
+    return aniso_block_gmres_prec(h, rhs, x, m, max_iter, tol, nullptr, nullptr, iters, hist, hist_cap);
 }
 
 void* aniso_stream(aniso_t* h) { return h ? (void*)h->st : nullptr; }
@@ -1639,6 +1843,53 @@ int aniso_apply_bytes(const aniso_t* h, int64_t out[3]) {
     out[2] = (int64_t)9 * h->plan.c2 * h->nown * 8;
     return ANISO_OK;
 }
+int aniso_time_forward(aniso_t* h, int reps, double* ms) {
+    API_BEGIN
+    REQUIRE(h && ms && reps >= 1, "bad arguments");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede the operator");
+    ensure_ops(h, 0, PART_BOTH);
+    ensure_stencils(h, 0);
+    CK(cudaMemsetAsync(h->d_a, 0, sizeof(double) * h->plan.N, h->st));
+    forward_own(h, h->d_a + h->slot0, h->d_b);  // warm-up
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    CK(cudaEventRecord(e0, h->st));
+    for (int i = 0; i < reps; ++i) forward_own(h, h->d_a + h->slot0, h->d_b);
+    CK(cudaEventRecord(e1, h->st));
+    CK(cudaEventSynchronize(e1));
+    float t = 0;
+    CK(cudaEventElapsedTime(&t, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ms = t / reps;
+    return ANISO_OK;
+    API_END
+}
+
+const char* aniso_get_config(const aniso_t* h) {
+    // the environment switches that select a code path (development A/B switches; all default off), as one string a
+    // benchmark line can carry so that a run describes itself
+    static thread_local std::string cfg;
+    static const char* names[] = {"ANISO_GMRES_ORTHO", "ANISO_GMRES_SYNC", "ANISO_NO_SYM", "ANISO_NO_SUBTREE", "ANISO_NO_OVERLAP",
+                                  "ANISO_CELL_WALK", "ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS", "ANISO_SYMG_NO_DMMA", "ANISO_NO_DMMA",
+                                  "ANISO_BLOCK_LOOP", "ANISO_BLOCK_PER_ID", "ANISO_NO_SHARED_TAU", "ANISO_SUBTREE_D",
+                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_NO_GRAPH"};
+    cfg = "aniso_b200 0.2 (sm_100a)";
+    if (h) {
+        cfg += "; ranks=" + std::to_string(h->nranks) + " sym=" + std::to_string(h->plan.m2l.symmetric ? 1 : 0) +
+               " subtree=" + std::to_string(h->subtree_ok ? 1 : 0) + " overlap=" + std::to_string(h->overlap ? 1 : 0) +
+               " table_line_integral=" + std::to_string(h->S.ty ? 1 : 0);
+    }
+    const char* o = getenv("ANISO_GMRES_ORTHO");
+    cfg += std::string("; gmres=") + (o ? o : "cgs2") + (getenv("ANISO_GMRES_SYNC") ? "/sync" : "/pipelined");
+    for (const char* n : names)
+        if (const char* v = getenv(n)) cfg += std::string("; ") + n + "=" + v;
+    return cfg.c_str();
+}
+
 int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms) {
     API_BEGIN
     REQUIRE(h && ms && reps >= 1 && (which == 0 || which == 1), "bad arguments");

@@ -2,9 +2,22 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdint>
 
 namespace an {
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: a kernel instantiation opts in once per device a
+// handle runs on (handles of one process may sit on different GPUs, from different host threads)
+struct PerDeviceOnce {
+    std::atomic<unsigned long long> seen{0};
+    bool first() {
+        int d = 0;
+        cudaGetDevice(&d);
+        const unsigned long long bit = 1ull << (d & 63);
+        return (seen.fetch_or(bit) & bit) == 0;
+    }
+};
 
 enum PartMask { PART_REAL = 1, PART_IMAG = 2, PART_BOTH = 3 };  // realParts / imagParts of KernelFactory.h:22-23
 
@@ -205,5 +218,12 @@ void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t s
 void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, int squared, cudaStream_t st);
 void launch_sqrt1(double* v, cudaStream_t st);
 void launch_sub(int n, const double* a, const double* b, double* out, cudaStream_t st);  // out = a - b
+// scalar part of Arnoldi step i on the device (gmres.cpp:123-144): column i of H from the projections h1 (+ h2 for CGS2) and
+// norm2 = w . w, previous rotations applied, new rotation generated, s updated; report[0] = |s(i+1)| / normb,
+// report[1] = 1 when that is below tol.  beta is read at i == 0.
+void launch_givens_step(int i, const double* h1, const double* h2, const double* norm2, const double* beta, double* H, int ldh,
+                        double* cs, double* sn, double* s, double normb, double tol, double* report, cudaStream_t st);
+// yneg = -(H(0:k,0:k)^-1 s(0:k)) (Update, gmres.cpp:12-24)
+void launch_gm_solve(int k, const double* H, int ldh, const double* s, double* yneg, cudaStream_t st);
 
 }  // namespace an

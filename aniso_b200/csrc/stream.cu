@@ -505,11 +505,10 @@ template <int R, int NRHS>
 static void launch_ring(const DevCSR& m, const double* A, const double* x, size_t xstride, double* scr, size_t sstride, double sign,
                         cudaStream_t st) {
     constexpr int STAGES = 3;  // 3 CTAs x (8 warps x 3 stages x ~2.3 KB) per SM
-    static bool once = false;  // per instantiation
-    if (!once) {
+    static PerDeviceOnce once;  // per instantiation and device
+    if (once.first()) {
         cudaFuncSetAttribute(bsr_apply_sym_ring_kernel<R, NRHS, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              ring_smem_bytes<R, NRHS, STAGES>());
-        once = true;
     }
     bsr_apply_sym_ring_kernel<R, NRHS, STAGES>
         <<<(m.groups + 7) / 8, 256, ring_smem_bytes<R, NRHS, STAGES>(), st>>>(m, A, x, xstride, scr, sstride, sign);
@@ -687,10 +686,9 @@ __global__ void __launch_bounds__(256, 3) bsr_apply_sym_mma_kernel(DevCSR m, con
 static void launch_mma(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,
                        double sign, cudaStream_t st) {
     constexpr int STAGES = 3, SMEM = 8 * (STAGES * MMA_STAGE + STAGES * 8);
-    static bool once = false;
-    if (!once) {
+    static PerDeviceOnce once;  // per instantiation and device
+    if (once.first()) {
         cudaFuncSetAttribute(bsr_apply_sym_mma_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-        once = true;
     }
     bsr_apply_sym_mma_kernel<STAGES><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, xstride, nrhs, scr, sstride, sign);
 }
@@ -861,10 +859,9 @@ __global__ void __launch_bounds__(256, 3) bsr_apply_sym_mma_ids_kernel(DevCSR m,
 void launch_bsr_apply_ids(const DevCSR& m, const IdList& ids, size_t xstride, int nrhs, double* scr, size_t sstride, cudaStream_t st) {
     if (m.groups == 0 || nrhs == 0 || ids.n == 0) return;
     constexpr int STAGES = 3, SMEM = 8 * (STAGES * MMA_STAGE + STAGES * 8 + 32 * 4);
-    static bool once = false;
-    if (!once) {
+    static PerDeviceOnce once;  // per instantiation and device
+    if (once.first()) {
         cudaFuncSetAttribute(bsr_apply_sym_mma_ids_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-        once = true;
     }
     bsr_apply_sym_mma_ids_kernel<STAGES><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, ids, xstride, nrhs, scr, sstride);
 }
@@ -1138,10 +1135,9 @@ __global__ void __launch_bounds__(256, MINB) bsr_apply_symg_ring_kernel(DevCSR m
 template <int R, int STAGES, int MINB>
 static void launch_symg_ring(const DevCSR& m, const double* A, const double* x, double sign, cudaStream_t st) {
     constexpr int SMEM = 8 * STAGES * (64 * R + 16) + 8 * STAGES * 8 + 8 * 8 * 8;
-    static bool once = false;  // per instantiation
-    if (!once) {
+    static PerDeviceOnce once;  // per instantiation and device
+    if (once.first()) {
         cudaFuncSetAttribute(bsr_apply_symg_ring_kernel<R, STAGES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-        once = true;
     }
     bsr_apply_symg_ring_kernel<R, STAGES, MINB><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, sign);
 }
@@ -1301,10 +1297,9 @@ __global__ void __launch_bounds__(256, MINB) bsr_apply_symg_mma_kernel(DevCSR m,
 template <int R, int STAGES, int MINB>
 static void launch_symg_mma(const DevCSR& m, const double* A, const double* x, double sign, cudaStream_t st) {
     constexpr int SMEM = 8 * STAGES * (64 * R + 16) + 8 * STAGES * 8 + 8 * 8 * 8;
-    static bool once = false;  // per instantiation
-    if (!once) {
+    static PerDeviceOnce once;  // per instantiation and device
+    if (once.first()) {
         cudaFuncSetAttribute(bsr_apply_symg_mma_kernel<R, STAGES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-        once = true;
     }
     bsr_apply_symg_mma_kernel<R, STAGES, MINB><<<(m.groups + 7) / 8, 256, SMEM, st>>>(m, A, x, sign);
 }

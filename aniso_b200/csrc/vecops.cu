@@ -191,6 +191,73 @@ void launch_sub(int n, const double* a, const double* b, double* out, cudaStream
     if (n) sub_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, a, b, out);
 }
 
+// ---- scalar part of an Arnoldi step on the device (gmres.cpp:123-144) ------------------------------------------------
+// The host version reads the new Hessenberg column back and synchronises once per step; with the column, the rotations
+// and the recurrence residual kept on the device the host can queue step i+1 before it learns how step i ended.
+// One thread; the arithmetic is written with non-contracting intrinsics in the order of the host code (capi.cu
+// plane_rotation / apply_rotation), so both paths produce the same bits.
+__device__ __forceinline__ void dev_apply_rotation(double& dx, double& dy, double cs, double sn) {  // ApplyPlaneRotation
+    const double t = __dadd_rn(__dmul_rn(cs, dx), __dmul_rn(sn, dy));
+    dy = __dadd_rn(__dmul_rn(-sn, dx), __dmul_rn(cs, dy));
+    dx = t;
+}
+__global__ void givens_step_kernel(int i, const double* __restrict__ h1, const double* __restrict__ h2, const double* __restrict__ norm2,
+                                   const double* __restrict__ beta, double* __restrict__ H, int ldh, double* __restrict__ cs,
+                                   double* __restrict__ sn, double* __restrict__ s, double normb, double tol, double* __restrict__ report) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double* __restrict__ col = H + (size_t)i * ldh;
+    for (int k = 0; k <= i; ++k) col[k] = h2 ? __dadd_rn(h1[k], h2[k]) : h1[k];  // CGS2: H(:, i) = h1 + h2
+    col[i + 1] = sqrt(*norm2);
+    if (i == 0) s[0] = *beta;
+    s[i + 1] = 0.0;
+    for (int k = 0; k < i; ++k) dev_apply_rotation(col[k], col[k + 1], cs[k], sn[k]);
+    const double dx = col[i], dy = col[i + 1];
+    double c, sv;  // GeneratePlaneRotation, gmres.cpp:26-39
+    if (dy == 0.0) {
+        c = 1.0;
+        sv = 0.0;
+    } else if (fabs(dy) > fabs(dx)) {
+        const double t = __ddiv_rn(dx, dy);
+        sv = __ddiv_rn(1.0, __dsqrt_rn(__dadd_rn(1.0, __dmul_rn(t, t))));
+        c = __dmul_rn(t, sv);
+    } else {
+        const double t = __ddiv_rn(dy, dx);
+        c = __ddiv_rn(1.0, __dsqrt_rn(__dadd_rn(1.0, __dmul_rn(t, t))));
+        sv = __dmul_rn(t, c);
+    }
+    cs[i] = c;
+    sn[i] = sv;
+    dev_apply_rotation(col[i], col[i + 1], c, sv);
+    dev_apply_rotation(s[i], s[i + 1], c, sv);
+    const double resid = __ddiv_rn(fabs(s[i + 1]), normb);
+    report[0] = resid;
+    report[1] = resid < tol ? 1.0 : 0.0;  // gmres.cpp:135
+}
+void launch_givens_step(int i, const double* h1, const double* h2, const double* norm2, const double* beta, double* H, int ldh,
+                        double* cs, double* sn, double* s, double normb, double tol, double* report, cudaStream_t st) {
+    givens_step_kernel<<<1, 32, 0, st>>>(i, h1, h2, norm2, beta, H, ldh, cs, sn, s, normb, tol, report);
+}
+
+// Update, gmres.cpp:12-24: y = H(0:k, 0:k)^-1 s(0:k) by back substitution (same operation order as the host form, the inner
+// loop spread over one warp); writes -y so that x += V y is one launch_multi_axpy (which subtracts)
+__global__ void gm_solve_kernel(int k, const double* __restrict__ H, int ldh, const double* __restrict__ s, double* __restrict__ yneg) {
+    extern __shared__ double y[];
+    const int lane = threadIdx.x;
+    for (int q = lane; q <= k; q += 32) y[q] = s[q];
+    __syncwarp();
+    for (int i = k; i >= 0; --i) {
+        if (lane == 0) y[i] = __ddiv_rn(y[i], H[i + (size_t)i * ldh]);
+        __syncwarp();
+        const double yi = y[i];
+        for (int j = i - 1 - lane; j >= 0; j -= 32) y[j] = __dadd_rn(y[j], -__dmul_rn(H[j + (size_t)i * ldh], yi));
+        __syncwarp();
+    }
+    for (int q = lane; q <= k; q += 32) yneg[q] = -y[q];
+}
+void launch_gm_solve(int k, const double* H, int ldh, const double* s, double* yneg, cudaStream_t st) {
+    gm_solve_kernel<<<1, 32, (size_t)(k + 1) * sizeof(double), st>>>(k, H, ldh, s, yneg);
+}
+
 // ---- classical Gram-Schmidt with re-orthogonalisation (CGS2): all projections of one pass in two launches ----
 // multi_dot: partial[(k * gridDim.x) + b] = sum over block b's share of w . V_k, k = blockIdx.y * 8 + kk
 static constexpr int kMD = 8;

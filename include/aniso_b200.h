@@ -37,6 +37,10 @@ enum {
     ANISO_ENCCL = -6
 };
 
+/* Sharded handles (aniso_create_sharded with nranks > 1) are SPMD objects: every rank makes the same calls in the same
+ * order, as in any NCCL program.  The entry points that take HOST vectors move 1/nranks of each vector per rank over PCIe
+ * and all-gather the pieces over NVLink, so they are collective too. */
+
 /* kernel parts of KernelFactory.h:22-23: realParts = singular cos(k theta)/r, imagParts = attenuated remainder */
 enum { ANISO_PART_REAL = 1, ANISO_PART_IMAG = 2, ANISO_PART_BOTH = 3 };
 
@@ -139,6 +143,17 @@ int aniso_gmres(aniso_t* h, const double* b_host, double* x_host, int m, int max
 int aniso_gmres_dev(aniso_t* h, const double* b_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
                     double* resid_hist, int hist_cap);
 
+/* Left-preconditioned GMRES: the DSA preconditioner hook of the MATLAB application, `prec` of aniso.m:111-119 handed to
+ * gmres(A, rhs, 400, 1e-11, 400, @obj.prec) at aniso.m:165 (gmres.cpp:7 lists it as "todo: preconditioner").  The callback
+ * maps r -> z = M^-1 r on HOST vectors of n doubles in reference node order (n = N, or K*N mode-major for the block solve) and
+ * returns 0; it is applied to b, to the initial residual and after every operator application, so the iteration runs on
+ * M^-1 A x = M^-1 b and the reported residuals are |M^-1 (b - A x)| / |M^-1 b| (MATLAB's convention).  prec == NULL is the
+ * unpreconditioned solve.  A non-zero return aborts with ANISO_ECUDA-class error text.  The FEM solve behind aniso.m's
+ * callback (femm) is outside this library. */
+typedef int (*aniso_prec_fn)(void* ctx, int n, const double* r_host, double* z_host);
+int aniso_gmres_prec(aniso_t* h, const double* b_host, double* x_host, int m, int max_iter, double tol, aniso_prec_fn prec,
+                     void* ctx, int* iters, double* resid_hist, int hist_cap);
+
 /* ---- multi-mode block operator (MATLAB application layer: aniso.m:121-156 forward / mforward, aniso.m:158-172 solve) ----
  * Block vectors hold K = kernel_size angular modes of N values, mode-major: mode a at [a*N, (a+1)*N), reference node order.
  *   weighted = 0  `forward`:  out_i = sum_{j=-(K-1)}^{K-1} mapping_{|i+j|}(u_|j|)                         (aniso.m:121-136)
@@ -153,6 +168,9 @@ int aniso_block_gmres(aniso_t* h, const double* rhs_host, double* x_host, int m,
                       double* resid_hist, int hist_cap);
 int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
                           double* resid_hist, int hist_cap);
+/* aniso.m:165 with pr == 1: gmres(A, rhs, 400, 1e-11, 400, @obj.prec); callback on K*N host doubles, mode-major */
+int aniso_block_gmres_prec(aniso_t* h, const double* rhs_host, double* x_host, int m, int max_iter, double tol,
+                           aniso_prec_fn prec, void* ctx, int* iters, double* resid_hist, int hist_cap);
 
 /* ---- device probes (parity tests of K1/K2 pieces) ---------------------------------------------------------- */
 /* lineIntegral(x0,y0,x1,y1) KernelFactory.cpp:67-166 for n segments, pts4 = n x 4 host doubles */
@@ -183,6 +201,12 @@ int aniso_apply_bytes(const aniso_t* h, int64_t out[3]);
 /* time the streaming apply kernels alone: `reps` back-to-back launches of (0) M2L stream, (1) P2P stream on the cache of `id`,
  * CUDA events on the handle's stream; returns average milliseconds per launch */
 int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms_per_launch);
+/* `reps` applications of the GMRES operator y = x - mapping_0(sigma_s x) (main.cpp:123-136) on device vectors, CUDA events on
+ * the handle's stream: average milliseconds per application (collective on a sharded handle) */
+int aniso_time_forward(aniso_t* h, int reps, double* ms_per_apply);
+/* one line naming the code paths in effect (library version, handle layout, GMRES form, every ANISO_* development switch
+ * set in the environment): lets a benchmark record describe itself.  Thread-local storage. */
+const char* aniso_get_config(const aniso_t* h);
 
 #ifdef __cplusplus
 }

@@ -5,17 +5,14 @@ MASK = (1 << 64) - 1
 
 
 def splitmix64(seed, n):
-    """n uniform doubles in [0,1) from splitmix64(seed)."""
-    out = np.empty(n)
-    s = seed & MASK
-    for i in range(n):
-        s = (s + 0x9E3779B97F4A7C15) & MASK
-        z = s
-        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & MASK
-        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & MASK
-        z ^= z >> 31
-        out[i] = (z >> 11) * (1.0 / (1 << 53))
-    return out
+    """n uniform doubles in [0,1) from splitmix64(seed); the state after i draws is
+    seed + i * golden (mod 2^64), so the sequence vectorises exactly."""
+    with np.errstate(over="ignore"):
+        s = np.uint64(seed & MASK) + np.arange(1, n + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15)
+        z = (s ^ (s >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z ^= z >> np.uint64(31)
+    return (z >> np.uint64(11)).astype(np.float64) * (1.0 / (1 << 53))
 
 
 def gaussian_source(x, y):
@@ -61,6 +58,10 @@ CASES = {
     "ml12d2": (12, 2, 1, 0.5, 4, 3, 2, "main"),     # maxLevel cap, non power-of-two sz
     "c2": (128, 1, 5, 0.5, 10, 4, 20, "const"),     # BASELINE config 2
     "c1": (64, 3, 1, 0.95, 8, 4, 20, "main"),       # BASELINE config 1 (data.cfg)
+    "c3": (256, 1, 5, 0.9, 10, 6, 20, "hetero"),    # BASELINE config 3 (N = 2^16, np 6, heterogeneous sigma)
+    "c4n4": (512, 1, 1, 0.9, 10, 4, 20, "hetero"),  # BASELINE config 4 (N = 2^18), Chebyshev order 4
+    "c4n8": (512, 1, 1, 0.9, 10, 8, 20, "hetero"),  # BASELINE config 4, Chebyshev order 8 (64-point leaves)
+    "c5": (1024, 1, 1, 0.9, 10, 4, 20, "layers"),   # BASELINE config 5 (N = 2^20): the headline workload of bench.py
 }
 
 # multi-mode block operator (aniso.m forward / mforward / solve): name -> same tuple

@@ -15,7 +15,7 @@ import cases  # noqa: E402
 from oracle.refapi import RefAniso, gl_table  # noqa: E402
 
 FULL = {"a16", "b8d3", "h32", "nu6d5", "ml12d2"}  # small: store full vectors
-IDS = {"c2": [0, 1, 4], "c1": [0]}
+IDS = {"c2": [0, 1, 4], "c1": [0], "c3": [0, 3]}
 STRIDE = 61  # subsampling stride for the large cases
 
 

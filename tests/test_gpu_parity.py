@@ -12,6 +12,8 @@ pytestmark = pytest.mark.gpu
 
 TOL = 1e-10  # north_star: matvec relative L2 error <= 1e-10 in FP64
 SMALL = ["a16", "b8d3", "h32", "nu6d5", "ml12d2"]
+# BASELINE configs 3, 4 (np 4 and 8) and 5: fixtures from the compiled reference run at the full size (tests/golden/make_golden.py)
+LARGE = ["c3", "c4n4", "c4n8", "c5"]
 STAGES = ("imag_fmm", "real_fmm", "k7", "k8", "k9", "out")
 
 
@@ -30,7 +32,7 @@ def make(name):
     return a, x, y, w
 
 
-@pytest.mark.parametrize("name", SMALL + ["c2", "c1"])
+@pytest.mark.parametrize("name", SMALL + ["c2", "c1"] + LARGE)
 def test_line_integral_and_kernels(golden, name):
     g = golden(name)
     a, *_ = make(name)
@@ -52,7 +54,7 @@ def test_sigma_coeff(golden, name):
     a.delete()
 
 
-@pytest.mark.parametrize("name", SMALL + ["c2", "c1"])
+@pytest.mark.parametrize("name", SMALL + ["c2", "c1"] + LARGE)
 def test_mapping_stages_vs_reference_golden(golden, name):
     g = golden(name)
     a, x, y, w = make(name)
@@ -91,7 +93,7 @@ def test_mapping_vs_oracle_seeded(name):
     a.delete()
 
 
-@pytest.mark.parametrize("name", ["a16", "b8d3", "nu6d5", "c2", "c1"])
+@pytest.mark.parametrize("name", ["a16", "b8d3", "nu6d5", "c2", "c1"] + LARGE)
 def test_gmres_vs_reference_golden(golden, name):
     g = golden(name)
     a, x, y, w = make(name)
