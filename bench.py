@@ -12,7 +12,11 @@ GMRES operator y = x - mapping_0(sigma_s .* x) (main.cpp:123-136), i.e. exactly 
          no L2 flush is needed between iterations.
   e2e    the same through the reference-facing C-ABI call aniso_mapping() with HOST buffers (H2D + D2H inside).
   --impl reference  times the compiled, unmodified reference (oracle/_ref/libaniso_ref_fast.so, OpenMP on all host
-         cores) on a bounded sample of the same workload (smaller sz; the FMM is O(N), the metric is per point).
+         cores) on the SAME configuration (N = 2^20) when a short probe at N = 2^16 projects the whole run under
+         REF_BUDGET_S and the host has the memory (about 30 GB); otherwise on the largest of N = 2^18 / 2^16 / 2^14 that
+         fits, and says which in config.sample.
+  parity   the line carries the comparison of this very run with the reference: against the committed fixture of the
+         compiled reference at N = 2^20 (tests/golden/c5.npz) and, in cpu_baseline, against the reference run beside it.
 """
 import argparse
 import json
@@ -36,6 +40,7 @@ NP_ORDER, SING_RULE, G_ANISO, MAX_LEVEL = 4, 10, 0.9, 20
 # capture profiles/r01_final_ncu_raw.csv (cannot be measured live); keyed by (sz, n_gpus)
 # (TMA-ring kernel: the two launches of a matvec, levels 2-7 and level 8, read 0.590 + 1.813 GB and write 0.007 + 0.077 GB)
 NCU_TRAFFIC = {(1024, 1): 590147000 + 1813174000 + 7098000 + 76844000}
+NCU_TRAFFIC_SOURCE = "profiles/r01_final_ncu_raw.csv"
 
 
 def workload_name(sz):
@@ -104,8 +109,17 @@ def measured_peak():
     return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
 
 
-def reference_sample_sz(cores):
-    return 256 if cores >= 16 else 128
+REF_BUDGET_S = 600.0  # the reference arm must end within a few minutes (the driver's per-N limit is ~870 s)
+
+
+def mem_available_gb():
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable"):
+                return int(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
 
 
 def use_all_host_threads():
@@ -122,102 +136,165 @@ def use_all_host_threads():
     return cores
 
 
-def run_reference(args):
-    """The reference's own CPU implementation (compiled unmodified, its own -Ofast/-ffast-math flags, OpenMP on all
-    host cores) on a bounded sample; rank 0 only."""
-    if int(os.environ.get("RANK", "0")) != 0:
-        return
-    cores = use_all_host_threads()
-    from oracle import refapi  # the one place bench.py executes oracle/ besides cpu_baseline
+def make_reference(sz):
+    """(object, kind, cores): the compiled reference with its own flags when oracle/_ref travelled, else the scalar C port"""
+    from oracle import refapi  # bench.py executes oracle/ only in run_reference and cpu_baseline
 
-    sz = args.ref_sz or reference_sample_sz(cores)
-    kind = "reference" if refapi.available(fast=True) else "port"
-    if kind == "reference":
-        r = refapi.RefAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL, fast=True)
-    else:
-        from oracle import oracleapi
-
-        r = oracleapi.OracleAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
-        cores = 1
-    if kind == "reference":
-        cores = int(r.num_threads())  # the threads the reference's OpenMP regions actually get
-    x, y, w = r.nodes()
-    ss, st = cases.sigma_fields("layers", x, y, sz, 1)
-    t0 = time.perf_counter()
-    r.set_coeff(ss, st)
-    r.cache(0)
-    t_cache = time.perf_counter() - t0
-    f = cases.gaussian_source(x, y)
-    for _ in range(args.warmup):
-        r.mapping(ss * f, 0)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        out = f - r.mapping(ss * f, 0)  # same operator as our step
-    dt = (time.perf_counter() - t0) / max(args.steps, 1)
-    n = sz * sz
-    val = n / dt
-    sample = "N=%d (sz %d) sub-problem of the same workload; per-point cost of the O(N) FMM; cache phase %.1f s" % (n, sz, t_cache)
-    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args.sz), "sample": sample},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
-                             "cache_phase_s": t_cache, "near_field_interactions_per_s": None},
-            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0, "checksum": float(np.linalg.norm(out))}
-    print(json.dumps(line), flush=True)
-
-
-def cpu_baseline(args):
-    """Bounded CPU sample (10-30 s of CPU work) timed beside the GPU run: rank 0, N=1 only.  The compiled reference
-    (its own -Ofast flags, OpenMP on all host cores) when oracle/_ref is present, else the scalar C port."""
-    from oracle import refapi
-
-    cores = host_cores()
     if refapi.available(fast=True):
-        sz, kind = (256 if cores >= 12 else 128), "reference"
         r = refapi.RefAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL, fast=True)
-    else:
-        from oracle import oracleapi
+        return r, "reference", int(r.num_threads())
+    from oracle import oracleapi
 
-        sz, kind, cores = 64, "port", 1
-        r = oracleapi.OracleAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
+    return oracleapi.OracleAniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL), "port", 1
+
+
+def time_reference(r, sz, warmup, steps):
+    """cache phase + `steps` applications of the GMRES operator on the reference object r"""
     x, y, w = r.nodes()
     ss, st = cases.sigma_fields("layers", x, y, sz, 1)
     t0 = time.perf_counter()
     r.set_coeff(ss, st)
     times = r.cache(0)
     t_cache = time.perf_counter() - t0
+    f = cases.gaussian_source(x, y)
+    for _ in range(warmup):
+        r.mapping(ss * f, 0)
+    t0 = time.perf_counter()
+    out = None
+    for _ in range(steps):
+        out = f - r.mapping(ss * f, 0)  # same operator as our step
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    return {"t_cache": t_cache, "cache_times": times, "dt": dt, "out": out, "f": f, "ss": ss, "x": x, "y": y}
+
+
+def choose_reference_sz(args, kind):
+    """Same configuration (sz 1024) when it fits the time and memory budget, judged from a probe at sz 256 (the FMM apply
+    is O(N); the cache phase grows a little faster because coarse-level rays cross more cells: measured 1.3x per 4x points)."""
+    if args.ref_sz:
+        return args.ref_sz, None
+    if kind != "reference":
+        return 64, None
+    r, _, _ = make_reference(256)
+    p = time_reference(r, 256, 0, 2)
+    r.close()
+    mem = mem_available_gb()
+    probe = {"sz": 256, "cache_s": p["t_cache"], "matvec_s": p["dt"], "mem_available_gb": mem}
+    napply = args.warmup + args.steps + (30 if args.gpus == 1 else 0)  # + the GMRES solve reported at N = 1
+    for sz, need_gb in ((args.sz, 48.0), (512, 12.0)):
+        scale = (sz / 256.0) ** 2
+        growth = 1.3 ** (np.log(scale) / np.log(4.0)) if scale > 1 else 1.0
+        projected = p["t_cache"] * scale * max(growth, 1.0) + p["dt"] * scale * napply
+        probe["projected_s_sz%d" % sz] = projected
+        if sz >= 256 and projected <= REF_BUDGET_S and mem >= need_gb:
+            return sz, probe
+    return 256, probe
+
+
+def run_reference(args):
+    """The reference's own CPU implementation (compiled unmodified, its own -Ofast/-ffast-math flags, OpenMP on all
+    host cores); rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    use_all_host_threads()
+    from oracle import refapi
+
+    kind = "reference" if refapi.available(fast=True) else "port"
+    sz, probe = choose_reference_sz(args, kind)
+    r, kind, cores = make_reference(sz)
+    t = time_reference(r, sz, args.warmup, args.steps)
+    n = sz * sz
+    val = n / t["dt"]
+    same = sz == args.sz
+    sample = ("the full workload, N=%d (sz %d): same configuration as the GPU arm" % (n, sz)) if same else \
+        ("N=%d (sz %d) sub-problem of the same workload (%s); per-point cost of the O(N) FMM"
+         % (n, sz, "size chosen with --ref-sz" if args.ref_sz else
+            "the full size does not fit the %d s / memory budget of this arm on this host" % int(REF_BUDGET_S)))
+    sample += "; cache phase %.1f s" % t["t_cache"]
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t["dt"] * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args.sz), "sample": sample, "same_config": same},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                             "cache_phase_s": t["t_cache"], "ms_per_matvec": t["dt"] * 1e3},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "checksum": float(np.linalg.norm(t["out"]))}
+    if probe:
+        line["probe"] = probe
+    ct = t["cache_times"]
+    if ct is not None and len(ct) >= 4:
+        line["cpu_baseline"]["cache_labels_s"] = {"Non Singular Cache": float(ct[0]), "Singular Cache": float(ct[1]),
+                                                  "NearAddOn Cache": float(ct[2]), "SingularAddOn Cache": float(ct[3])}
+        ts = r.tree_stats(0)
+        evals = ts["p2p_pairs"] + (ts["sumV"] + ts["sumX"]) * NP_ORDER ** 4
+        if ct[0] > 0:
+            line["cpu_baseline"]["kernel_evals_per_s"] = evals / float(ct[0])
+    if args.gpus == 1 and not args.no_ref_gmres:
+        # GMRES time-to-solve of the reference on this host (main.cpp:141: GMRES(80, 400, 1e-12), x0 = 0)
+        b = r.mapping(t["f"], 0)
+        t0 = time.perf_counter()
+        xs, rc, it, hist = r.gmres(b, m=80, max_iter=400, tol=1e-12)
+        line["gmres"] = {"rc": int(rc), "iters": int(it), "time_to_solve_s": time.perf_counter() - t0,
+                         "last_printed_resid": float(hist[-1]) if len(hist) else None, "m": 80, "tol": 1e-12}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(args):
+    """Bounded CPU sample (10-30 s of CPU work) timed beside the GPU run: rank 0, N=1 only.  The compiled reference
+    (its own -Ofast flags, OpenMP on all host cores) when oracle/_ref is present, else the scalar C port.  Its output is
+    not thrown away: the GPU library runs the same sub-problem and the line reports how far the two are apart."""
+    from oracle import refapi
+
+    cores = host_cores()
+    sz = (256 if cores >= 12 else 128) if refapi.available(fast=True) else 64
+    r, kind, cores = make_reference(sz)
+    t = time_reference(r, sz, 1, 5)
     ts = r.tree_stats(0)
     evals = ts["p2p_pairs"] + (ts["sumV"] + ts["sumX"]) * NP_ORDER ** 4
-    f = cases.gaussian_source(x, y)
-    r.mapping(f, 0)
-    reps = 5
-    t0 = time.perf_counter()
-    for _ in range(reps):
-        r.mapping(ss * f, 0)
-    dt = (time.perf_counter() - t0) / reps
     n = sz * sz
-    out = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": kind,
-           "sample": "N=%d (sz %d) sub-problem of the same workload, %d matvecs after a %.1f s cache phase" % (n, sz, reps, t_cache),
-           "ms_per_matvec": dt * 1e3, "cache_phase_s": t_cache}
-    if times is not None and len(times) and times[0] > 0:
-        out["kernel_evals_per_s"] = evals / float(times[0])  # 'Non Singular Cache': P2P + M2L evaluations with line integrals
+    out = {"value": n / t["dt"], "unit": UNIT, "cores": cores, "kind": kind,
+           "sample": "N=%d (sz %d) sub-problem of the same workload, 5 matvecs after a %.1f s cache phase" % (n, sz, t["t_cache"]),
+           "ms_per_matvec": t["dt"] * 1e3, "cache_phase_s": t["t_cache"]}
+    ct = t["cache_times"]
+    if ct is not None and len(ct) and ct[0] > 0:
+        out["kernel_evals_per_s"] = evals / float(ct[0])  # 'Non Singular Cache': P2P + M2L evaluations with line integrals
+    # parity of the GPU path against this very reference run (same sub-problem, same inputs)
+    from aniso_b200 import Aniso
+
+    f, ss = t["f"], t["ss"]
+    b_ref = r.mapping(f, 0)
+    t0 = time.perf_counter()
+    xr, rcr, itr, histr = r.gmres(b_ref, m=80, max_iter=400, tol=1e-12)
+    t_ref_gmres = time.perf_counter() - t0
+    a = Aniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
+    a.setCoeff(ss, cases.sigma_fields("layers", t["x"], t["y"], sz, 1)[1])
+    a.cache(0)
+    got = f - a.mapping(ss * f, 0)
+    xg, rcg, itg, histg = a.gmres(a.mapping(f, 0), m=80, max_iter=400, tol=1e-12)
+    a.delete()
+    rel = lambda u, v: float(np.linalg.norm(u - v) / np.linalg.norm(v))  # noqa: E731
+    out["parity"] = {"config": "N=%d (sz %d), same inputs through the %s and through libaniso_b200" % (n, sz, kind),
+                     "operator_rel_l2": rel(got, t["out"]), "gmres_iters_ref": int(itr), "gmres_iters_gpu": int(itg),
+                     "gmres_solution_rel_l2": rel(xg, xr), "ref_gmres_s": t_ref_gmres}
     return out
 
 
-def block_section(sz, K=2):
+def block_section(sz, K=2, world=1, rank=0, new_uid=None, device=0):
     """the multi-mode block operator of the MATLAB layer (aniso.m forward / mforward / solve) on the same
     geometry with K = 2 angular modes (kernel ids 0..2, g = 0.9): device-resident mforward (regrouped tensor-core form and
-    the loop of K(2K-1) mappings) and the block GMRES of aniso.m:158-172 (restart 400, tol 1e-11) through the host API."""
+    the loop of K(2K-1) mappings) and the block GMRES of aniso.m:158-172 (restart 400, tol 1e-11).  On world > 1 ranks the
+    vectors are K blocks of owned rows; the checksums (norm of mforward's result, of the solution) let a sharded run be
+    compared with the one-GPU line."""
     import ctypes as C
+
+    import torch
+    import torch.distributed as dist
 
     from aniso_b200 import Aniso, _lib
 
-    a = Aniso(sz, 1, K, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
+    a = Aniso(sz, 1, K, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL, nranks=world, rank=rank, nccl_uid=new_uid() if world > 1 else None,
+              device=device)
     L = a.L
     x, y, w = a.nodes()
-    n = x.size
     ss, st = cases.sigma_fields("layers", x, y, sz, 1)
     a.setCoeff(ss, st)
     t0 = time.perf_counter()
@@ -225,47 +302,102 @@ def block_section(sz, K=2):
         a.cache(k)
     a.synchronize()
     t_cache = time.perf_counter() - t0
-    du, dout = C.c_void_p(), C.c_void_p()
-    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(du)))
-    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(dout)))
-    src = cases.gaussian_source(x, y)
-    for m in range(K):
-        _lib.check(L.aniso_to_slots(a.h, src, C.c_void_p(du.value + 8 * m * n)))
-    res = {"K": K, "kernel_ids": 2 * K - 1, "cache_all_ids_s": t_cache}
+    slot0, slot1 = a.owned_range()
+    nown = slot1 - slot0
+    perm = a.slot_permutation()
+    src_own = torch.from_numpy(cases.gaussian_source(x, y)[perm][slot0:slot1].copy()).cuda()
+    du = src_own.repeat(K).contiguous()
+    dout = torch.empty_like(du)
+
+    def norm_all(t):
+        v = (t * t).sum().reshape(1)
+        if world > 1:
+            dist.all_reduce(v)
+        return float(v.sqrt().item())
+
+    res = {"K": K, "kernel_ids": 2 * K - 1, "cache_all_ids_s": t_cache, "ranks": world}
     for key, env in (("mforward_ms", None), ("mforward_loop_ms", "1")):
         if env:
             os.environ["ANISO_BLOCK_LOOP"] = env
         else:
             os.environ.pop("ANISO_BLOCK_LOOP", None)
         for _ in range(3):
-            _lib.check(L.aniso_block_forward_dev(a.h, du, 1, dout))
+            _lib.check(L.aniso_block_forward_dev(a.h, du.data_ptr(), 1, dout.data_ptr()))
         a.synchronize()
         l0, t0, reps = a.launch_count(), time.perf_counter(), 10
         for _ in range(reps):
-            _lib.check(L.aniso_block_forward_dev(a.h, du, 1, dout))
+            _lib.check(L.aniso_block_forward_dev(a.h, du.data_ptr(), 1, dout.data_ptr()))
         a.synchronize()
         res[key] = (time.perf_counter() - t0) / reps * 1e3
         res[key.replace("_ms", "_launches")] = (a.launch_count() - l0) // reps
+        res[key.replace("_ms", "_checksum")] = norm_all(dout)
     os.environ.pop("ANISO_BLOCK_LOOP", None)
-    drhs, dx = C.c_void_p(), C.c_void_p()
-    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(drhs)))
-    _lib.check(L.aniso_dev_alloc(a.h, 8 * K * n, C.byref(dx)))
+    drhs, dx = torch.empty_like(du), torch.empty_like(du)
     it = C.c_int(0)
     hist = np.zeros(402)
-    zeros = np.zeros(n)
     for _ in range(2):  # the first solve allocates the Krylov work space (restart 400: 403 vectors of K*N doubles)
-        for m in range(K):  # x0 = 0
-            _lib.check(L.aniso_to_slots(a.h, zeros, C.c_void_p(dx.value + 8 * m * n)))
-        a.synchronize()
+        dx.zero_()
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
-        _lib.check(L.aniso_block_forward_dev(a.h, du, 0, drhs))  # rhs = forward(charge), aniso.m:160
-        rc = _lib.check(L.aniso_block_gmres_dev(a.h, drhs, dx, 400, 400, 1e-11, C.byref(it), hist, hist.size))
+        _lib.check(L.aniso_block_forward_dev(a.h, du.data_ptr(), 0, drhs.data_ptr()))  # rhs = forward(charge), aniso.m:160
+        rc = _lib.check(L.aniso_block_gmres_dev(a.h, drhs.data_ptr(), dx.data_ptr(), 400, 400, 1e-11, C.byref(it), hist, hist.size))
         a.synchronize()
         t_solve = time.perf_counter() - t0
     res.update({"solve_s": t_solve, "solve_iters": int(it.value), "solve_rc": int(rc), "solve_final_resid": float(hist[it.value]),
+                "solve_checksum": norm_all(dx),
                 "solve_note": "device-resident: rhs = forward(charge), then GMRES(400, 1e-11, 400) on I - mforward (aniso.m:158-172)"})
     a.delete()
     return res
+
+
+CONFIG_ROWS = [("C1", "c1", None), ("C2", "c2", None), ("C3", "c3", None), ("C4 np4", "c4n4", None),
+               ("C4 np5", None, (512, 1, 1, 0.9, 10, 5, 20, "hetero")), ("C4 np6", None, (512, 1, 1, 0.9, 10, 6, 20, "hetero")),
+               ("C4 np7", None, (512, 1, 1, 0.9, 10, 7, 20, "hetero")), ("C4 np8", "c4n8", None)]
+
+
+def configs_section():
+    """The other BASELINE configurations (C1 - C4, Chebyshev order sweep 4 - 8) on this GPU, kernel id 0: time of one
+    application of the GMRES operator (CUDA events, device-resident), the M2L operator stream against the HBM roofline,
+    the evaluator (cache phase) and the GMRES solve of main.cpp:141.  Where a fixture of the compiled reference exists
+    (tests/golden/<name>.npz) the same run reports its distance from it."""
+    from aniso_b200 import Aniso
+
+    peak, _ = measured_peak()
+    rows = {}
+    for label, name, cfg in CONFIG_ROWS:
+        sz, deg, K, g, sr, np_, ml, kind = cases.CASES[name] if name else cfg
+        t0 = time.perf_counter()
+        a = Aniso(sz, deg, K, g, sr, np_, ml)
+        setup = time.perf_counter() - t0
+        x, y, w = a.nodes()
+        ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+        a.setCoeff(ss, st)
+        a.cache(0)
+        ct, cnt, ab, tr = a.cache_times(), a.cache_counts(), a.apply_bytes(), a.tree_stats()
+        r = np_ * np_
+        m2l_ms, p2p_ms = a.time_kernel(0, 0, 20), a.time_kernel(0, 1, 20)
+        m2l_alg = ab["m2l"] + 8 * r * tr["nodes"]
+        b = a.mapping(cases.gaussian_source(x, y), 0)
+        a.gmres(b)  # allocates the Krylov work space
+        t0 = time.perf_counter()
+        xs, rc, it, hist = a.gmres(b)
+        t_gm = time.perf_counter() - t0
+        row = {"N": int(x.size), "np": np_, "deg": deg, "setup_s": setup, "matvec_ms": a.time_forward(20),
+               "m2l_stream_ms": m2l_ms, "m2l_stream_gbs": m2l_alg / m2l_ms / 1e6, "m2l_stream_frac_of_peak": m2l_alg / m2l_ms / 1e6 / peak,
+               "p2p_stream_ms": p2p_ms, "p2p_fill_ms": ct["p2p_fill_ms"], "m2l_fill_ms": ct["m2l_fill_ms"], "stencil_ms": ct["stencil_ms"],
+               "near_field_interactions_per_s": cnt["p2p"] / (ct["p2p_fill_ms"] * 1e-3) if ct["p2p_fill_ms"] else None,
+               "gmres_iters": int(it), "gmres_rc": int(rc), "gmres_ms_host_api": t_gm * 1e3, "gmres_final_resid": float(hist[it])}
+        gpath = os.path.join(ROOT, "tests", "golden", "%s.npz" % name) if name else None
+        if gpath and os.path.exists(gpath):
+            gd = np.load(gpath)
+            stride = int(gd["stride"])
+            row["parity"] = {"fixture": "tests/golden/%s.npz (compiled reference)" % name,
+                             "gm_b_rel_l2": float(np.linalg.norm(b[::stride] - gd["gm_b"]) / np.linalg.norm(gd["gm_b"])),
+                             "gmres_iters_ref": int(gd["gm_iters"]), "gmres_iters_gpu": int(it),
+                             "gm_x_rel_l2": float(np.linalg.norm(xs[::stride] - gd["gm_x"]) / np.linalg.norm(gd["gm_x"]))}
+        rows[label] = row
+        a.delete()
+    return rows
 
 
 def run_ours(args):
@@ -282,18 +414,22 @@ def run_ours(args):
     torch.cuda.set_device(local)
     L = _lib.load()
     uid = None
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def new_uid():  # a fresh NCCL unique id from rank 0, agreed by all ranks (one per communicator / handle)
+        import ctypes
+
         buf = torch.zeros(128, dtype=torch.uint8)
         if rank == 0:
-            import ctypes
-
             raw = ctypes.create_string_buffer(128)
             _lib.check(L.aniso_nccl_unique_id(raw))
             buf = torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8).clone()
         buf = buf.cuda()
         dist.broadcast(buf, 0)
-        uid = bytes(buf.cpu().numpy().tobytes())
+        return bytes(buf.cpu().numpy().tobytes())
+
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        uid = new_uid()
 
     def barrier():
         torch.cuda.synchronize()
@@ -377,6 +513,42 @@ def run_ours(args):
     barrier()
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
 
+    # ---- parity of this run against the compiled reference at the same configuration (tests/golden/c5.npz) ----
+    parity = None
+    gpath = os.path.join(ROOT, "tests", "golden", "c5.npz")
+    if sz == 1024 and os.path.exists(gpath):
+        gd = np.load(gpath)
+        stride = int(gd["stride"])
+        f1 = cases.tilted_source(x, y)
+
+        def gather_rows(own_dev):  # owned rows (slot order) of every rank -> full vector in reference order, on every rank
+            full = torch.zeros(n, dtype=torch.float64, device="cuda")
+            full[slot0:slot1] = own_dev
+            if world > 1:
+                dist.all_reduce(full)
+            ref_order = np.empty(n)
+            ref_order[perm] = full.cpu().numpy()
+            return ref_order
+
+        def sampled_err(got, key):
+            return float(np.linalg.norm(got[::stride] - gd[key]) * np.sqrt(stride) / float(gd[key + "_norm"]))
+
+        # (a) device-resident sharded matvec  (b) the host API (every rank fills its owned rows)
+        f1_slots = torch.from_numpy(f1[perm]).cuda()
+        o_own = torch.empty(nown, dtype=torch.float64, device="cuda")
+        _lib.check(L.aniso_mapping_dev(a.h, f1_slots.data_ptr(), 0, o_own.data_ptr()))
+        a.synchronize()
+        dev_res = gather_rows(o_own)
+        host_out = np.zeros(n)
+        _lib.check(L.aniso_mapping(a.h, f1, 0, host_out))
+        if world > 1:
+            t = torch.from_numpy(host_out).cuda()
+            dist.all_reduce(t)
+            host_out = t.cpu().numpy()
+        parity = {"fixture": "tests/golden/c5.npz: the compiled reference at this configuration (N=2^20), every %dth row" % stride,
+                  "mapping_dev_rel_l2": sampled_err(dev_res, "f1_id0_out"), "mapping_host_api_rel_l2": sampled_err(host_out, "f1_id0_out"),
+                  "gather_rows": gather_rows}
+
     # ---- roofline of the dominant kernel: the M2L streaming apply (bsr_apply_kernel over the V/X blocks) ----
     ab = a.apply_bytes()
     tr = a.tree_stats()
@@ -428,6 +600,18 @@ def run_ours(args):
         if t_first is None:
             t_first = t_gmres
 
+    if parity is not None:
+        gather_rows = parity.pop("gather_rows")
+        xs_ref = gather_rows(xs)
+        b_ref = gather_rows(b_own)
+        gd = np.load(gpath)
+        stride = int(gd["stride"])
+        parity.update({"gm_b_rel_l2": float(np.linalg.norm(b_ref[::stride] - gd["gm_b"]) / np.linalg.norm(gd["gm_b"])),
+                       "gmres_iters_ref": int(gd["gm_iters"]), "gmres_iters_gpu": int(it.value),
+                       "gmres_x_rel_l2": float(np.linalg.norm(xs_ref[::stride] - gd["gm_x"]) / np.linalg.norm(gd["gm_x"])),
+                       "gmres_last_printed_resid_ref": float(gd["gm_hist"][-1]),
+                       "gmres_same_step_resid_gpu": float(hist[min(int(gd["gm_iters"]), int(it.value)) - 1])})
+
     line = None
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -435,8 +619,9 @@ def run_ours(args):
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload_name(sz), "l2": "operator stream %.2f GB per step > 126 MB L2, no flush needed"
                            % ((ab["p2p"] + ab["m2l"]) / 1e9), "partition": "target leaves by quadtree ownership, %d rank(s)" % world},
-                "e2e": {"value": n / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8 * nown,
-                        "ms_per_step": e2e_s * 1e3},
+                "e2e": {"value": n / e2e_s, "unit": UNIT, "h2d_bytes_per_step": 8 * ((n + world - 1) // world), "d2h_bytes_per_step": 8 * nown,
+                        "ms_per_step": e2e_s * 1e3,
+                        "note": "per rank: each rank uploads 1/n_gpus of the source (the pieces are all-gathered over NVLink) and reads back its owned rows"},
                 "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof,
                 "near_field_interactions_per_s": all_p2p / (p2p_fill_ms * 1e-3) if p2p_fill_ms else None,
                 "cache": {"wall_s": t_cache, "p2p_pairs": int(all_p2p), "m2l_pairs": int(all_m2l), "p2p_fill_ms": p2p_fill_ms,
@@ -444,11 +629,23 @@ def run_ours(args):
                           "m2l_evals_per_s": all_m2l / (m2l_fill_ms * 1e-3) if m2l_fill_ms else None},
                 "gmres": {"rc": int(rc), "iters": int(it.value), "final_resid": float(hist[it.value]), "time_to_solve_s": t_gmres,
                           "first_call_s": t_first, "m": 80, "tol": 1e-12, "gpu_launches": int(gm_launches)},
-                "setup_s": t_setup}
-        if world == 1 and not args.no_block:
-            a.delete()
-            a = None
-            line["block_operator"] = block_section(sz)
+                "setup_s": t_setup, "library_config": a.config()}
+        if parity is not None:
+            line["parity" if world == 1 else "parity_sharded"] = parity
+        roof["traffic_source"] = ("dram__bytes_read.sum + dram__bytes_write.sum of the same kernel from the committed `ncu --set full` "
+                                  "capture %s (cannot be measured live)" % NCU_TRAFFIC_SOURCE) if roof["traffic"] else None
+    if not args.no_block and (world == 1 or args.block_sharded):
+        a.delete()
+        a = None
+        blk = block_section(sz, world=world, rank=rank, new_uid=new_uid, device=local)
+        if rank == 0:
+            line["block_operator"] = blk
+    if rank == 0:
+        if world == 1 and not args.no_configs:
+            if a is not None:
+                a.delete()
+                a = None
+            line["configs"] = configs_section()
         if world == 1 and not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_baseline(args)
@@ -472,7 +669,10 @@ def main():
     ap.add_argument("--sz", type=int, default=1024, help="cells per side (N = sz^2); 1024 = BASELINE C5")
     ap.add_argument("--ref-sz", type=int, default=0, help="sample size of the reference arm (0 = by core count)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-block", action="store_true", help="skip the multi-mode block operator section (N = 1 only)")
+    ap.add_argument("--no-block", action="store_true", help="skip the multi-mode block operator section")
+    ap.add_argument("--block-sharded", action="store_true", help="run the block operator section on N > 1 ranks too")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1-C4 rows (N = 1 only)")
+    ap.add_argument("--no-ref-gmres", action="store_true", help="reference arm: skip its GMRES solve")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

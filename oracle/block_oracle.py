@@ -46,8 +46,14 @@ def _rotation(dx, dy):  # GeneratePlaneRotation, gmres.cpp:26-39
     return cs, t * cs
 
 
-def gmres(A, b, x0=None, m=400, max_iter=400, tol=1e-11):
-    """gmres.cpp:53-169.  Returns (x, rc, iterations, residual history); rc 0 = converged."""
+def gmres(A, b, x0=None, m=400, max_iter=400, tol=1e-11, prec=None):
+    """gmres.cpp:53-169.  Returns (x, rc, iterations, residual history); rc 0 = converged.
+    prec: left preconditioner r -> M^-1 r (the hook aniso.m:165 passes to MATLAB's gmres; gmres.cpp:7 "todo:
+    preconditioner"): the same recurrence on M^-1 A x = M^-1 b, residuals measured as |M^-1 (b - A x)| / |M^-1 b|."""
+    if prec is not None:
+        A0, b0 = A, b
+        A = lambda v: prec(A0(v))  # noqa: E731
+        b = prec(b0)
     n = b.size
     x = np.zeros(n) if x0 is None else x0.copy()
     m = min(m, max(max_iter, 1))

@@ -20,7 +20,10 @@ def golden():
 
     def load(name):
         if name not in cache:
-            cache[name] = dict(np.load(os.path.join(ROOT, "tests", "golden", name + ".npz")))
+            path = os.path.join(ROOT, "tests", "golden", name + ".npz")
+            if not os.path.exists(path):
+                pytest.skip("fixture %s.npz has not been generated (tests/golden/make_golden.py %s)" % (name, name))
+            cache[name] = dict(np.load(path))
         return cache[name]
 
     return load

@@ -123,3 +123,70 @@ def test_batched_block_operator_matches_the_loop(cfg, monkeypatch):
     monkeypatch.setenv("ANISO_STREAM_REGS", "1")  # ... and with register-held loads instead of the TMA ring
     assert rel(a.forward(u), fw) < 1e-13
     a.delete()
+
+
+def _diag_prec(n, K=1):
+    """a fixed diagonal left preconditioner (stand-in for the FEM diffusion solve of aniso.m:111-119, which is outside the path)"""
+    d = 1.0 / (1.0 + 0.5 * np.cos(np.arange(K * n) * 0.37) ** 2)
+    return lambda r: d * r
+
+
+@pytest.mark.parametrize("name", ["a16", "k3h16", "b8d3"])
+def test_block_gmres_preconditioner_hook(golden, name):
+    """aniso.m:165 `gmres(A, rhs, 400, 1e-11, 400, @obj.prec)`: the identity callback reproduces the unpreconditioned solve
+    step for step; a diagonal callback follows the oracle's left-preconditioned GMRES (restated gmres.cpp with M^-1 applied
+    to b, r0 and every A v) on the compiled reference's operator values (golden forward / the oracle mforward)."""
+    from oracle import block_oracle, oracleapi
+
+    g = golden(name + "_block")
+    a, K, gg, ss, n = make(name)
+    charge = g["u"]
+    x0, rc0, it0, h0 = a.solve(charge)
+    x1, rc1, it1, h1 = a.solve(charge, prec=lambda r: r)
+    assert rc0 == rc1 == 0 and it1 == it0
+    assert rel(x1, x0) < 1e-10
+    np.testing.assert_allclose(h1[: it0 - 2], h0[: it0 - 2], rtol=1e-6, atol=1e-12)
+    P = _diag_prec(n, K)
+    x2, rc2, it2, h2 = a.solve(charge, prec=P)
+    sz, deg, _, _, sr, np_, ml, kind = cases.BLOCK_CASES[name]
+    o = oracleapi.OracleAniso(sz, deg, K, gg, sr, np_, ml)
+    xo, yo, wo = o.nodes()
+    o.set_coeff(*cases.sigma_fields(kind, xo, yo, sz, deg))
+    A = lambda v: v - block_oracle.mforward(o, v, K, n, gg, ss)  # noqa: E731
+    xr, rcr, itr, hr = block_oracle.gmres(A, g["forward"], m=400, max_iter=400, tol=1e-11, prec=P)
+    assert rc2 == rcr == 0 and abs(it2 - itr) <= 1, (it2, itr)
+    assert rel(x2, xr) < 1e-8
+    m = min(it2, itr) - 2
+    np.testing.assert_allclose(h2[:m], hr[:m], rtol=5e-3, atol=1e-8)
+    assert rel(x2, x0) < 1e-7  # same solution as the unpreconditioned solve
+    a.delete()
+
+
+def test_gmres_preconditioner_hook_single_mode(golden):
+    """aniso_gmres_prec on the main.cpp operator: identity = plain solve, diagonal = oracle's left-preconditioned GMRES;
+    a failing callback surfaces as an error instead of crossing the C boundary."""
+    from aniso_b200 import Aniso, AnisoError
+    from oracle import block_oracle, oracleapi
+
+    g = golden("b8d3")
+    sz, deg, K, gg, sr, np_, ml, kind = cases.CASES["b8d3"]
+    a = Aniso(sz, deg, K, gg, sr, np_, ml)
+    x, y, w = a.nodes()
+    ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+    a.setCoeff(ss, st)
+    a.cache(0)
+    b = g["gm_b"]
+    x0, rc0, it0, h0 = a.gmres(b)
+    x1, rc1, it1, h1 = a.gmres(b, prec=lambda r: r)
+    assert rc0 == rc1 == 0 and it0 == it1 == int(g["gm_iters"]) and rel(x1, x0) < 1e-10
+    P = _diag_prec(x.size)
+    x2, rc2, it2, h2 = a.gmres(b, prec=P)
+    o = oracleapi.OracleAniso(sz, deg, K, gg, sr, np_, ml)
+    o.set_coeff(ss, st)
+    A = lambda v: v - o.mapping(ss * v, 0)  # noqa: E731
+    xr, rcr, itr, hr = block_oracle.gmres(A, b, m=80, max_iter=400, tol=1e-12, prec=P)
+    assert rc2 == rcr == 0 and abs(it2 - itr) <= 1
+    assert rel(x2, xr) < 1e-8
+    with pytest.raises(AnisoError):
+        a.gmres(b, prec=lambda r: 1 / 0)
+    a.delete()
