@@ -52,8 +52,11 @@ struct aniso_handle {
     // second stream of the matvec: the two big operator streams (P2P, deepest-level M2L) run here while the
     // latency-bound tree passes run on `st`; forked and joined with events inside every run_fmm
     cudaStream_t st_bulk = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr, ev_own = nullptr;
     bool overlap = true;
+    // sharded upward pass (nranks > 1, complete uniform tree, equal shares): every rank runs P2M / M2M on its own sub-trees
+    // only and the multipoles of all levels are all-gathered (one grouped NCCL call) instead of a replicated upward pass
+    bool up_sharded = false;
     std::vector<cudaEvent_t> copy_ev;  // per-chunk events of the device -> host copy
     // ANISO_PHASE_TIMES=1: events between the phases of every matvec on `st`, averages printed by aniso_destroy (development aid)
     struct PhaseTimer {
@@ -214,7 +217,7 @@ void ensure_device(aniso_handle* h) {
         CK(cudaStreamCreateWithPriority(&h->st, cudaStreamNonBlocking, hi));
         CK(cudaStreamCreateWithPriority(&h->st_bulk, cudaStreamNonBlocking, lo));
     }
-    for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join, &h->ev_own}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
     h->pt.on = getenv("ANISO_PHASE_TIMES") != nullptr;
     const HostPlan& p = h->plan;
@@ -317,6 +320,10 @@ void ensure_device(aniso_handle* h) {
         for (size_t k = 0; ok && k < p.leaves.size(); ++k) ok = p.leaves[k] == p.level_ptr[deepest] + (int)k;
         h->subtree_ok = ok;
         if (ok) h->sub = make_subtree_plan(h->first_m2l_level, deepest, r);
+        bool equal = h->nranks > 1 && h->overlap && !getenv("ANISO_UP_REPLICATED");
+        for (int q = 0; equal && q < h->nranks; ++q)
+            equal = h->all_slot_end[q] - h->all_slot_begin[q] == N / h->nranks && h->all_slot_begin[q] == q * (N / h->nranks);
+        h->up_sharded = ok && equal && N % h->nranks == 0 && (1 << (2 * h->first_m2l_level)) % h->nranks == 0;
     }
     // sigma grid
     h->d_chat = dalloc<double>(h, N);
@@ -499,7 +506,7 @@ int aniso_destroy(aniso_t* h) {
         if (h->pinned) cudaFreeHost(h->pinned);
         if (h->pinned_small) cudaFreeHost(h->pinned_small);
         cudaStreamSynchronize(h->st_bulk);
-        for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join})
+        for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join, h->ev_own})
             if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : h->copy_ev) cudaEventDestroy(e);
         for (cudaEvent_t e : h->gm_ev)
@@ -703,10 +710,36 @@ StencilCache& ensure_stencils(aniso_handle* h, int id) {
     return h->stencils[id] = s;
 }
 
+// The source of a sharded operator application when it exists only as the owned shards of the ranks (GMRES vectors): the
+// all-gather and the scaling are then part of the two-stream schedule of run_fmm instead of preceding it.
+struct ShardSource {
+    const double* shard;  // owned rows, slot order
+    const double* sig_s;  // full vector (slot order) or nullptr
+};
+
+void allgather_slots(aniso_handle* h, const double* shard, double* full, cudaStream_t st);
+
+// all-gather of the multipoles of every level that has M2L lists: level L holds 4^L nodes in Morton order and rank q owns
+// the q-th of nranks equal ranges, so each level is one in-place ncclAllGather; the calls are grouped into a single launch
+void allgather_multipoles(aniso_handle* h) {
+    NcclApi* a = h->nccl;
+    const int r = h->T.r, deepest = h->T.nlevels - 1;
+    a->GroupStart();
+    for (int L = h->first_m2l_level; L <= deepest; ++L) {
+        const size_t cnt = ((size_t)1 << (2 * L)) / h->nranks * r;
+        double* lvl = h->d_mcharge + (size_t)h->plan.level_ptr[L] * r;
+        ncclResult_t rc = a->AllGather(lvl + cnt * h->rank, lvl, cnt, ncclDouble, h->comm, h->st);
+        if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather: ") + a->GetErrorString(rc));
+    }
+    ncclResult_t rc = a->GroupEnd();
+    if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclGroupEnd: ") + a->GetErrorString(rc));
+}
+
 // kernel::runFast (bbfmm.h:565-592): upPass + downPassFast from the cached operators.
 // q: scaled source, full vector in slot order.  out: owned range.
+// src (sharded handles, sub-tree path): the source is still spread over the ranks; q / f are produced here (h->d_q, h->d_f).
 void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* out, int mode = 0, const double* stencil = nullptr,
-             const double* f = nullptr, const double* x_own = nullptr) {
+             const double* f = nullptr, const double* x_own = nullptr, const ShardSource* src = nullptr) {
     const HostPlan& p = h->plan;
     const DevTree& T = h->T;
     const int L0 = h->first_m2l_level, deepest = T.nlevels - 1;
@@ -720,15 +753,39 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     const int ng = h->m2l.groups, gd = h->overlap ? h->m2l_deep_g0 : ng;
     cudaStream_t sb = h->overlap ? h->st_bulk : h->st;
     if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
-    if (h->overlap) {
+    if (src) {
+        // Sharded source (requires up_sharded): the owned part is scaled at once on `st`, so that this rank's upward pass
+        // starts from its own shard while the all-gather of the other shards and their scaling run on `st_bulk`.
+        const int N = p.N, s0 = h->slot0, n = h->nown;
+        CK(cudaEventRecord(h->ev_fork, h->st));
+        CK(cudaStreamWaitEvent(sb, h->ev_fork, 0));
+        LAUNCH(h, launch_scale(n, src->shard, src->sig_s ? src->sig_s + s0 : nullptr, h->G.pw + s0, h->G.perm + s0, h->d_f, h->d_q + s0, h->st));
+        CK(cudaEventRecord(h->ev_own, h->st));
+        phase_mark(h, "scale_own");
+        allgather_slots(h, src->shard, h->d_xfull, sb);
+        LAUNCH(h, launch_scale(s0, h->d_xfull, src->sig_s, h->G.pw, h->G.perm, h->d_f, h->d_q, sb));
+        const int e0 = s0 + n;
+        LAUNCH(h, launch_scale(N - e0, h->d_xfull + e0, src->sig_s ? src->sig_s + e0 : nullptr, h->G.pw + e0, h->G.perm + e0, h->d_f,
+                               h->d_q + e0, sb));
+        CK(cudaStreamWaitEvent(sb, h->ev_own, 0));  // P2P reads the whole of q
+        q = h->d_q;
+    } else if (h->overlap) {
         CK(cudaEventRecord(h->ev_fork, h->st));
         CK(cudaStreamWaitEvent(sb, h->ev_fork, 0));
     }
     LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, sb));
     if (h->subtree_ok) {
         // complete uniform tree: each pass is ceil(levels/3) launches (subtree.cu)
-        h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, h->overlap ? h->ev_leaf : nullptr);
-        phase_mark(h, "up");
+        if (h->up_sharded) {
+            h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, nullptr, h->rank, h->nranks);
+            phase_mark(h, "up_own");
+            allgather_multipoles(h);
+            CK(cudaEventRecord(h->ev_leaf, h->st));
+            phase_mark(h, "gather_multipoles");
+        } else {
+            h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, h->overlap ? h->ev_leaf : nullptr);
+            phase_mark(h, "up");
+        }
         if (h->overlap) {
             CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
             if (gd < ng) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd, ng - gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, sb));
@@ -781,9 +838,9 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
 
 // all-gather of the owned shards into a full slot-order vector; counts differ per rank, so this is a
 // grouped broadcast per owner
-void allgather_slots(aniso_handle* h, const double* shard, double* full) {
+void allgather_slots(aniso_handle* h, const double* shard, double* full, cudaStream_t st) {
     if (h->nranks == 1) {
-        if (shard != full) CK(cudaMemcpyAsync(full, shard, sizeof(double) * h->plan.N, cudaMemcpyDeviceToDevice, h->st));
+        if (shard != full) CK(cudaMemcpyAsync(full, shard, sizeof(double) * h->plan.N, cudaMemcpyDeviceToDevice, st));
         return;
     }
     NcclApi* a = h->nccl;
@@ -793,7 +850,7 @@ void allgather_slots(aniso_handle* h, const double* shard, double* full) {
         for (int r = 0; r < h->nranks; ++r)
             equal = equal && h->all_slot_end[r] - h->all_slot_begin[r] == cnt && h->all_slot_begin[r] == r * cnt;
         if (equal) {  // one collective instead of nranks broadcasts
-            ncclResult_t rc = a->AllGather(shard, full, cnt, ncclDouble, h->comm, h->st);
+            ncclResult_t rc = a->AllGather(shard, full, cnt, ncclDouble, h->comm, st);
             if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather: ") + a->GetErrorString(rc));
             return;
         }
@@ -802,12 +859,13 @@ void allgather_slots(aniso_handle* h, const double* shard, double* full) {
     for (int r = 0; r < h->nranks; ++r) {
         const int b = h->all_slot_begin[r], n = h->all_slot_end[r] - b;
         if (n == 0) continue;
-        ncclResult_t rc = a->Broadcast(r == h->rank ? shard : full + b, full + b, n, ncclDouble, r, h->comm, h->st);
+        ncclResult_t rc = a->Broadcast(r == h->rank ? shard : full + b, full + b, n, ncclDouble, r, h->comm, st);
         if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclBroadcast: ") + a->GetErrorString(rc));
     }
     ncclResult_t rc = a->GroupEnd();
     if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclGroupEnd: ") + a->GetErrorString(rc));
 }
+void allgather_slots(aniso_handle* h, const double* shard, double* full) { allgather_slots(h, shard, full, h->st); }
 
 void allreduce_scalars(aniso_handle* h, double* d, int n) {
     if (h->nranks == 1) return;
@@ -817,9 +875,19 @@ void allreduce_scalars(aniso_handle* h, double* d, int n) {
 
 // mapping in slot order: full source (unscaled) -> owned rows
 void mapping_slots(aniso_handle* h, const double* f_full, int id, const double* sig_s, const double* x_own, double* out,
-                   int subtract) {
+                   int subtract, const double* f_shard = nullptr) {
     OperatorCache& c = ensure_ops(h, id, PART_BOTH);
     StencilCache& s = ensure_stencils(h, id);
+    if (f_shard && h->up_sharded) {  // the source is the owned shard of every rank: gather + scale inside the schedule
+        const ShardSource src{f_shard, sig_s};
+        run_fmm(h, c, nullptr, out, subtract ? 2 : 1, s.call, h->d_f, x_own, &src);
+        return;
+    }
+    if (f_shard) {
+        allgather_slots(h, f_shard, h->d_xfull);
+        f_full = h->d_xfull;
+        phase_mark(h, "allgather");
+    }
     const double* f = f_full;
     if (sig_s) {
         LAUNCH(h, launch_scale(h->plan.N, f_full, sig_s, h->G.pw, h->G.perm, h->d_f, h->d_q, h->st));
@@ -1044,14 +1112,9 @@ int aniso_forward_dev(aniso_t* h, const double* x_dev, double* y_dev) {
     REQUIRE(h && x_dev && y_dev, "null pointer");
     ensure_device(h);
     CK(cudaSetDevice(h->device));
-    const double* full = x_dev;
     phase_mark(h, nullptr);
-    if (h->nranks > 1) {
-        allgather_slots(h, x_dev, h->d_xfull);
-        full = h->d_xfull;
-    }
-    phase_mark(h, "allgather");
-    mapping_slots(h, full, 0, h->d_sig_s, x_dev, y_dev, 1);
+    if (h->nranks > 1) mapping_slots(h, nullptr, 0, h->d_sig_s, x_dev, y_dev, 1, x_dev);
+    else mapping_slots(h, x_dev, 0, h->d_sig_s, x_dev, y_dev, 1);
     return ANISO_OK;
     API_END
 }
@@ -1193,12 +1256,8 @@ double read_scalar(aniso_handle* h, const double* d) {
 }
 
 void forward_own(aniso_handle* h, const double* x_own, double* y_own) {
-    const double* full = x_own;
-    if (h->nranks > 1) {
-        allgather_slots(h, x_own, h->d_xfull);
-        full = h->d_xfull;
-    }
-    mapping_slots(h, full, 0, h->d_sig_s, x_own, y_own, 1);
+    if (h->nranks > 1) mapping_slots(h, nullptr, 0, h->d_sig_s, x_own, y_own, 1, x_own);
+    else mapping_slots(h, x_own, 0, h->d_sig_s, x_own, y_own, 1);
 }
 
 // Multi-mode block operator of the MATLAB application (aniso.m:121-156): K angular modes of n values,

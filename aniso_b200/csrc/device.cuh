@@ -152,9 +152,10 @@ struct SubtreePlan {
 };
 SubtreePlan make_subtree_plan(int first_m2l_level, int deepest, int r);
 // P2M + M2M of every level down to first_m2l_level; leaf_done (optional) is recorded once the leaf multipoles exist.
-// Return value: kernels launched.
+// part / nparts: only the sub-trees of share `part` out of `nparts` equal Morton ranges (sharded upward pass; nparts must
+// divide the number of sub-tree roots of every chunk, i.e. 4^first_m2l_level).  Return value: kernels launched.
 int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
-                   cudaEvent_t leaf_done);
+                   cudaEvent_t leaf_done, int part = 0, int nparts = 1);
 // fl != nullptr: multi-term folds (block operator; needs fold == fold_p2p == true); C / f_ref / pot are then unused
 int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st,
                          const FoldList* fl = nullptr);

@@ -21,6 +21,7 @@ __global__ void scale_kernel(int n, const double* __restrict__ x, const double* 
 }
 void launch_scale(int n, const double* x, const double* sig_s, const double* w, const int* perm, double* f_ref, double* q,
                   cudaStream_t st) {
+    if (n <= 0) return;
     scale_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, x, sig_s, w, perm, f_ref, q);
 }
 

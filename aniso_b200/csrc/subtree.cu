@@ -57,12 +57,12 @@ __device__ __forceinline__ void subtree_m2m(const DevTree& T, int Ls, int m, int
 // once and parked in shared memory), then M2M up to the sub-tree root.
 template <int NP, int LANES, bool SMEM_R>
 __global__ void __launch_bounds__(256) up_leaf_kernel(DevTree T, DevGeom G, const double* __restrict__ q, double* __restrict__ mcharge,
-                                                      int Ls, int D) {
+                                                      int Ls, int D, int cta0) {
     extern __shared__ double sm[];
     __shared__ double tn[NP_MAX * NP_MAX];
     constexpr int UMAX = NP ? (NP * NP + LANES - 1) / LANES : (NP_MAX * NP_MAX + LANES - 1) / LANES;
     const int np = NP ? NP : T.np, r = np * np;
-    const int m = blockIdx.x, nl = 1 << (2 * D);
+    const int m = blockIdx.x + cta0, nl = 1 << (2 * D);  // cta0: first sub-tree of this rank's share (sharded upward pass)
     const int grp = threadIdx.x / LANES, lane = threadIdx.x % LANES, ngrp = blockDim.x / LANES;
     const int stride = 2 * np + 1;
     double* __restrict__ mult = sm;                                   // [lvoff(D+1)][r]
@@ -137,9 +137,9 @@ __global__ void __launch_bounds__(256) up_leaf_kernel(DevTree T, DevGeom G, cons
 }
 
 template <bool SMEM_R>
-__global__ void __launch_bounds__(256) up_mid_kernel(DevTree T, double* __restrict__ mcharge, int Ls, int D) {
+__global__ void __launch_bounds__(256) up_mid_kernel(DevTree T, double* __restrict__ mcharge, int Ls, int D, int cta0) {
     extern __shared__ double sm[];
-    const int r = T.r, m = blockIdx.x, nb = 1 << (2 * D);
+    const int r = T.r, m = blockIdx.x + cta0, nb = 1 << (2 * D);
     double* __restrict__ Rs = sm + (size_t)lvoff(D + 1) * r;
     if (SMEM_R)
         for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.R + i);
@@ -366,15 +366,16 @@ SubtreePlan make_subtree_plan(int L0, int deepest, int r) {
 }
 
 template <int NP>
-static void up_leaf_launch(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st) {
-    const int r = T.r, D = sp.leaf_D, ctas = 1 << (2 * sp.leaf_Ls);
+static void up_leaf_launch(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
+                           int part, int nparts) {
+    const int r = T.r, D = sp.leaf_D, all = 1 << (2 * sp.leaf_Ls), ctas = all / nparts, cta0 = part * ctas;
     const bool sr = smem_R(r);
     const size_t bytes = ((size_t)lvoff(D + 1) * r + (size_t)256 * (2 * T.np + 1) + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
     const bool l16 = T.r <= 16 && T.max_leaf <= 16;
 #define UP_LEAF(LANES, SR)                                                             \
     do {                                                                               \
         want_smem(up_leaf_kernel<NP, LANES, SR>, bytes);                               \
-        up_leaf_kernel<NP, LANES, SR><<<ctas, 256, bytes, st>>>(T, G, q, mcharge, sp.leaf_Ls, D); \
+        up_leaf_kernel<NP, LANES, SR><<<ctas, 256, bytes, st>>>(T, G, q, mcharge, sp.leaf_Ls, D, cta0); \
     } while (0)
     if (l16 && sr) UP_LEAF(16, true);
     else if (l16) UP_LEAF(16, false);
@@ -384,25 +385,25 @@ static void up_leaf_launch(const DevTree& T, const DevGeom& G, const SubtreePlan
 }
 
 int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
-                   cudaEvent_t leaf_done) {
+                   cudaEvent_t leaf_done, int part, int nparts) {
     switch (T.np) {
-        case 4: up_leaf_launch<4>(T, G, sp, q, mcharge, st); break;
-        case 6: up_leaf_launch<6>(T, G, sp, q, mcharge, st); break;
-        case 8: up_leaf_launch<8>(T, G, sp, q, mcharge, st); break;
-        default: up_leaf_launch<0>(T, G, sp, q, mcharge, st);
+        case 4: up_leaf_launch<4>(T, G, sp, q, mcharge, st, part, nparts); break;
+        case 6: up_leaf_launch<6>(T, G, sp, q, mcharge, st, part, nparts); break;
+        case 8: up_leaf_launch<8>(T, G, sp, q, mcharge, st, part, nparts); break;
+        default: up_leaf_launch<0>(T, G, sp, q, mcharge, st, part, nparts);
     }
     if (leaf_done) cudaEventRecord(leaf_done, st);
     const int r = T.r;
     const bool sr = smem_R(r);
     for (int c = 0; c < sp.nmid; ++c) {
-        const int D = sp.mid_D[c], ctas = 1 << (2 * sp.mid_Ls[c]);
+        const int D = sp.mid_D[c], ctas = (1 << (2 * sp.mid_Ls[c])) / nparts, cta0 = part * ctas;
         const size_t bytes = ((size_t)lvoff(D + 1) * r + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
         if (sr) {
             want_smem(up_mid_kernel<true>, bytes);
-            up_mid_kernel<true><<<ctas, 256, bytes, st>>>(T, mcharge, sp.mid_Ls[c], D);
+            up_mid_kernel<true><<<ctas, 256, bytes, st>>>(T, mcharge, sp.mid_Ls[c], D, cta0);
         } else {
             want_smem(up_mid_kernel<false>, bytes);
-            up_mid_kernel<false><<<ctas, 256, bytes, st>>>(T, mcharge, sp.mid_Ls[c], D);
+            up_mid_kernel<false><<<ctas, 256, bytes, st>>>(T, mcharge, sp.mid_Ls[c], D, cta0);
         }
     }
     return 1 + sp.nmid;
