@@ -1609,11 +1609,18 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
         std::fill(s.begin(), s.end(), 0.0);
         s[0] = beta;
         if (pipelined) {
+            int queued = 0;  // highest Arnoldi step of this cycle that has been queued
             queue_step(0);
             for (i = 0; i < m && j <= max_iter; ++i, ++j) {
                 if (hist && j - 1 < hist_cap) hist[j - 1] = resid;
                 *iters = j;
-                if (i + 1 < m && j + 1 <= max_iter) queue_step(i + 1);  // one step ahead of the report being waited for
+                if (queued < i) queue_step(queued = i);
+                // One step ahead of the report being waited for - unless the last known residual is within a factor 100 of the
+                // tolerance: GMRES gains well under a digit per step here, so above that step i does not converge and the
+                // queued step is never surplus, while the last two or three steps run one at a time (a surplus operator
+                // application costs more than the idle gaps of a whole solve).  The rule reads all-reduced values only, so
+                // every rank queues the same steps.
+                if (i + 1 < m && j + 1 <= max_iter && resid > 100.0 * tol) queue_step(queued = i + 1);
                 CK(cudaEventSynchronize(h->gm_ev[i & 1]));
                 resid = col[2 * (i & 1)];
                 if (col[2 * (i & 1) + 1] != 0.0) {
