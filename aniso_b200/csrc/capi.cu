@@ -53,6 +53,7 @@ struct aniso_handle {
     // latency-bound tree passes run on `st`; forked and joined with events inside every run_fmm
     cudaStream_t st_bulk = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr, ev_own = nullptr;
+    cudaEvent_t ev_chunk[kDeepChunks] = {};  // chunked tail: the deepest-level M2L rows of chunk c have been streamed
     bool overlap = true;
     // sharded upward pass (nranks > 1, complete uniform tree, equal shares): every rank runs P2M / M2M on its own sub-trees
     // only and the multipoles of all levels are all-gathered (one grouped NCCL call) instead of a replicated upward pass
@@ -113,18 +114,21 @@ struct aniso_handle {
 
 namespace {
 
-void phase_mark(aniso_handle* h, const char* name) {  // name == nullptr: start of a matvec
+// ANISO_PHASE_TIMES=1 (development aid): a time line of the matvec.  Every mark records an event on the stream given
+// (default: the latency stream `st`); when the next matvec starts, the marks of the previous one are turned into times
+// since its start and accumulated.  name == nullptr: start of a matvec (only aniso_forward_dev starts one).
+void phase_mark(aniso_handle* h, const char* name, cudaStream_t stream = nullptr) {
     auto& t = h->pt;
     if (!t.on) return;
-    if (name && (t.cur == 0 || t.cur >= 12 || t.closed)) return;  // only inside a matvec started by aniso_forward_dev
+    if (name && (t.cur == 0 || t.cur >= 24 || t.closed)) return;  // only inside a matvec started by aniso_forward_dev
     if (!name) {
         t.closed = false;
         if (t.cur > 1) {  // fold in the previous matvec (its events have completed by now or are waited for)
-            cudaEventSynchronize(t.ev[t.cur - 1]);
             if (t.sum.size() < (size_t)t.cur) t.sum.resize(t.cur, 0.0);
             for (int i = 1; i < t.cur; ++i) {
+                cudaEventSynchronize(t.ev[i]);
                 float ms = 0;
-                cudaEventElapsedTime(&ms, t.ev[i - 1], t.ev[i]);
+                cudaEventElapsedTime(&ms, t.ev[0], t.ev[i]);
                 t.sum[i] += ms;
             }
             ++t.reps;
@@ -137,7 +141,7 @@ void phase_mark(aniso_handle* h, const char* name) {  // name == nullptr: start 
         t.ev.push_back(e);
         t.name.push_back(name ? name : "start");
     }
-    cudaEventRecord(t.ev[t.cur++], h->st);
+    cudaEventRecord(t.ev[t.cur++], stream ? stream : h->st);
     if (name && std::string(name) == "down_leaf") t.closed = true;
 }
 
@@ -218,6 +222,7 @@ void ensure_device(aniso_handle* h) {
         CK(cudaStreamCreateWithPriority(&h->st_bulk, cudaStreamNonBlocking, lo));
     }
     for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join, &h->ev_own}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    for (auto& e : h->ev_chunk) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
     h->pt.on = getenv("ANISO_PHASE_TIMES") != nullptr;
     const HostPlan& p = h->plan;
@@ -294,23 +299,8 @@ void ensure_device(aniso_handle* h) {
         T.level_ptr = upload(h, p.level_ptr);
     }
     h->d_leaf_of_slot = upload(h, p.leaf_of_slot);
-    h->m2l = upload_csr(h, p.m2l);
-    h->p2p = upload_csr(h, p.p2p);
     h->first_m2l_level = T.nlevels;
     for (int g : p.m2l.group_node) h->first_m2l_level = std::min(h->first_m2l_level, p.nodes[g].level);
-    h->m2l_top_groups = 0;
-    for (int g : p.m2l.group_node)
-        if (p.nodes[g].level == h->first_m2l_level) ++h->m2l_top_groups;
-    {
-        // suffix of groups at the deepest level whose sources are all leaves (their multipoles come straight from P2M)
-        const int deepest = T.nlevels - 1, ng = (int)p.m2l.group_node.size();
-        int g0 = ng;
-        while (g0 > 0 && p.nodes[p.m2l.group_node[g0 - 1]].level == deepest) --g0;
-        bool leaf_sources = true;
-        for (int e = g0 < ng ? p.m2l.ent_ptr[g0] : (int)p.m2l.src_node.size(); e < (int)p.m2l.src_node.size(); ++e)
-            leaf_sources = leaf_sources && p.nodes[p.m2l.src_node[e]].leaf;
-        h->m2l_deep_g0 = (leaf_sources && h->first_m2l_level < deepest) ? g0 : ng;
-    }
     {
         // complete uniform quadtree?  (every node non-empty, all leaves on the deepest level, 4^L nodes on level L)
         const int deepest = T.nlevels - 1;
@@ -323,7 +313,43 @@ void ensure_device(aniso_handle* h) {
         bool equal = h->nranks > 1 && h->overlap && !getenv("ANISO_UP_REPLICATED");
         for (int q = 0; equal && q < h->nranks; ++q)
             equal = h->all_slot_end[q] - h->all_slot_begin[q] == N / h->nranks && h->all_slot_begin[q] == q * (N / h->nranks);
-        h->up_sharded = ok && equal && N % h->nranks == 0 && (1 << (2 * h->first_m2l_level)) % h->nranks == 0;
+        h->up_sharded = ok && equal && p.m2l.symmetric && N % h->nranks == 0 && (h->nranks & (h->nranks - 1)) == 0 &&
+                        (1 << (2 * h->first_m2l_level)) % h->nranks == 0;
+    }
+    if (h->up_sharded) {
+        // rank-major multipole storage (DevTree::pack_*): one all-gather moves the multipoles of every level
+        int logP = 0;
+        while ((1 << logP) < h->nranks) ++logP;
+        T.pack_logP = logP;
+        T.pack_L0 = h->first_m2l_level;
+        T.pack_tot = ((((1 << (2 * T.nlevels)) - 1) / 3) - (((1 << (2 * T.pack_L0)) - 1) / 3)) >> logP;
+        BlockCSR packed = p.m2l;  // sources of the M2L blocks are read at the packed positions
+        for (size_t e = 0; e < packed.col_off.size(); ++e) {
+            const int s = packed.src_node[e], L = p.nodes[s].level;
+            packed.col_off[e] = mc_node(T, L, s - p.level_ptr[L]) * r;
+        }
+        // symmetric storage: a group's row offset is only used to read the target's OWN multipole (the transposed product;
+        // results go to scratch rows), so it follows the multipole numbering too
+        for (size_t g = 0; g < packed.group_node.size(); ++g) {
+            const int t = packed.group_node[g], L = p.nodes[t].level;
+            packed.row_off[g] = mc_node(T, L, t - p.level_ptr[L]) * r;
+        }
+        h->m2l = upload_csr(h, packed);
+    } else
+        h->m2l = upload_csr(h, p.m2l);
+    h->p2p = upload_csr(h, p.p2p);
+    h->m2l_top_groups = 0;
+    for (int g : p.m2l.group_node)
+        if (p.nodes[g].level == h->first_m2l_level) ++h->m2l_top_groups;
+    {
+        // suffix of groups at the deepest level whose sources are all leaves (their multipoles come straight from P2M)
+        const int deepest = T.nlevels - 1, ng = (int)p.m2l.group_node.size();
+        int g0 = ng;
+        while (g0 > 0 && p.nodes[p.m2l.group_node[g0 - 1]].level == deepest) --g0;
+        bool leaf_sources = true;
+        for (int e = g0 < ng ? p.m2l.ent_ptr[g0] : (int)p.m2l.src_node.size(); e < (int)p.m2l.src_node.size(); ++e)
+            leaf_sources = leaf_sources && p.nodes[p.m2l.src_node[e]].leaf;
+        h->m2l_deep_g0 = (leaf_sources && h->first_m2l_level < deepest) ? g0 : ng;
     }
     // sigma grid
     h->d_chat = dalloc<double>(h, N);
@@ -497,7 +523,7 @@ int aniso_destroy(aniso_t* h) {
         cudaStreamSynchronize(h->st);
         if (h->pt.on && h->pt.reps > 0) {
             phase_mark(h, nullptr);
-            fprintf(stderr, "[aniso rank %d] phases over %d matvecs (us):", h->rank, h->pt.reps);
+            fprintf(stderr, "[aniso rank %d] time line over %d matvecs (us after the start; [b] = bulk stream):", h->rank, h->pt.reps);
             for (size_t i = 1; i < h->pt.sum.size(); ++i) fprintf(stderr, " %s %.1f", h->pt.name[i], 1e3 * h->pt.sum[i] / h->pt.reps);
             fprintf(stderr, "\n");
         }
@@ -510,6 +536,8 @@ int aniso_destroy(aniso_t* h) {
             if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : h->copy_ev) cudaEventDestroy(e);
         for (cudaEvent_t e : h->gm_ev)
+            if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : h->ev_chunk)
             if (e) cudaEventDestroy(e);
         cudaStreamDestroy(h->st_bulk);
         cudaStreamDestroy(h->st);
@@ -719,20 +747,13 @@ struct ShardSource {
 
 void allgather_slots(aniso_handle* h, const double* shard, double* full, cudaStream_t st);
 
-// all-gather of the multipoles of every level that has M2L lists: level L holds 4^L nodes in Morton order and rank q owns
-// the q-th of nranks equal ranges, so each level is one in-place ncclAllGather; the calls are grouped into a single launch
+// all-gather of the multipoles of every level that has M2L lists: rank-major storage (DevTree::pack_*, mc_node) puts the
+// nodes a rank owns on all levels back to back, so this is one in-place ncclAllGather of pack_tot * r doubles per rank
 void allgather_multipoles(aniso_handle* h) {
     NcclApi* a = h->nccl;
-    const int r = h->T.r, deepest = h->T.nlevels - 1;
-    a->GroupStart();
-    for (int L = h->first_m2l_level; L <= deepest; ++L) {
-        const size_t cnt = ((size_t)1 << (2 * L)) / h->nranks * r;
-        double* lvl = h->d_mcharge + (size_t)h->plan.level_ptr[L] * r;
-        ncclResult_t rc = a->AllGather(lvl + cnt * h->rank, lvl, cnt, ncclDouble, h->comm, h->st);
-        if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather: ") + a->GetErrorString(rc));
-    }
-    ncclResult_t rc = a->GroupEnd();
-    if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclGroupEnd: ") + a->GetErrorString(rc));
+    const size_t cnt = (size_t)h->T.pack_tot * h->T.r;
+    ncclResult_t rc = a->AllGather(h->d_mcharge + cnt * h->rank, h->d_mcharge, cnt, ncclDouble, h->comm, h->st);
+    if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllGather: ") + a->GetErrorString(rc));
 }
 
 // kernel::runFast (bbfmm.h:565-592): upPass + downPassFast from the cached operators.
@@ -753,52 +774,91 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     const int ng = h->m2l.groups, gd = h->overlap ? h->m2l_deep_g0 : ng;
     cudaStream_t sb = h->overlap ? h->st_bulk : h->st;
     if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
+    // The launches of the latency chain are issued to `st` BEFORE the bulk stream's operator streams: a stream kernel fills
+    // every SM, and sub-tree CTAs launched behind it would wait for its CTAs to retire (measured: upward pass 88 us instead of
+    // 55 at N = 2^20).  Issued first, they take their slots at once and the stream kernel fills the rest of the machine.
+    auto p2p_on_bulk = [&] {
+        LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, sb));
+        phase_mark(h, "[b]p2p", sb);
+    };
     if (src) {
-        // Sharded source (requires up_sharded): the owned part is scaled at once on `st`, so that this rank's upward pass
-        // starts from its own shard while the all-gather of the other shards and their scaling run on `st_bulk`.
+        // Sharded source (requires up_sharded): the all-gather of the shards starts at once on `st_bulk`; meanwhile the owned
+        // part is scaled on `st` and this rank's upward pass runs from it.  The other parts are scaled behind the gather.
         const int N = p.N, s0 = h->slot0, n = h->nown;
         CK(cudaEventRecord(h->ev_fork, h->st));
         CK(cudaStreamWaitEvent(sb, h->ev_fork, 0));
+        allgather_slots(h, src->shard, h->d_xfull, sb);
         LAUNCH(h, launch_scale(n, src->shard, src->sig_s ? src->sig_s + s0 : nullptr, h->G.pw + s0, h->G.perm + s0, h->d_f, h->d_q + s0, h->st));
         CK(cudaEventRecord(h->ev_own, h->st));
         phase_mark(h, "scale_own");
-        allgather_slots(h, src->shard, h->d_xfull, sb);
+        q = h->d_q;
+        h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, nullptr, h->rank, h->nranks);
+        phase_mark(h, "up_own");
         LAUNCH(h, launch_scale(s0, h->d_xfull, src->sig_s, h->G.pw, h->G.perm, h->d_f, h->d_q, sb));
         const int e0 = s0 + n;
         LAUNCH(h, launch_scale(N - e0, h->d_xfull + e0, src->sig_s ? src->sig_s + e0 : nullptr, h->G.pw + e0, h->G.perm + e0, h->d_f,
                                h->d_q + e0, sb));
         CK(cudaStreamWaitEvent(sb, h->ev_own, 0));  // P2P reads the whole of q
-        q = h->d_q;
+        phase_mark(h, "[b]x_gathered+scaled", sb);
+        p2p_on_bulk();
+        allgather_multipoles(h);
+        CK(cudaEventRecord(h->ev_leaf, h->st));
+        phase_mark(h, "gather_multipoles");
     } else if (h->overlap) {
         CK(cudaEventRecord(h->ev_fork, h->st));
         CK(cudaStreamWaitEvent(sb, h->ev_fork, 0));
     }
-    LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, sb));
+    if (!h->subtree_ok || !h->overlap) p2p_on_bulk();
     if (h->subtree_ok) {
         // complete uniform tree: each pass is ceil(levels/3) launches (subtree.cu)
-        if (h->up_sharded) {
+        if (src) {
+            // done above
+        } else if (h->up_sharded) {
             h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, nullptr, h->rank, h->nranks);
             phase_mark(h, "up_own");
+            p2p_on_bulk();
             allgather_multipoles(h);
             CK(cudaEventRecord(h->ev_leaf, h->st));
             phase_mark(h, "gather_multipoles");
         } else {
             h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, h->overlap ? h->ev_leaf : nullptr);
             phase_mark(h, "up");
+            if (h->overlap) p2p_on_bulk();
         }
+        // Chunked tail (plan.deep_chunks > 1): the deepest-level M2L rows are streamed chunk by chunk, and the leaf pass of a
+        // chunk's sub-trees (L2L + L2P + folds + stencil, latency-bound) starts as soon as that chunk has been streamed, under
+        // the HBM-bound stream of the next chunks; only the last chunk's leaf pass is exposed.
+        const int nch = (h->overlap && gd < ng && p.deep_chunks > 1 && (ng - gd) % p.deep_chunks == 0) ? p.deep_chunks : 1;
         if (h->overlap) {
             CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
-            if (gd < ng) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd, ng - gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, sb));
-            CK(cudaEventRecord(h->ev_join, sb));
+            const int per = (ng - gd) / nch;
+            for (int k = 0; k < nch && gd < ng; ++k) {
+                LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd + k * per, per), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, sb));
+                CK(cudaEventRecord(nch > 1 ? h->ev_chunk[k] : h->ev_join, sb));
+            }
+            if (gd >= ng) CK(cudaEventRecord(h->ev_join, sb));
+            phase_mark(h, "[b]m2l_deep", sb);
         }
         if (gd > 0) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, 0, gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
         phase_mark(h, "m2l_shallow");
         h->launches += launch_down_mid_tree(T, h->m2l, sym_m, h->sub, L0, h->d_mpot, h->st);
         phase_mark(h, "down_mid");
-        if (h->overlap) CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
-        phase_mark(h, "join_bulk");
-        h->launches += launch_down_leaf_tree(T, h->G, h->m2l, sym_m, h->p2p, sym_p, h->sub, L0, h->d_leaf_of_slot, h->slot0, h->nown,
-                                             h->d_mpot, h->d_pot, stencil, f, x_own, out, mode, h->st);
+        if (nch > 1) {
+            const int per_root = 1 << (2 * h->sub.leaf_D);  // leaves per sub-tree of the leaf pass
+            const int root0 = h->leaf_begin / per_root, nroots = (h->leaf_end - h->leaf_begin) / per_root / nch;
+            for (int k = 0; k < nch; ++k) {
+                CK(cudaStreamWaitEvent(h->st, h->ev_chunk[k], 0));
+                h->launches += launch_down_leaf_tree(T, h->G, h->m2l, sym_m, h->p2p, sym_p, h->sub, L0, h->d_leaf_of_slot, h->slot0,
+                                                     h->nown, h->d_mpot, h->d_pot, stencil, f, x_own, out, mode, h->st, nullptr,
+                                                     root0 + k * nroots, nroots);
+                if (k == nch - 2) phase_mark(h, "down_leaf_but_last");
+            }
+        } else {
+            if (h->overlap) CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
+            phase_mark(h, "join_bulk");
+            h->launches += launch_down_leaf_tree(T, h->G, h->m2l, sym_m, h->p2p, sym_p, h->sub, L0, h->d_leaf_of_slot, h->slot0, h->nown,
+                                                 h->d_mpot, h->d_pot, stencil, f, x_own, out, mode, h->st);
+        }
         phase_mark(h, "down_leaf");
         CK(cudaGetLastError());
         return;

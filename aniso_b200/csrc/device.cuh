@@ -69,7 +69,20 @@ struct DevTree {
     int* level_ptr = nullptr;                                   // nodes of level L: [level_ptr[L], level_ptr[L+1])
     int4* leaf_info = nullptr;                                  // per leaf: node id, pt_off, npts, 0
     int* child0 = nullptr;                                      // first child (children are consecutive) or -1
+    // Rank-major multipole storage of a sharded handle on a complete tree (pack_logP >= 0): the nodes rank q owns on the
+    // levels pack_L0 .. deepest (the q-th of 2^pack_logP equal Morton ranges of every level) are stored back to back,
+    // pack_tot nodes per rank, so that the multipoles of all levels travel in ONE in-place ncclAllGather.  Only the
+    // multipole array (mcharge) uses this numbering; see mc_node().
+    int pack_logP = -1, pack_L0 = 0, pack_tot = 0;
 };
+// position (in nodes) of node i of level L in the multipole array; complete trees only when packed
+__host__ __device__ __forceinline__ int mc_node(const DevTree& T, int L, int i) {
+    const int off = ((1 << (2 * L)) - 1) / 3;  // nodes above level L
+    if (T.pack_logP < 0) return off + i;
+    const int sh = 2 * L - T.pack_logP;        // 4^L / P nodes of this level per rank
+    const int base = (off - ((1 << (2 * T.pack_L0)) - 1) / 3) >> T.pack_logP;
+    return (i >> sh) * T.pack_tot + base + (i & ((1 << sh) - 1));
+}
 
 // cell-based correction tables (Geometry / singPrecompute data, uploaded once)
 struct DevGeom {
@@ -162,7 +175,7 @@ int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const S
 int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                           const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
                           const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
-                          const FoldList* fl = nullptr);
+                          const FoldList* fl = nullptr, int cta0 = 0, int nctas = -1);  // [cta0, cta0 + nctas): sub-trees of one chunk
 // L2P + tail of the matvec for slots [slot0, slot0+n):  fmm = pot[p] + L2P(p)
 //   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi   (C: fused stencil, f_ref: full unscaled source in reference order)
 void launch_l2p(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,

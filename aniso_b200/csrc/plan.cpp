@@ -496,7 +496,12 @@ static void finish_csr(BlockCSR& b) {
 }
 
 // Rewrites a uniform-block CSR into symmetric storage (see BlockCSR::symmetric).
-static void symmetrize(BlockCSR& b) {
+// chunk (optional): node -> chunk number.  A pair whose two nodes sit in different chunks is kept by the node of the LOWER
+// chunk: when the rows of the chunks are streamed one launch after the other, everything a target of chunk c receives -
+// its own products and the transposed products other targets drop into its scratch rows - has been written once the
+// launches of chunks <= c are done, so the consumer of chunk c (L2L / L2P of its sub-trees) can start while the later
+// chunks are still streaming.
+static void symmetrize(BlockCSR& b, const std::vector<int>* chunk = nullptr) {
     const int groups = (int)b.nrow.size(), R = b.uniform_block;
     if (!groups || R < 4 || R > 64 || getenv("ANISO_NO_SYM")) return;  // R = 16, 64: stream.cu bsr_apply_sym_kernel; else symg
     auto key = [](int t, int s) { return ((int64_t)t << 32) | (uint32_t)s; };
@@ -506,7 +511,10 @@ static void symmetrize(BlockCSR& b) {
     // Of a pair (A,B) the block is kept by A when A+B is even and A < B, or A+B is odd and A > B: every target keeps
     // about half of its pairs, so the warps of the streaming kernel stay balanced.  An entry is a mirror (dropped)
     // when its partner exists and the partner owns the pair.
-    auto owns = [](int t, int s) { return ((t + s) & 1) ? t > s : t < s; };
+    auto owns = [chunk](int t, int s) {
+        if (chunk && (*chunk)[t] != (*chunk)[s]) return (*chunk)[t] < (*chunk)[s];
+        return ((t + s) & 1) ? t > s : t < s;
+    };
     std::vector<char> is_mirror(b.col_off.size(), 0);
     std::vector<int> row_of_entry(b.col_off.size(), -1);
     b.srow_ptr.assign(groups + 1, 0);
@@ -604,7 +612,20 @@ void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
     }
     finish_csr(m);
     finish_csr(q);
-    symmetrize(m);
+    // Chunks of the deepest level (complete trees: all owned leaves on the deepest level, in Morton order): kDeepChunks
+    // equal ranges of the owned leaves, aligned to whole sub-trees of the leaf pass (64 leaves).  Other nodes: chunk 0.
+    p.deep_chunks = 1;
+    std::vector<int> chunk(nn, 0);
+    {
+        const int nown = leaf_end - leaf_begin, deepest = p.treeMaxLevel;
+        bool ok = nown > 0 && nown % (kDeepChunks * 64) == 0 && leaf_begin % 64 == 0 && !getenv("ANISO_NO_CHUNKS");
+        for (int k = leaf_begin; ok && k < leaf_end; ++k) ok = p.nodes[p.leaves[k]].level == deepest && p.leaves[k] == p.leaves[leaf_begin] + (k - leaf_begin);
+        if (ok) {
+            p.deep_chunks = kDeepChunks;
+            for (int k = leaf_begin; k < leaf_end; ++k) chunk[p.leaves[k]] = (int)((int64_t)(k - leaf_begin) * kDeepChunks / nown);
+        }
+    }
+    symmetrize(m, p.deep_chunks > 1 ? &chunk : nullptr);
     symmetrize(q);
     p.m2l = std::move(m);
     p.p2p = std::move(q);

@@ -55,6 +55,8 @@ struct BlockCSR {
     int nrows_total = 0;                  // launch rows
 };
 
+constexpr int kDeepChunks = 4;
+
 struct HostPlan {
     // parameters (Aniso ctor, Aniso.h:14-15)
     int sz = 0, deg = 0, K = 0, kernelSize = 0, sr = 0, np = 0, maxLevelArg = 0;
@@ -81,6 +83,8 @@ struct HostPlan {
     std::vector<double> tnode;                // T_k(t_m), m*np+k
     std::vector<double> R;                    // 4 x r x r transfer matrices, R[c][(a)*r + b]
     BlockCSR m2l, p2p;
+    int deep_chunks = 1;                      // > 1: the owned deepest-level M2L rows form this many equal Morton ranges whose
+                                              //      symmetric pairs are kept by the earlier range (see symmetrize)
     std::vector<int> leaves;                  // non-empty leaves (new numbering)
     // statistics in the order of the golden fixtures
     long stats[9] = {0};

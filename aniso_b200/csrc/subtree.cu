@@ -34,7 +34,7 @@ __device__ __forceinline__ void subtree_m2m(const DevTree& T, int Ls, int m, int
         const int nb = 1 << (2 * d);
         const double* __restrict__ kids = sm + (size_t)lvoff(d + 1) * r;
         double* __restrict__ mine = sm + (size_t)lvoff(d) * r;
-        const size_t gbase = ((size_t)lvoff(Ls + d) + ((size_t)m << (2 * d))) * r;
+        const size_t gbase = (size_t)mc_node(T, Ls + d, m << (2 * d)) * r;  // a sub-tree's boxes of one level stay contiguous
         for (int o = threadIdx.x; o < nb * r; o += blockDim.x) {
             const int g = o / r, b = o - g * r;
             const double* __restrict__ src = kids + (size_t)g * 4 * r;
@@ -88,12 +88,12 @@ __global__ void __launch_bounds__(256) up_leaf_kernel(DevTree T, DevGeom G, cons
         if (j >= nl) break;
         int id, off, n;
         if (n0) {
-            id = lvoff(Ls + D) + m * nl + j;
+            id = mc_node(T, Ls + D, m * nl + j);
             off = (m * nl + j) * n0;
             n = n0;
         } else {
             const int4 info = T.leaf_info[(size_t)m * nl + j];  // id, pt_off, npts
-            id = info.x; off = info.y; n = info.z;
+            id = mc_node(T, Ls + D, info.x - lvoff(Ls + D)); off = info.y; n = info.z;
         }
         double acc[UMAX];
 #pragma unroll
@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(256) up_mid_kernel(DevTree T, double* __restri
     double* __restrict__ Rs = sm + (size_t)lvoff(D + 1) * r;
     if (SMEM_R)
         for (int i = threadIdx.x; i < 4 * r * r; i += blockDim.x) Rs[i] = __ldg(T.R + i);
-    const double* __restrict__ src = mcharge + ((size_t)lvoff(Ls + D) + (size_t)m * nb) * r;
+    const double* __restrict__ src = mcharge + (size_t)mc_node(T, Ls + D, m * nb) * r;
     double* __restrict__ dst = sm + (size_t)lvoff(D) * r;
     for (int i = threadIdx.x; i < nb * r; i += blockDim.x) dst[i] = src[i];
     __syncthreads();
@@ -247,10 +247,10 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
                                                         double* __restrict__ mpot, const double* __restrict__ pot,
                                                         const double* __restrict__ C, const double* __restrict__ f_ref,
                                                         const double* __restrict__ x, double* __restrict__ out, int mode, int Ls,
-                                                        int D, int top, const __grid_constant__ FoldList fl) {
+                                                        int D, int top, int cta0, const __grid_constant__ FoldList fl) {
     extern __shared__ double sm[];
     __shared__ double tn[NP_MAX * NP_MAX];
-    const int np = NP ? NP : T.np, r = np * np, m = blockIdx.x;
+    const int np = NP ? NP : T.np, r = np * np, m = blockIdx.x + cta0;  // cta0: first sub-tree of this launch (chunked tail)
     const int root = lvoff(Ls) + m;
     const int n0 = T.uniform_npts;  // > 0: slot ranges follow from the leaf index, no table look-ups
     const int rb = n0 ? (m << (2 * D)) * n0 : T.pt_off[root], rn = n0 ? n0 << (2 * D) : T.npts[root];
@@ -442,17 +442,18 @@ template <int NP>
 static void down_leaf_launch(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                              const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
                              const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
-                             const FoldList* flp) {
+                             const FoldList* flp, int cta0, int nctas) {
     static const FoldList none = FoldList();
     const FoldList& fl = flp ? *flp : none;
-    const int r = T.r, D = sp.leaf_D, Ls = sp.leaf_Ls, ctas = 1 << (2 * Ls), top = Ls == L0;
+    const int r = T.r, D = sp.leaf_D, Ls = sp.leaf_Ls, ctas = nctas >= 0 ? nctas : 1 << (2 * Ls), top = Ls == L0;
+    if (ctas == 0) return;
     const bool sr = smem_R(r);
     const size_t bytes = ((size_t)lvoff(D + 1) * r + (sr ? (size_t)4 * r * r : 0)) * sizeof(double);
 #define DOWN_LEAF(SR, FO, MU)                                                                                                   \
     do {                                                                                                                        \
         want_smem(down_leaf_kernel<NP, SR, FO, MU>, bytes);                                                                     \
         down_leaf_kernel<NP, SR, FO, MU><<<ctas, 256, bytes, st>>>(T, G, m2l, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, \
-                                                                   C, f_ref, x, out, mode, Ls, D, top, fl);                     \
+                                                                   C, f_ref, x, out, mode, Ls, D, top, cta0, fl);               \
     } while (0)
     if (flp && sr) DOWN_LEAF(true, true, true);
     else if (flp) DOWN_LEAF(false, true, true);
@@ -466,13 +467,13 @@ static void down_leaf_launch(const DevTree& T, const DevGeom& G, const DevCSR& m
 int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                           const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
                           const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
-                          const FoldList* fl) {
+                          const FoldList* fl, int cta0, int nctas) {
     if (n == 0) return 0;
     switch (T.np) {
-        case 4: down_leaf_launch<4>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl); break;
-        case 6: down_leaf_launch<6>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl); break;
-        case 8: down_leaf_launch<8>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl); break;
-        default: down_leaf_launch<0>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl);
+        case 4: down_leaf_launch<4>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas); break;
+        case 6: down_leaf_launch<6>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas); break;
+        case 8: down_leaf_launch<8>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas); break;
+        default: down_leaf_launch<0>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas);
     }
     return 1;
 }
