@@ -58,6 +58,17 @@ struct aniso_handle {
     // sharded upward pass (nranks > 1, complete uniform tree, equal shares): every rank runs P2M / M2M on its own sub-trees
     // only and the multipoles of all levels are all-gathered (one grouped NCCL call) instead of a replicated upward pass
     bool up_sharded = false;
+    // CUDA graphs of the operator y = x - mapping_0(sigma_s x), keyed by its two device pointers: the second application
+    // with a pointer pair is captured (both streams, the NCCL calls and the fork / join events become one graph), later ones
+    // replay it - one launch per matvec instead of ~12 kernel launches, ~8 event calls and 2 NCCL enqueues, which the host
+    // cannot issue fast enough for a 0.1 - 0.2 ms sharded matvec.  Dropped whenever the operators change (setCoeff).
+    struct FwdGraph {
+        int seen = 0;
+        cudaGraphExec_t exec = nullptr;
+        int64_t kernels = 0;
+    };
+    std::map<std::pair<const void*, void*>, FwdGraph> fwd_graphs;
+    bool use_graphs = true;
     std::vector<cudaEvent_t> copy_ev;  // per-chunk events of the device -> host copy
     // ANISO_PHASE_TIMES=1: events between the phases of every matvec on `st`, averages printed by aniso_destroy (development aid)
     struct PhaseTimer {
@@ -145,6 +156,12 @@ void phase_mark(aniso_handle* h, const char* name, cudaStream_t stream = nullptr
     if (name && std::string(name) == "down_leaf") t.closed = true;
 }
 
+void drop_graphs(aniso_handle* h) {
+    for (auto& kv : h->fwd_graphs)
+        if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    h->fwd_graphs.clear();
+}
+
 template <class T>
 T* dalloc(aniso_handle* h, size_t n) {
     T* p = nullptr;
@@ -225,6 +242,7 @@ void ensure_device(aniso_handle* h) {
     for (auto& e : h->ev_chunk) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
     h->pt.on = getenv("ANISO_PHASE_TIMES") != nullptr;
+    h->use_graphs = getenv("ANISO_NO_GRAPH") == nullptr && !h->pt.on;
     const HostPlan& p = h->plan;
     const int N = p.N, nn = (int)p.nodes.size(), r = p.rank;
     // geometry in slot order
@@ -527,6 +545,7 @@ int aniso_destroy(aniso_t* h) {
             for (size_t i = 1; i < h->pt.sum.size(); ++i) fprintf(stderr, " %s %.1f", h->pt.name[i], 1e3 * h->pt.sum[i] / h->pt.reps);
             fprintf(stderr, "\n");
         }
+        drop_graphs(h);
         if (h->comm && h->nccl) h->nccl->CommDestroy(h->comm);
         for (void* p : h->allocs) cudaFree(p);
         if (h->pinned) cudaFreeHost(h->pinned);
@@ -660,6 +679,7 @@ DevCSR sub_range(const DevCSR& m, int g0, int count) {
 }
 
 void free_caches(aniso_handle* h) {
+    drop_graphs(h);
     for (auto& kv : h->ops) {
         dfree(h, kv.second.p2p);
         dfree(h, kv.second.m2l);
@@ -958,6 +978,8 @@ void mapping_slots(aniso_handle* h, const double* f_full, int id, const double* 
     run_fmm(h, c, h->d_q, out, subtract ? 2 : 1, s.call, f, x_own);
 }
 
+void forward_own(aniso_handle* h, const double* x_own, double* y_own, bool graph);
+
 // host vector (N doubles) -> h->d_stage through the pinned buffer; the stream is drained first so the pinned
 // buffer is never rewritten under an in-flight copy.  Chunked: the CPU copy of chunk c+1 overlaps the DMA of chunk c.
 constexpr int COPY_CHUNK = 1 << 18;  // doubles (2 MB)
@@ -1173,8 +1195,8 @@ int aniso_forward_dev(aniso_t* h, const double* x_dev, double* y_dev) {
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     phase_mark(h, nullptr);
-    if (h->nranks > 1) mapping_slots(h, nullptr, 0, h->d_sig_s, x_dev, y_dev, 1, x_dev);
-    else mapping_slots(h, x_dev, 0, h->d_sig_s, x_dev, y_dev, 1);
+    if (!h->coeff_set) throw std::logic_error("setCoeff must precede the operator");
+    forward_own(h, x_dev, y_dev, true);
     return ANISO_OK;
     API_END
 }
@@ -1315,9 +1337,52 @@ double read_scalar(aniso_handle* h, const double* d) {
     return v;
 }
 
-void forward_own(aniso_handle* h, const double* x_own, double* y_own) {
+void forward_eager(aniso_handle* h, const double* x_own, double* y_own) {
     if (h->nranks > 1) mapping_slots(h, nullptr, 0, h->d_sig_s, x_own, y_own, 1, x_own);
     else mapping_slots(h, x_own, 0, h->d_sig_s, x_own, y_own, 1);
+}
+
+// graph == true: the caller applies the operator to this pointer pair again and again (GMRES on its fixed input buffer,
+// aniso_forward_dev from a benchmark or solver loop): first application eager (it also builds the operator caches and makes
+// the per-kernel shared-memory opt-ins), second one captured, then replays.
+void forward_own(aniso_handle* h, const double* x_own, double* y_own, bool graph) {
+    if (!graph || !h->use_graphs || !h->subtree_ok) {
+        forward_eager(h, x_own, y_own);
+        return;
+    }
+    if (h->fwd_graphs.size() > 32) drop_graphs(h);  // callers that never repeat a pointer pair
+    auto& g = h->fwd_graphs[{x_own, y_own}];
+    if (g.exec) {
+        CK(cudaGraphLaunch(g.exec, h->st));
+        h->launches += g.kernels;
+        return;
+    }
+    if (++g.seen < 2) {
+        forward_eager(h, x_own, y_own);
+        return;
+    }
+    const int64_t l0 = h->launches;
+    cudaGraph_t graph_obj = nullptr;
+    CK(cudaStreamBeginCapture(h->st, cudaStreamCaptureModeThreadLocal));
+    try {
+        forward_eager(h, x_own, y_own);
+    } catch (...) {
+        cudaStreamEndCapture(h->st, &graph_obj);
+        if (graph_obj) cudaGraphDestroy(graph_obj);
+        cudaGetLastError();
+        throw;
+    }
+    CK(cudaStreamEndCapture(h->st, &graph_obj));
+    g.kernels = h->launches - l0;
+    h->launches = l0;
+    const cudaError_t e = cudaGraphInstantiate(&g.exec, graph_obj, 0);
+    cudaGraphDestroy(graph_obj);
+    if (e != cudaSuccess) {
+        g.exec = nullptr;
+        throw std::runtime_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+    }
+    CK(cudaGraphLaunch(g.exec, h->st));
+    h->launches += g.kernels;
 }
 
 // Multi-mode block operator of the MATLAB application (aniso.m:121-156): K angular modes of n values,
@@ -1535,8 +1600,10 @@ struct HostPrec {
 using DevOp = std::function<void(const double*, double*)>;
 using DevPrec = std::function<void(double*)>;
 
+// Afix (optional): the same operator, applied by the pipelined Arnoldi to ONE fixed pair of buffers (every new basis vector is
+// also written to the input buffer), so that it can be a captured graph
 int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* x, int m, int max_iter, double tol, int* iters,
-               double* hist, int hist_cap, const DevPrec* P = nullptr) {
+               double* hist, int hist_cap, const DevPrec* P = nullptr, const DevOp* Afix = nullptr) {
     const int ldh = m + 1;
     GmresWork g{h, n, m, nullptr, nullptr, nullptr};
     // device scalars of a solve: projections h1 / h2 (m + 2 each), then the state of the device-side Givens recurrence
@@ -1544,7 +1611,7 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     {
         // one allocation, kept in the handle between solves (680 MB at C5, m = 80: cudaMalloc/cudaFree of that size cost
         // milliseconds, a visible share of a 25 ms solve)
-        const size_t need = (size_t)(m + 4) * n + (size_t)(m + 1) * h->dot.blocks + nscal;
+        const size_t need = (size_t)(m + 5) * n + (size_t)(m + 1) * h->dot.blocks + nscal;
         if (h->gm_cap < need) {
             dfree(h, h->gm_buf);
             h->gm_buf = nullptr;
@@ -1566,7 +1633,8 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     g.w = h->gm_buf;
     g.r = g.w + n;
     double* pb = g.r + n;  // M^-1 b of a preconditioned solve
-    g.V = pb + n;
+    double* gx = pb + n;   // fixed input buffer of the operator graph (pipelined form)
+    g.V = gx + n;
     double* md_partial = g.V + (size_t)(m + 1) * n;
     double* dh = md_partial + (size_t)(m + 1) * h->dot.blocks;  // h1: m + 2 entries
     double* h2 = dh + m + 2;
@@ -1657,15 +1725,16 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     };
     // everything of Arnoldi step i that the pipelined form queues without looking at results
     auto queue_step = [&](int i) {
-        A(g.v(i), g.w);
+        if (Afix) (*Afix)(gx, g.w);  // gx holds v_i
+        else A(g.v(i), g.w);
         orthogonalise_cgs2(i);
-        LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), 1, h->st));
+        LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), 1, h->st, Afix ? gx : nullptr));
         LAUNCH(h, launch_givens_step(i, dh, h2, dh + i + 1, dbeta, dH, ldh, dcs, dsn, ds, normb, tol, drep + 2 * i, h->st));
         CK(cudaMemcpyAsync(col + 2 * (i & 1), drep + 2 * i, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->st));
         CK(cudaEventRecord(h->gm_ev[i & 1], h->st));
     };
     while (!done && j <= max_iter) {
-        LAUNCH(h, launch_scale_inv_dev(n, dbeta, g.r, g.v(0), 0, h->st));
+        LAUNCH(h, launch_scale_inv_dev(n, dbeta, g.r, g.v(0), 0, h->st, pipelined && Afix ? gx : nullptr));
         std::fill(s.begin(), s.end(), 0.0);
         s[0] = beta;
         if (pipelined) {
@@ -1779,8 +1848,9 @@ int aniso_gmres_dev(aniso_t* h, const double* b, double* x, int m, int max_iter,
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede GMRES");
     ensure_ops(h, 0, PART_BOTH);
     ensure_stencils(h, 0);
-    return gmres_core(h, [h](const double* xx, double* yy) { forward_own(h, xx, yy); }, h->nown, b, x, m, max_iter, tol, iters,
-                      hist, hist_cap);
+    const DevOp Afix = [h](const double* xx, double* yy) { forward_own(h, xx, yy, true); };
+    return gmres_core(h, [h](const double* xx, double* yy) { forward_own(h, xx, yy, false); }, h->nown, b, x, m, max_iter, tol, iters,
+                      hist, hist_cap, nullptr, &Afix);
     API_END
 }
 
@@ -1802,8 +1872,9 @@ int aniso_gmres_prec(aniso_t* h, const double* b, double* x, int m, int max_iter
     to_slots(h, x, dx);
     HostPrec hp{h, prec, ctx, 1, {}, {}};
     const DevPrec P = [&hp](double* v) { hp(v); };
-    const int rc = gmres_core(h, [h](const double* xx, double* yy) { forward_own(h, xx, yy); }, h->nown, db + h->slot0,
-                              dx + h->slot0, m, max_iter, tol, iters, hist, hist_cap, prec ? &P : nullptr);
+    const DevOp Afix = [h](const double* xx, double* yy) { forward_own(h, xx, yy, true); };
+    const int rc = gmres_core(h, [h](const double* xx, double* yy) { forward_own(h, xx, yy, false); }, h->nown, db + h->slot0,
+                              dx + h->slot0, m, max_iter, tol, iters, hist, hist_cap, prec ? &P : nullptr, &Afix);
     from_slots(h, dx + h->slot0, x);
     return rc;
     API_END
@@ -1978,12 +2049,13 @@ int aniso_time_forward(aniso_t* h, int reps, double* ms) {
     ensure_ops(h, 0, PART_BOTH);
     ensure_stencils(h, 0);
     CK(cudaMemsetAsync(h->d_a, 0, sizeof(double) * h->plan.N, h->st));
-    forward_own(h, h->d_a + h->slot0, h->d_b);  // warm-up
+    forward_own(h, h->d_a + h->slot0, h->d_b, true);  // warm-up
+    forward_own(h, h->d_a + h->slot0, h->d_b, true);  // (captured)
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
     CK(cudaEventRecord(e0, h->st));
-    for (int i = 0; i < reps; ++i) forward_own(h, h->d_a + h->slot0, h->d_b);
+    for (int i = 0; i < reps; ++i) forward_own(h, h->d_a + h->slot0, h->d_b, true);
     CK(cudaEventRecord(e1, h->st));
     CK(cudaEventSynchronize(e1));
     float t = 0;

@@ -229,7 +229,9 @@ void launch_multi_axpy(int n, int nv, const double* h, const double* V, size_t l
 void launch_axpy_neg_dev(int n, const double* h, const double* v, double* w, cudaStream_t st);
 void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t st);
 // out = in * (1/ *norm), or 1/sqrt(*norm) when `squared` (norm holds w . w)
-void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, int squared, cudaStream_t st);
+// out2 (optional): a second copy of the result (the fixed input buffer of the captured operator graph)
+void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, int squared, cudaStream_t st,
+                          double* out2 = nullptr);
 void launch_sqrt1(double* v, cudaStream_t st);
 void launch_sub(int n, const double* a, const double* b, double* out, cudaStream_t st);  // out = a - b
 // scalar part of Arnoldi step i on the device (gmres.cpp:123-144): column i of H from the projections h1 (+ h2 for CGS2) and

@@ -618,7 +618,7 @@ void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
     std::vector<int> chunk(nn, 0);
     {
         const int nown = leaf_end - leaf_begin, deepest = p.treeMaxLevel;
-        bool ok = nown > 0 && nown % (kDeepChunks * 64) == 0 && leaf_begin % 64 == 0 && !getenv("ANISO_NO_CHUNKS");
+        bool ok = nown > 0 && nown % (kDeepChunks * 64) == 0 && leaf_begin % 64 == 0 && getenv("ANISO_DEEP_CHUNKS");  // opt-in: measured slower
         for (int k = leaf_begin; ok && k < leaf_end; ++k) ok = p.nodes[p.leaves[k]].level == deepest && p.leaves[k] == p.leaves[leaf_begin] + (k - leaf_begin);
         if (ok) {
             p.deep_chunks = kDeepChunks;

@@ -341,9 +341,19 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
 // ------------------------------------------------------------------------------------------------
 static bool smem_R(int r) { return (size_t)4 * r * r * sizeof(double) <= 36 * 1024; }  // r <= 33 (np <= 5)
 
+// opt-in above 48 KB of dynamic shared memory: once per kernel instantiation, device and size (never while a stream is
+// being captured into a graph: the first, uncaptured application of an operator has made the calls)
 template <class K>
 static void want_smem(K kernel, size_t bytes) {
-    if (bytes > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (bytes <= 48 * 1024) return;
+    static std::atomic<size_t> largest[64];  // per device: the attribute is per device
+    int d = 0;
+    cudaGetDevice(&d);
+    d &= 63;
+    if (bytes > largest[d].load()) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        largest[d].store(bytes);
+    }
 }
 
 SubtreePlan make_subtree_plan(int L0, int deepest, int r) {

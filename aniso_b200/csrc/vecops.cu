@@ -155,13 +155,17 @@ void launch_axpy(int n, double alpha, const double* x, double* y, cudaStream_t s
 }
 
 __global__ void scale_inv_dev_kernel(int n, const double* __restrict__ norm, const double* __restrict__ in, double* __restrict__ out,
-                                     int squared) {
+                                     double* __restrict__ out2, int squared) {
     const double s = 1.0 / (squared ? sqrt(*norm) : *norm);  // gmres.cpp:122 / 100: dscal(1.0 / h, v)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = in[i] * s;
+    if (i < n) {
+        const double v = in[i] * s;
+        out[i] = v;
+        if (out2) out2[i] = v;
+    }
 }
-void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, int squared, cudaStream_t st) {
-    if (n) scale_inv_dev_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, norm, in, out, squared);
+void launch_scale_inv_dev(int n, const double* norm, const double* in, double* out, int squared, cudaStream_t st, double* out2) {
+    if (n) scale_inv_dev_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, norm, in, out, out2, squared);
 }
 
 // block operator: the inputs of (kernel id, output mode) pairs are combinations of at most two scaled input modes
