@@ -242,7 +242,7 @@ void ensure_device(aniso_handle* h) {
     for (auto& e : h->ev_chunk) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
     h->pt.on = getenv("ANISO_PHASE_TIMES") != nullptr;
-    h->use_graphs = getenv("ANISO_NO_GRAPH") == nullptr && !h->pt.on;
+    h->use_graphs = getenv("ANISO_GRAPH") != nullptr && !h->pt.on;  // opt-in: measured slower than stream launches
     const HostPlan& p = h->plan;
     const int N = p.N, nn = (int)p.nodes.size(), r = p.rank;
     // geometry in slot order
@@ -1650,8 +1650,9 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     // launch and one all-reduce per pass instead of i+1 dependent ones).  ANISO_GMRES_ORTHO=mgs: the reference's MGS
     // (gmres.cpp:115-119); cgs2_unfused: the two-launch form
     const char* oenv = getenv("ANISO_GMRES_ORTHO");
-    const bool cgs2 = oenv ? std::string(oenv) == "cgs2" || std::string(oenv) == "cgs2_unfused" : true;
+    const bool cgs2 = oenv ? std::string(oenv) == "cgs2" || std::string(oenv) == "cgs2_unfused" || std::string(oenv) == "cgs2_3red" : true;
     const bool cgs_fused = !(oenv && std::string(oenv) == "cgs2_unfused");
+    const bool cgs_3red = oenv && std::string(oenv) == "cgs2_3red";  // the fused form with a third reduction for the norm
     double* col = h->pinned_small;
     std::vector<double> H((size_t)(m + 1) * m, 0.0), s(m + 1, 0.0), cs(m + 1, 0.0), sn(m + 1, 0.0);
     int rc = 1, j = 1, i = 0;
@@ -1704,6 +1705,18 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     }
     // the orthogonalisation of Arnoldi step i (w against v_0 .. v_i) with CGS2; leaves h1 in dh, h2 in h2, w . w in dh[i + 1]
     auto orthogonalise_cgs2 = [&](int i) {
+        if (cgs_fused && !cgs_3red && cgs_pass_ok(n, i + 1, g.V, (size_t)n, g.w)) {
+            // three fused passes, TWO reductions: h1; w -= V h1 with h2 AND |w|^2 of the new w in the same pass; w -= V h2,
+            // whose norm needs no pass of its own: |w - V h2|^2 = |w|^2 - |h2|^2 for the orthonormal basis and h2 = V^T w
+            // (h2 is the rounding-level correction of the second Gram-Schmidt sweep, so the identity holds to O(eps)).
+            // One all-reduce fewer per Arnoldi step on a sharded handle.
+            LAUNCH(h, launch_cgs_pass(0, n, i + 1, nullptr, g.V, (size_t)n, g.w, dh, md_partial, h->dot, h->st));
+            allreduce_scalars(h, dh, i + 1);
+            LAUNCH(h, launch_cgs_pass(3, n, i + 1, dh, g.V, (size_t)n, g.w, h2, md_partial, h->dot, h->st));
+            allreduce_scalars(h, h2, i + 2);
+            LAUNCH(h, launch_cgs_pass(4, n, i + 1, h2, g.V, (size_t)n, g.w, dh + i + 1, md_partial, h->dot, h->st));
+            return;
+        }
         if (cgs_fused && cgs_pass_ok(n, i + 1, g.V, (size_t)n, g.w)) {
             // three fused passes over the basis (vecops.cu cgs_pass_kernel): h1; w -= V h1 and h2; w -= V h2 and |w|^2
             LAUNCH(h, launch_cgs_pass(0, n, i + 1, nullptr, g.V, (size_t)n, g.w, dh, md_partial, h->dot, h->st));
@@ -2074,7 +2087,7 @@ const char* aniso_get_config(const aniso_t* h) {
     static const char* names[] = {"ANISO_GMRES_ORTHO", "ANISO_GMRES_SYNC", "ANISO_NO_SYM", "ANISO_NO_SUBTREE", "ANISO_NO_OVERLAP",
                                   "ANISO_CELL_WALK", "ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS", "ANISO_SYMG_NO_DMMA", "ANISO_NO_DMMA",
                                   "ANISO_BLOCK_LOOP", "ANISO_BLOCK_PER_ID", "ANISO_NO_SHARED_TAU", "ANISO_SUBTREE_D",
-                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_NO_GRAPH"};
+                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_GRAPH", "ANISO_DEEP_CHUNKS"};
     cfg = "aniso_b200 0.2 (sm_100a)";
     if (h) {
         cfg += "; ranks=" + std::to_string(h->nranks) + " sym=" + std::to_string(h->plan.m2l.symmetric ? 1 : 0) +

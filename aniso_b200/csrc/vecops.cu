@@ -378,7 +378,9 @@ __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, 
     extern __shared__ double cg_sm[];  // hs[nv] | wpart[nout][8]
     double* __restrict__ hs = cg_sm;
     double* __restrict__ wpart = cg_sm + nv;
-    const int nout = MODE == 2 ? 1 : nv;
+    // MODE 3: MODE 1 plus one more output, |w|^2 of the updated w (out[nv]); MODE 4: the update only, and
+    // out[0] = h_in[nv] - sum_k h_in[k]^2 = |w - V h|^2 for orthonormal V and h = V^T w (h_in[nv] = |w|^2 from MODE 3)
+    const int nout = MODE == 2 ? 1 : MODE == 3 ? nv + 1 : MODE == 4 ? 0 : nv;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (MODE)
         for (int k = threadIdx.x; k < nv; k += blockDim.x) hs[k] = h_in[k];
@@ -416,14 +418,15 @@ __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, 
             for (int u = 0; u < CGS_U; ++u)
                 if (ok[u]) w2[idx[u]] = a[u];
         }
-        if (MODE == 2) {
+        if (MODE == 2 || MODE == 3) {
             double s = 0;
 #pragma unroll
             for (int u = 0; u < CGS_U; ++u) s = fma(a[u].x, a[u].x, fma(a[u].y, a[u].y, s));
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (lane == 0) wpart[warp] += s;
-        } else {
+            if (lane == 0) wpart[(MODE == 3 ? nv * 8 : 0) + warp] += s;
+        }
+        if (MODE == 0 || MODE == 1 || MODE == 3) {
 #pragma unroll kCgsKU
             for (int k = 0; k < nv; ++k) {
                 const double2* __restrict__ Vk = reinterpret_cast<const double2*>(V + (size_t)k * ldv);
@@ -442,6 +445,14 @@ __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, 
                 if (lane == 0) wpart[k * 8 + warp] += s;
             }
         }
+    }
+    if (MODE == 4) {  // no reduction: the norm of the result follows from the values of the previous pass
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            double s = 0;
+            for (int k = 0; k < nv; ++k) s = fma(hs[k], hs[k], s);
+            out[0] = h_in[nv] - s;
+        }
+        return;
     }
     __syncthreads();
     for (int k = threadIdx.x; k < nout; k += blockDim.x) {
@@ -482,11 +493,13 @@ void launch_cgs_pass(int mode, int n, int nv, const double* h_in, const double* 
     const int npair = n >> 1;
     int nb = std::min(std::min(148 * CGS_CTAS, wk.blocks), (npair + 256 * CGS_U - 1) / (256 * CGS_U));  // one balanced wave of resident CTAs
     if (nb < 1) nb = 1;
-    const int nout = mode == 2 ? 1 : nv;
+    const int nout = mode == 2 ? 1 : mode == 3 ? nv + 1 : mode == 4 ? 0 : nv;
     const size_t smem = (size_t)(nv + 8 * nout) * sizeof(double);
     if (mode == 0) cgs_pass_kernel<0><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
     else if (mode == 1) cgs_pass_kernel<1><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
-    else cgs_pass_kernel<2><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
+    else if (mode == 2) cgs_pass_kernel<2><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
+    else if (mode == 3) cgs_pass_kernel<3><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
+    else cgs_pass_kernel<4><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
 }
 
 }  // namespace an

@@ -123,12 +123,13 @@ def test_gmres_vs_reference_golden(golden, name):
 
 @pytest.mark.parametrize("name", ["b8d3", "ml12d2"])
 def test_gmres_orthogonalisation_forms_agree(golden, name, monkeypatch):
-    """The Arnoldi orthogonalisation has three forms: classical Gram-Schmidt applied twice in three fused passes (default),
-    the same in two launches per pass, and the reference's modified Gram-Schmidt (gmres.cpp:115-119).  Same right-hand
+    """The Arnoldi orthogonalisation has four forms: classical Gram-Schmidt applied twice in three fused passes with two
+    reductions (default; the norm of the last pass from |w|^2 - |h2|^2), the same with a third reduction for the norm, the
+    two-launches-per-pass form, and the reference's modified Gram-Schmidt (gmres.cpp:115-119).  Same right-hand
     side: the reference's iteration count from each, residual histories and solutions equal to rounding."""
     g = golden(name)
     runs = {}
-    for form in ("cgs2", "cgs2_unfused", "mgs"):
+    for form in ("cgs2", "cgs2_3red", "cgs2_unfused", "mgs"):
         monkeypatch.setenv("ANISO_GMRES_ORTHO", form)
         a, x, y, w = make(name)
         a.cache(0)
@@ -138,7 +139,7 @@ def test_gmres_orthogonalisation_forms_agree(golden, name, monkeypatch):
     monkeypatch.delenv("ANISO_GMRES_ORTHO")
     xs, rc, it, hist = runs["cgs2"]
     assert rc == 0 and it == int(g["gm_iters"])
-    for form in ("cgs2_unfused", "mgs"):
+    for form in ("cgs2_3red", "cgs2_unfused", "mgs"):
         xo, rco, ito, histo = runs[form]
         assert rco == 0 and ito == it
         assert rel(xo, xs) < 1e-10
