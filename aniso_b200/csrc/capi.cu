@@ -17,6 +17,7 @@
 #include "../../include/aniso_b200.h"
 #include "device.cuh"
 #include "nccl_dyn.hpp"
+#include "peer.hpp"
 #include "plan.hpp"
 
 using namespace an;
@@ -120,6 +121,7 @@ struct aniso_handle {
     double* d_scal = nullptr;  // Hessenberg column / scalars on device
     NcclApi* nccl = nullptr;
     ncclComm_t comm = nullptr;
+    PeerComm peer;  // peer-memory collectives of the sharded matvec and of the GMRES reductions (peer.cu); NCCL otherwise
     unsigned char uid[128];
 };
 
@@ -408,6 +410,41 @@ void ensure_device(aniso_handle* h) {
         std::memcpy(&id, h->uid, 128);
         ncclResult_t rc = h->nccl->CommInitRank(&h->comm, h->nranks, id, h->rank);
         if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclCommInitRank: ") + h->nccl->GetErrorString(rc));
+        if (h->up_sharded && h->nranks <= kMaxPeers && !getenv("ANISO_NO_PEER")) {
+            // peer-memory collectives: one symmetric region per rank, mapped into every rank through CUDA IPC (the handles
+            // travel through an NCCL all-gather); every rank must succeed, else all fall back to NCCL
+            PeerComm& pc = h->peer;
+            pc.P = h->nranks;
+            pc.me = h->rank;
+            peer_layout(pc, (size_t)N, (size_t)T.pack_tot * r * h->nranks, 1024);
+            int ok = 1;
+            try {
+                peer_open(pc, [&](const void* mine, void* all, size_t bytes) {
+                    char* d = dalloc<char>(h, bytes * h->nranks);
+                    CK(cudaMemcpyAsync(d + bytes * h->rank, mine, bytes, cudaMemcpyHostToDevice, h->st));
+                    ncclResult_t e = h->nccl->AllGather(d + bytes * h->rank, d, bytes, ncclChar, h->comm, h->st);
+                    if (e != ncclSuccess) throw std::runtime_error(h->nccl->GetErrorString(e));
+                    CK(cudaMemcpyAsync(all, d, bytes * h->nranks, cudaMemcpyDeviceToHost, h->st));
+                    CK(cudaStreamSynchronize(h->st));
+                    dfree(h, d);
+                });
+            } catch (const std::exception& e) {
+                fprintf(stderr, "[aniso rank %d] peer-memory collectives unavailable (%s): using NCCL\n", h->rank, e.what());
+                cudaGetLastError();
+                ok = 0;
+            }
+            int* d_ok = dalloc<int>(h, 1);
+            CK(cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, h->st));
+            rc = h->nccl->AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, h->comm, h->st);
+            if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce: ") + h->nccl->GetErrorString(rc));
+            CK(cudaMemcpyAsync(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, h->st));
+            CK(cudaStreamSynchronize(h->st));
+            dfree(h, d_ok);
+            if (!ok) {
+                pc.ready = false;
+                peer_close(pc);
+            }
+        }
     }
     if (h->nranks > 1) {
         // host path of the sharded handle: padded staging vector for the in-place all-gather of uploaded pieces, and the
@@ -546,6 +583,14 @@ int aniso_destroy(aniso_t* h) {
             fprintf(stderr, "\n");
         }
         drop_graphs(h);
+        if (h->peer.local) {
+            // no rank may unmap or free its region while a peer can still store into it: a barrier first
+            if (h->comm && h->nccl && h->d_scal) {
+                h->nccl->AllReduce(h->d_scal, h->d_scal, 1, ncclDouble, ncclSum, h->comm, h->st);
+                cudaStreamSynchronize(h->st);
+            }
+            peer_close(h->peer);
+        }
         if (h->comm && h->nccl) h->nccl->CommDestroy(h->comm);
         for (void* p : h->allocs) cudaFree(p);
         if (h->pinned) cudaFreeHost(h->pinned);
@@ -793,6 +838,7 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     // streams that depend on little: P2P needs only q, the deepest-level M2L only the leaf multipoles from P2M.
     const int ng = h->m2l.groups, gd = h->overlap ? h->m2l_deep_g0 : ng;
     cudaStream_t sb = h->overlap ? h->st_bulk : h->st;
+    double* mch = h->d_mcharge;  // multipoles (the peer-memory exchange uses its own double-buffered arrays)
     if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
     // The launches of the latency chain are issued to `st` BEFORE the bulk stream's operator streams: a stream kernel fills
     // every SM, and sub-tree CTAs launched behind it would wait for its CTAs to retire (measured: upward pass 88 us instead of
@@ -807,21 +853,44 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
         const int N = p.N, s0 = h->slot0, n = h->nown;
         CK(cudaEventRecord(h->ev_fork, h->st));
         CK(cudaStreamWaitEvent(sb, h->ev_fork, 0));
-        allgather_slots(h, src->shard, h->d_xfull, sb);
+        PeerComm& pc = h->peer;
+        const bool peer = pc.ready && (n & 1) == 0 && (s0 & 1) == 0;
+        const double* xfull = h->d_xfull;
+        unsigned long long ex = 0, em = 0;
+        if (peer) {
+            // all-gather by push over peer memory: this rank's shard goes straight into the gathered vector of every rank
+            ex = ++pc.epoch_x;
+            em = ++pc.epoch_mc;
+            xfull = peer_x(pc, (int)(ex & 1));
+            mch = peer_mc(pc, (int)(em & 1));
+            const double* shard = src->shard;
+            if ((uintptr_t)shard & 15) {  // 16-byte stores need an aligned source: go through a local copy
+                CK(cudaMemcpyAsync(h->d_a + s0, shard, sizeof(double) * n, cudaMemcpyDeviceToDevice, sb));
+                shard = h->d_a + s0;
+            }
+            LAUNCH(h, peer_push(pc, 0, (int)(ex & 1), ex, shard, (size_t)s0, (size_t)n, sb));
+        } else
+            allgather_slots(h, src->shard, h->d_xfull, sb);
         LAUNCH(h, launch_scale(n, src->shard, src->sig_s ? src->sig_s + s0 : nullptr, h->G.pw + s0, h->G.perm + s0, h->d_f, h->d_q + s0, h->st));
         CK(cudaEventRecord(h->ev_own, h->st));
         phase_mark(h, "scale_own");
         q = h->d_q;
-        h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, nullptr, h->rank, h->nranks);
+        h->launches += launch_up_tree(T, h->G, h->sub, q, mch, h->st, nullptr, h->rank, h->nranks);
         phase_mark(h, "up_own");
-        LAUNCH(h, launch_scale(s0, h->d_xfull, src->sig_s, h->G.pw, h->G.perm, h->d_f, h->d_q, sb));
+        if (peer) LAUNCH(h, peer_wait(pc, 0, (int)(ex & 1), ex, sb));
+        LAUNCH(h, launch_scale(s0, xfull, src->sig_s, h->G.pw, h->G.perm, h->d_f, h->d_q, sb));
         const int e0 = s0 + n;
-        LAUNCH(h, launch_scale(N - e0, h->d_xfull + e0, src->sig_s ? src->sig_s + e0 : nullptr, h->G.pw + e0, h->G.perm + e0, h->d_f,
+        LAUNCH(h, launch_scale(N - e0, xfull + e0, src->sig_s ? src->sig_s + e0 : nullptr, h->G.pw + e0, h->G.perm + e0, h->d_f,
                                h->d_q + e0, sb));
         CK(cudaStreamWaitEvent(sb, h->ev_own, 0));  // P2P reads the whole of q
         phase_mark(h, "[b]x_gathered+scaled", sb);
         p2p_on_bulk();
-        allgather_multipoles(h);
+        if (peer) {
+            const size_t cnt = (size_t)T.pack_tot * T.r;
+            LAUNCH(h, peer_push(pc, 1, (int)(em & 1), em, mch + cnt * h->rank, cnt * h->rank, cnt, h->st));
+            LAUNCH(h, peer_wait(pc, 1, (int)(em & 1), em, h->st));
+        } else
+            allgather_multipoles(h);
         CK(cudaEventRecord(h->ev_leaf, h->st));
         phase_mark(h, "gather_multipoles");
     } else if (h->overlap) {
@@ -853,13 +922,13 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
             CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
             const int per = (ng - gd) / nch;
             for (int k = 0; k < nch && gd < ng; ++k) {
-                LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd + k * per, per), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, sb));
+                LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd + k * per, per), c.m2l, mch, h->d_mpot, c.sign, false, sb));
                 CK(cudaEventRecord(nch > 1 ? h->ev_chunk[k] : h->ev_join, sb));
             }
             if (gd >= ng) CK(cudaEventRecord(h->ev_join, sb));
             phase_mark(h, "[b]m2l_deep", sb);
         }
-        if (gd > 0) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, 0, gd), c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
+        if (gd > 0) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, 0, gd), c.m2l, mch, h->d_mpot, c.sign, false, h->st));
         phase_mark(h, "m2l_shallow");
         h->launches += launch_down_mid_tree(T, h->m2l, sym_m, h->sub, L0, h->d_mpot, h->st);
         phase_mark(h, "down_mid");
@@ -949,6 +1018,10 @@ void allgather_slots(aniso_handle* h, const double* shard, double* full) { allga
 
 void allreduce_scalars(aniso_handle* h, double* d, int n) {
     if (h->nranks == 1) return;
+    if (h->peer.ready && n <= h->peer.red_cap) {
+        peer_allreduce(h->peer, d, n, h->st);
+        return;
+    }
     ncclResult_t rc = h->nccl->AllReduce(d, d, n, ncclDouble, ncclSum, h->comm, h->st);
     if (rc != ncclSuccess) throw std::runtime_error(std::string("ncclAllReduce: ") + h->nccl->GetErrorString(rc));
 }
@@ -1330,6 +1403,10 @@ void ddot_dev(aniso_handle* h, int n, const double* a, const double* b, double* 
     allreduce_scalars(h, out, 1);
     if (take_sqrt) LAUNCH(h, launch_sqrt1(out, h->st));
 }
+void check_peer(aniso_handle* h) {  // a peer-memory wait that timed out leaves its mark in pinned host memory
+    if (h->peer.err && *h->peer.err) throw std::runtime_error("peer-memory exchange timed out (a rank is missing or out of step)");
+}
+
 double read_scalar(aniso_handle* h, const double* d) {
     double v;
     CK(cudaMemcpyAsync(&v, d, sizeof(double), cudaMemcpyDeviceToHost, h->st));
@@ -1839,6 +1916,7 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     }
     if (hist && *iters < hist_cap) hist[*iters] = resid;
     CK(cudaStreamSynchronize(h->st));
+    check_peer(h);
     if (gt_on) {
         const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - gt_t0).count();
         fprintf(stderr, "[aniso gmres] %d iterations: wall %.3f ms, operator %.3f ms, orthogonalisation %.3f ms (device, Arnoldi steps only)\n",
@@ -1989,6 +2067,7 @@ int aniso_synchronize(aniso_t* h) {
     API_BEGIN
     REQUIRE(h, "null handle");
     if (h->dev_ready) CK(cudaStreamSynchronize(h->st));
+    if (h->peer.err && *h->peer.err) throw std::runtime_error("peer-memory exchange timed out (a rank is missing or out of step)");
     return ANISO_OK;
     API_END
 }
@@ -2087,12 +2166,13 @@ const char* aniso_get_config(const aniso_t* h) {
     static const char* names[] = {"ANISO_GMRES_ORTHO", "ANISO_GMRES_SYNC", "ANISO_NO_SYM", "ANISO_NO_SUBTREE", "ANISO_NO_OVERLAP",
                                   "ANISO_CELL_WALK", "ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS", "ANISO_SYMG_NO_DMMA", "ANISO_NO_DMMA",
                                   "ANISO_BLOCK_LOOP", "ANISO_BLOCK_PER_ID", "ANISO_NO_SHARED_TAU", "ANISO_SUBTREE_D",
-                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_GRAPH", "ANISO_DEEP_CHUNKS"};
+                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_GRAPH", "ANISO_DEEP_CHUNKS", "ANISO_NO_PEER"};
     cfg = "aniso_b200 0.2 (sm_100a)";
     if (h) {
         cfg += "; ranks=" + std::to_string(h->nranks) + " sym=" + std::to_string(h->plan.m2l.symmetric ? 1 : 0) +
                " subtree=" + std::to_string(h->subtree_ok ? 1 : 0) + " overlap=" + std::to_string(h->overlap ? 1 : 0) +
-               " table_line_integral=" + std::to_string(h->S.ty ? 1 : 0);
+               " table_line_integral=" + std::to_string(h->S.ty ? 1 : 0) + " up_sharded=" + std::to_string(h->up_sharded ? 1 : 0) +
+               " peer_collectives=" + std::to_string(h->peer.ready ? 1 : 0);
     }
     const char* o = getenv("ANISO_GMRES_ORTHO");
     cfg += std::string("; gmres=") + (o ? o : "cgs2") + (getenv("ANISO_GMRES_SYNC") ? "/sync" : "/pipelined");
