@@ -105,6 +105,8 @@ struct aniso_handle {
     double* pinned_small = nullptr;  // Hessenberg column / step report read-back (2m + 8 doubles)
     size_t pinned_small_cap = 0;
     cudaEvent_t gm_ev[2] = {nullptr, nullptr};  // pipelined Arnoldi: report of step i has arrived
+    cudaStream_t st_aux = nullptr;              // scalar recurrence of the pipelined Arnoldi (Givens step + report copy)
+    cudaEvent_t ev_h = nullptr;                 // projections of the current step are complete
     double* pinned = nullptr;  // 2N doubles
     // sharded host path (nranks > 1): every rank moves 1/nranks of a host vector over PCIe, the rest travels over NVLink
     double* d_stage_pad = nullptr;     // nranks * stage_chunk doubles: in-place all-gather of the uploaded pieces
@@ -601,6 +603,8 @@ int aniso_destroy(aniso_t* h) {
         for (cudaEvent_t e : h->copy_ev) cudaEventDestroy(e);
         for (cudaEvent_t e : h->gm_ev)
             if (e) cudaEventDestroy(e);
+        if (h->ev_h) cudaEventDestroy(h->ev_h);
+        if (h->st_aux) cudaStreamDestroy(h->st_aux);
         for (cudaEvent_t e : h->ev_chunk)
             if (e) cudaEventDestroy(e);
         cudaStreamDestroy(h->st_bulk);
@@ -839,6 +843,8 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     const int ng = h->m2l.groups, gd = h->overlap ? h->m2l_deep_g0 : ng;
     cudaStream_t sb = h->overlap ? h->st_bulk : h->st;
     double* mch = h->d_mcharge;  // multipoles (the peer-memory exchange uses its own double-buffered arrays)
+    bool deep_gathered_on_bulk = false;  // peer exchange: the bulk stream itself has waited for the leaf multipoles
+    const bool m2l_deep_leaf_only = h->m2l_deep_g0 < h->m2l.groups;  // the deep rows exist and read leaf multipoles only
     if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
     // The launches of the latency chain are issued to `st` BEFORE the bulk stream's operator streams: a stream kernel fills
     // every SM, and sub-tree CTAs launched behind it would wait for its CTAs to retire (measured: upward pass 88 us instead of
@@ -875,7 +881,14 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
         CK(cudaEventRecord(h->ev_own, h->st));
         phase_mark(h, "scale_own");
         q = h->d_q;
-        h->launches += launch_up_tree(T, h->G, h->sub, q, mch, h->st, nullptr, h->rank, h->nranks);
+        // leaf level of this rank's part of the rank-major multipole array: its last cnt_leaf nodes
+        const size_t tot = (size_t)T.pack_tot * T.r, cnt_leaf = (((size_t)1 << (2 * deepest)) >> T.pack_logP) * T.r;
+        const size_t own0 = tot * h->rank, leaf0 = own0 + tot - cnt_leaf;
+        const std::function<void()> push_leaf = [&] {
+            // the deepest-level M2L rows only read leaf multipoles: they travel as soon as P2M has produced them
+            LAUNCH(h, peer_push(pc, 3, (int)(em & 1), em, mch + leaf0, leaf0, cnt_leaf, h->st));
+        };
+        h->launches += launch_up_tree(T, h->G, h->sub, q, mch, h->st, nullptr, h->rank, h->nranks, peer ? &push_leaf : nullptr);
         phase_mark(h, "up_own");
         if (peer) LAUNCH(h, peer_wait(pc, 0, (int)(ex & 1), ex, sb));
         LAUNCH(h, launch_scale(s0, xfull, src->sig_s, h->G.pw, h->G.perm, h->d_f, h->d_q, sb));
@@ -886,9 +899,11 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
         phase_mark(h, "[b]x_gathered+scaled", sb);
         p2p_on_bulk();
         if (peer) {
-            const size_t cnt = (size_t)T.pack_tot * T.r;
-            LAUNCH(h, peer_push(pc, 1, (int)(em & 1), em, mch + cnt * h->rank, cnt * h->rank, cnt, h->st));
-            LAUNCH(h, peer_wait(pc, 1, (int)(em & 1), em, h->st));
+            if (tot > cnt_leaf) LAUNCH(h, peer_push(pc, 1, (int)(em & 1), em, mch + own0, own0, tot - cnt_leaf, h->st));
+            LAUNCH(h, peer_wait(pc, 1, (int)(em & 1), em, h->st));   // levels above the leaves: the shallow M2L rows on `st`
+            LAUNCH(h, peer_wait(pc, 3, (int)(em & 1), em, sb));      // leaf level: the deepest M2L rows on `st_bulk`
+            deep_gathered_on_bulk = m2l_deep_leaf_only;
+            if (!deep_gathered_on_bulk) LAUNCH(h, peer_wait(pc, 3, (int)(em & 1), em, h->st));
         } else
             allgather_multipoles(h);
         CK(cudaEventRecord(h->ev_leaf, h->st));
@@ -919,7 +934,7 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
         // the HBM-bound stream of the next chunks; only the last chunk's leaf pass is exposed.
         const int nch = (h->overlap && gd < ng && p.deep_chunks > 1 && (ng - gd) % p.deep_chunks == 0) ? p.deep_chunks : 1;
         if (h->overlap) {
-            CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
+            if (!deep_gathered_on_bulk) CK(cudaStreamWaitEvent(sb, h->ev_leaf, 0));
             const int per = (ng - gd) / nch;
             for (int k = 0; k < nch && gd < ng; ++k) {
                 LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, gd + k * per, per), c.m2l, mch, h->d_mpot, c.sign, false, sb));
@@ -1684,7 +1699,7 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     const int ldh = m + 1;
     GmresWork g{h, n, m, nullptr, nullptr, nullptr};
     // device scalars of a solve: projections h1 / h2 (m + 2 each), then the state of the device-side Givens recurrence
-    const size_t nscal = (size_t)2 * (m + 2) + (size_t)ldh * m + (size_t)4 * (m + 1) + (size_t)2 * (m + 1) + 8;
+    const size_t nscal = (size_t)4 * (m + 2) + (size_t)ldh * m + (size_t)4 * (m + 1) + (size_t)2 * (m + 1) + 8;
     {
         // one allocation, kept in the handle between solves (680 MB at C5, m = 80: cudaMalloc/cudaFree of that size cost
         // milliseconds, a visible share of a 25 ms solve)
@@ -1706,6 +1721,8 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
         }
         for (auto& e : h->gm_ev)
             if (!e) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        if (!h->ev_h) CK(cudaEventCreateWithFlags(&h->ev_h, cudaEventDisableTiming));
+        if (!h->st_aux) CK(cudaStreamCreateWithFlags(&h->st_aux, cudaStreamNonBlocking));
     }
     g.w = h->gm_buf;
     g.r = g.w + n;
@@ -1715,7 +1732,9 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     double* md_partial = g.V + (size_t)(m + 1) * n;
     double* dh = md_partial + (size_t)(m + 1) * h->dot.blocks;  // h1: m + 2 entries
     double* h2 = dh + m + 2;
-    double* dH = h2 + m + 2;                 // (m + 1) x m, column-major: the rotated Hessenberg matrix (device Givens)
+    double* dh_b = h2 + m + 2;               // second set of projections: the pipelined form alternates by step parity, so that
+    double* h2_b = dh_b + m + 2;             //   the scalar recurrence of step i (on st_aux) can still read while step i + 1 writes
+    double* dH = h2_b + m + 2;               // (m + 1) x m, column-major: the rotated Hessenberg matrix (device Givens)
     double* dcs = dH + (size_t)ldh * m;
     double* dsn = dcs + m + 1;
     double* ds = dsn + m + 1;
@@ -1750,7 +1769,7 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     // alike, since all ranks see the same all-reduced scalars - and its results are discarded.  The synchronous form (read the
     // column back, rotate on the host like gmres.cpp:123-144) remains for MGS, the two-launch CGS2, a host preconditioner,
     // the timers and ANISO_GMRES_SYNC=1.
-    const bool pipelined = cgs2 && cgs_fused && !P && !gt_on && !getenv("ANISO_GMRES_SYNC") && cgs_pass_ok(n, 1, g.V, (size_t)n, g.w);
+    const bool pipelined = cgs2 && cgs_fused && !cgs_3red && !P && !gt_on && !getenv("ANISO_GMRES_SYNC") && cgs_pass_ok(n, 1, g.V, (size_t)n, g.w);
     const double* bb = b;  // right-hand side of the iteration: b or M^-1 b
     if (P) {
         CK(cudaMemcpyAsync(pb, b, sizeof(double) * n, cudaMemcpyDeviceToDevice, h->st));
@@ -1813,15 +1832,31 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
         }
         allreduce_scalars(h, dh + i + 1, 1);
     };
-    // everything of Arnoldi step i that the pipelined form queues without looking at results
+    // Everything of Arnoldi step i that the pipelined form queues without looking at results: the operator, then CGS2 in
+    // three passes over the basis with two reductions - h1; w' = w - V h1 with h2 = V^T w' and |w'|^2; v_{i+1} = (w' - V h2) /
+    // sqrt(|w'|^2 - |h2|^2) written straight to the basis (and to the operator's input buffer).  On a sharded handle the two
+    // reductions are completed across the ranks inside the pass kernels (peer memory).  The scalar recurrence (Hessenberg
+    // column, rotations, residual) only needs h1 and h2: it runs on st_aux beside the last pass and the next operator.
     auto queue_step = [&](int i) {
+        double* h1s = (i & 1) ? dh_b : dh;
+        double* h2s = (i & 1) ? h2_b : h2;
         if (Afix) (*Afix)(gx, g.w);  // gx holds v_i
         else A(g.v(i), g.w);
-        orthogonalise_cgs2(i);
-        LAUNCH(h, launch_scale_inv_dev(n, dh + i + 1, g.w, g.v(i + 1), 1, h->st, Afix ? gx : nullptr));
-        LAUNCH(h, launch_givens_step(i, dh, h2, dh + i + 1, dbeta, dH, ldh, dcs, dsn, ds, normb, tol, drep + 2 * i, h->st));
-        CK(cudaMemcpyAsync(col + 2 * (i & 1), drep + 2 * i, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->st));
-        CK(cudaEventRecord(h->gm_ev[i & 1], h->st));
+        const bool fused_red = h->peer.ready && i + 2 <= h->peer.red_cap;
+        PeerRed pr;
+        if (fused_red) peer_red_args(h->peer, pr);
+        LAUNCH(h, launch_cgs_pass(0, n, i + 1, nullptr, g.V, (size_t)n, g.w, h1s, md_partial, h->dot, h->st, fused_red ? &pr : nullptr));
+        if (!fused_red) allreduce_scalars(h, h1s, i + 1);
+        if (fused_red) peer_red_args(h->peer, pr);
+        LAUNCH(h, launch_cgs_pass(3, n, i + 1, h1s, g.V, (size_t)n, g.w, h2s, md_partial, h->dot, h->st, fused_red ? &pr : nullptr));
+        if (!fused_red) allreduce_scalars(h, h2s, i + 2);
+        CK(cudaEventRecord(h->ev_h, h->st));
+        LAUNCH(h, launch_cgs_pass(4, n, i + 1, h2s, g.V, (size_t)n, g.w, h1s + i + 1, md_partial, h->dot, h->st, nullptr, g.v(i + 1),
+                                  Afix ? gx : nullptr));
+        CK(cudaStreamWaitEvent(h->st_aux, h->ev_h, 0));
+        LAUNCH(h, launch_givens_step(i, h1s, h2s, nullptr, dbeta, dH, ldh, dcs, dsn, ds, normb, tol, drep + 2 * i, h->st_aux));
+        CK(cudaMemcpyAsync(col + 2 * (i & 1), drep + 2 * i, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->st_aux));
+        CK(cudaEventRecord(h->gm_ev[i & 1], h->st_aux));
     };
     while (!done && j <= max_iter) {
         LAUNCH(h, launch_scale_inv_dev(n, dbeta, g.r, g.v(0), 0, h->st, pipelined && Afix ? gx : nullptr));

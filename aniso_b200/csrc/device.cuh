@@ -4,6 +4,7 @@
 
 #include <atomic>
 #include <cstdint>
+#include <functional>
 
 namespace an {
 
@@ -167,8 +168,9 @@ SubtreePlan make_subtree_plan(int first_m2l_level, int deepest, int r);
 // P2M + M2M of every level down to first_m2l_level; leaf_done (optional) is recorded once the leaf multipoles exist.
 // part / nparts: only the sub-trees of share `part` out of `nparts` equal Morton ranges (sharded upward pass; nparts must
 // divide the number of sub-tree roots of every chunk, i.e. 4^first_m2l_level).  Return value: kernels launched.
+// after_leaf (optional): called once the leaf-level kernel has been launched (e.g. to push the leaf multipoles to the peers)
 int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
-                   cudaEvent_t leaf_done, int part = 0, int nparts = 1);
+                   cudaEvent_t leaf_done, int part = 0, int nparts = 1, const std::function<void()>* after_leaf = nullptr);
 // fl != nullptr: multi-term folds (block operator; needs fold == fold_p2p == true); C / f_ref / pot are then unused
 int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const SubtreePlan& sp, int L0, double* mpot, cudaStream_t st,
                          const FoldList* fl = nullptr);
@@ -221,8 +223,22 @@ void launch_axpy_dot(int n, const double* h, const double* v, double* w, const d
 void launch_multi_dot(int n, int nv, const double* w, const double* V, size_t ldv, double* out, double* partial, DotWork& wk,
                       cudaStream_t st);
 bool cgs_pass_ok(int n, int nv, const double* V, size_t ldv, const double* w);
+// Small all-reduce over peer memory (peer.cu) fused into the epilogue of a reduction kernel: the block that holds the final
+// sums pushes them to a slot of its own on every rank, waits for the slots of all ranks and adds them in rank order.
+// P == 0: no exchange.  Filled by peer_red_args().
+struct PeerRed {
+    int P = 0, me = 0, cap = 0;
+    double* red[16];
+    unsigned long long* flags[16];
+    const double* my_red = nullptr;
+    const unsigned long long* my_flags = nullptr;
+    unsigned long long epoch = 0;
+    int* err = nullptr;
+};
+// pr (optional, modes 0 - 3): the outputs are all-reduced over the ranks inside the kernel.  Mode 4 with vnext: the updated
+// vector is not written back to w but, scaled to unit length (its norm follows from h_in), to vnext (and vnext2).
 void launch_cgs_pass(int mode, int n, int nv, const double* h_in, const double* V, size_t ldv, double* w, double* out, double* partial,
-                     DotWork& wk, cudaStream_t st);
+                     DotWork& wk, cudaStream_t st, const PeerRed* pr = nullptr, double* vnext = nullptr, double* vnext2 = nullptr);
 void launch_multi_axpy(int n, int nv, const double* h, const double* V, size_t ldv, double* w, double* norm2_out, double* partial,
                        DotWork& wk, cudaStream_t st);
 // w -= h[0] * v  (h read from device memory)
@@ -237,6 +253,7 @@ void launch_sub(int n, const double* a, const double* b, double* out, cudaStream
 // scalar part of Arnoldi step i on the device (gmres.cpp:123-144): column i of H from the projections h1 (+ h2 for CGS2) and
 // norm2 = w . w, previous rotations applied, new rotation generated, s updated; report[0] = |s(i+1)| / normb,
 // report[1] = 1 when that is below tol.  beta is read at i == 0.
+// norm2 == nullptr: w . w = h2[i + 1] - sum_k h2[k]^2 (the two-reduction form of CGS2)
 void launch_givens_step(int i, const double* h1, const double* h2, const double* norm2, const double* beta, double* H, int ldh,
                         double* cs, double* sn, double* s, double normb, double tol, double* report, cudaStream_t st);
 // yneg = -(H(0:k,0:k)^-1 s(0:k)) (Update, gmres.cpp:12-24)

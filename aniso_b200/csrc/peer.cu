@@ -19,33 +19,11 @@
 
 #include "device.cuh"
 #include "peer.hpp"
+#include "peer_dev.cuh"
 
 namespace an {
 
 namespace {
-
-__device__ __forceinline__ unsigned long long ld_flag(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_flag(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-// waits until flags[0..P) >= epoch; ~2 s time-out at 1.9 GHz
-__device__ __forceinline__ bool wait_all(const unsigned long long* flags, int P, unsigned long long epoch, int* err) {
-    const long long t0 = clock64();
-    for (int r = 0; r < P; ++r) {
-        while (ld_flag(flags + r) < epoch) {
-            if (clock64() - t0 > 4000000000ll) {
-                *err = 1;
-                return false;
-            }
-        }
-    }
-    return true;
-}
 
 // All-gather by push: src (n doubles, n even, 16-byte aligned) -> dst[r] + 0..n on every rank r (dst[r] already points at
 // this rank's place in rank r's buffer).  The last block to finish raises this rank's flag on every rank.
@@ -65,35 +43,18 @@ __global__ void __launch_bounds__(256) peer_push_kernel(const double* __restrict
     __syncthreads();
     if (!last) return;
     __threadfence_system();
-    if (threadIdx.x < P) st_flag(flags.p[threadIdx.x] + me, epoch);
+    if (threadIdx.x < P) peer_st_flag(flags.p[threadIdx.x] + me, epoch);
     if (threadIdx.x == 0) *counter = 0;
 }
 
 __global__ void peer_wait_kernel(const unsigned long long* __restrict__ flags, int P, unsigned long long epoch, int* __restrict__ err) {
-    if (threadIdx.x == 0) wait_all(flags, P, epoch, err);
+    if (threadIdx.x == 0) peer_wait_all(flags, P, epoch, err);
 }
 
-// Small all-reduce (sum) of vals[0..n): push to slot `me` of every rank, wait for all slots, add in rank order.
-// One block; red[r] = base of rank r's slot array (P slots of `cap` doubles), flags as above.
-__global__ void __launch_bounds__(256) peer_allreduce_kernel(double* __restrict__ vals, int n, int cap, PeerPtrs red, PeerFlags flags,
-                                                             const double* __restrict__ my_red, const unsigned long long* __restrict__ my_flags,
-                                                             int P, int me, unsigned long long epoch, int* __restrict__ err) {
-    for (int k = threadIdx.x; k < n; k += blockDim.x) {
-        const double v = vals[k];
-        for (int r = 0; r < P; ++r) red.p[r][(size_t)me * cap + k] = v;
-    }
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x < P) st_flag(flags.p[threadIdx.x] + me, epoch);
-    __shared__ bool ok;
-    if (threadIdx.x == 0) ok = wait_all(my_flags, P, epoch, err);
-    __syncthreads();
-    if (!ok) return;
-    for (int k = threadIdx.x; k < n; k += blockDim.x) {
-        double s = 0;
-        for (int r = 0; r < P; ++r) s += __ldcg(my_red + (size_t)r * cap + k);
-        vals[k] = s;
-    }
+// Small all-reduce (sum) of vals[0..n) as a kernel of its own (one block); the reduction kernels of the GMRES passes carry the
+// same exchange in their epilogue (PeerRed in device.cuh).
+__global__ void __launch_bounds__(256) peer_allreduce_kernel(double* __restrict__ vals, int n, const __grid_constant__ PeerRed pr) {
+    peer_allreduce_block(vals, n, pr);
 }
 
 }  // namespace
@@ -106,7 +67,7 @@ __global__ void __launch_bounds__(256) peer_allreduce_kernel(double* __restrict_
     } while (0)
 
 // Layout of the symmetric region (the same on every rank), in bytes from its base:
-//   flags   3 kinds x 2 parities x kMaxPeers u64        (written by the peers)
+//   flags   4 kinds (source, multipoles, small reductions, leaf-level multipoles) x 2 parities x kMaxPeers u64   (written by the peers)
 //   red     2 parities x P slots x red_cap doubles
 //   x       2 parities x nx doubles                     gathered source vector (slot order)
 //   mc      2 parities x nmc doubles                    gathered multipoles (rank-major, see DevTree::pack_*)
@@ -116,7 +77,7 @@ void peer_layout(PeerComm& pc, size_t nx, size_t nmc, int red_cap) {
     pc.red_cap = red_cap;
     size_t off = 0;
     pc.off_flags = off;
-    off += sizeof(unsigned long long) * 3 * 2 * kMaxPeers;
+    off += sizeof(unsigned long long) * 4 * 2 * kMaxPeers;
     off = (off + 255) & ~size_t(255);
     pc.off_red = off;
     off += sizeof(double) * 2 * pc.P * red_cap;
@@ -133,8 +94,8 @@ void peer_layout(PeerComm& pc, size_t nx, size_t nmc, int red_cap) {
 void peer_open(PeerComm& pc, const std::function<void(const void*, void*, size_t)>& exchange) {
     PCK(cudaMalloc(&pc.local, pc.bytes));
     PCK(cudaMemset(pc.local, 0, pc.bytes));
-    PCK(cudaMalloc(&pc.counter, sizeof(unsigned int)));
-    PCK(cudaMemset(pc.counter, 0, sizeof(unsigned int)));
+    PCK(cudaMalloc(&pc.counter, 4 * sizeof(unsigned int)));  // one per kind: pushes of different kinds run on different streams
+    PCK(cudaMemset(pc.counter, 0, 4 * sizeof(unsigned int)));
     PCK(cudaHostAlloc(&pc.err, sizeof(int), cudaHostAllocMapped));
     *pc.err = 0;
     PCK(cudaHostGetDevicePointer(&pc.err_dev, pc.err, 0));
@@ -180,10 +141,10 @@ double* peer_mc(const PeerComm& pc, int par) { return reinterpret_cast<double*>(
 // skipped by pointing the local destination at itself - the store is idempotent.
 void peer_push(PeerComm& pc, int kind, int par, unsigned long long epoch, const double* src, size_t own_off, size_t n, cudaStream_t st) {
     PeerPtrs d;
-    const size_t base = kind == 0 ? pc.off_x + sizeof(double) * par * pc.nx : pc.off_mc + sizeof(double) * par * pc.nmc;
+    const size_t base = kind == 0 ? pc.off_x + sizeof(double) * par * pc.nx : pc.off_mc + sizeof(double) * par * pc.nmc;  // kinds 1, 3: multipoles
     for (int r = 0; r < pc.P; ++r) d.p[r] = reinterpret_cast<double*>(pc.remote[r] + base) + own_off;
     const int blocks = (int)std::min<size_t>(296, std::max<size_t>(1, (n / 2 + 255) / 256));
-    peer_push_kernel<<<blocks, 256, 0, st>>>(src, n, d, flag_ptrs(pc, kind, par), pc.P, pc.me, epoch, pc.counter);
+    peer_push_kernel<<<blocks, 256, 0, st>>>(src, n, d, flag_ptrs(pc, kind, par), pc.P, pc.me, epoch, pc.counter + kind);
 }
 
 void peer_wait(PeerComm& pc, int kind, int par, unsigned long long epoch, cudaStream_t st) {
@@ -191,15 +152,29 @@ void peer_wait(PeerComm& pc, int kind, int par, unsigned long long epoch, cudaSt
     peer_wait_kernel<<<1, 32, 0, st>>>(f, pc.P, epoch, pc.err_dev);
 }
 
-void peer_allreduce(PeerComm& pc, double* vals, int n, cudaStream_t st) {
-    if (n > pc.red_cap) throw std::runtime_error("peer_allreduce: too many values");
+// arguments of the next small all-reduce (advances the epoch: call once per exchange, on every rank alike)
+void peer_red_args(PeerComm& pc, PeerRed& pr) {
     const unsigned long long epoch = ++pc.epoch_red;
     const int par = (int)(epoch & 1);
-    PeerPtrs red;
-    for (int r = 0; r < pc.P; ++r) red.p[r] = reinterpret_cast<double*>(pc.remote[r] + pc.off_red) + (size_t)par * pc.P * pc.red_cap;
-    const double* my_red = reinterpret_cast<const double*>(pc.local + pc.off_red) + (size_t)par * pc.P * pc.red_cap;
-    const unsigned long long* my_flags = reinterpret_cast<const unsigned long long*>(pc.local + pc.off_flags) + ((size_t)2 * 2 + par) * kMaxPeers;
-    peer_allreduce_kernel<<<1, 256, 0, st>>>(vals, n, pc.red_cap, red, flag_ptrs(pc, 2, par), my_red, my_flags, pc.P, pc.me, epoch, pc.err_dev);
+    pr.P = pc.P;
+    pr.me = pc.me;
+    pr.cap = pc.red_cap;
+    const PeerFlags f = flag_ptrs(pc, 2, par);
+    for (int r = 0; r < pc.P; ++r) {
+        pr.red[r] = reinterpret_cast<double*>(pc.remote[r] + pc.off_red) + (size_t)par * pc.P * pc.red_cap;
+        pr.flags[r] = f.p[r];
+    }
+    pr.my_red = reinterpret_cast<const double*>(pc.local + pc.off_red) + (size_t)par * pc.P * pc.red_cap;
+    pr.my_flags = reinterpret_cast<const unsigned long long*>(pc.local + pc.off_flags) + ((size_t)2 * 2 + par) * kMaxPeers;
+    pr.epoch = epoch;
+    pr.err = pc.err_dev;
+}
+
+void peer_allreduce(PeerComm& pc, double* vals, int n, cudaStream_t st) {
+    if (n > pc.red_cap) throw std::runtime_error("peer_allreduce: too many values");
+    PeerRed pr;
+    peer_red_args(pc, pr);
+    peer_allreduce_kernel<<<1, 256, 0, st>>>(vals, n, pr);
 }
 
 }  // namespace an

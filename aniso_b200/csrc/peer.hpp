@@ -38,5 +38,7 @@ double* peer_mc(const PeerComm& pc, int par);
 void peer_push(PeerComm& pc, int kind, int par, unsigned long long epoch, const double* src, size_t own_off, size_t n, cudaStream_t st);
 void peer_wait(PeerComm& pc, int kind, int par, unsigned long long epoch, cudaStream_t st);
 void peer_allreduce(PeerComm& pc, double* vals, int n, cudaStream_t st);
+struct PeerRed;
+void peer_red_args(PeerComm& pc, PeerRed& pr);
 
 }  // namespace an

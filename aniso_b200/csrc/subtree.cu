@@ -17,6 +17,7 @@
 // contiguous slot range.
 #include <algorithm>
 #include <cstdlib>
+#include <functional>
 
 #include "device.cuh"
 #include "passes_inl.cuh"
@@ -395,7 +396,7 @@ static void up_leaf_launch(const DevTree& T, const DevGeom& G, const SubtreePlan
 }
 
 int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, const double* q, double* mcharge, cudaStream_t st,
-                   cudaEvent_t leaf_done, int part, int nparts) {
+                   cudaEvent_t leaf_done, int part, int nparts, const std::function<void()>* after_leaf) {
     switch (T.np) {
         case 4: up_leaf_launch<4>(T, G, sp, q, mcharge, st, part, nparts); break;
         case 6: up_leaf_launch<6>(T, G, sp, q, mcharge, st, part, nparts); break;
@@ -403,6 +404,7 @@ int launch_up_tree(const DevTree& T, const DevGeom& G, const SubtreePlan& sp, co
         default: up_leaf_launch<0>(T, G, sp, q, mcharge, st, part, nparts);
     }
     if (leaf_done) cudaEventRecord(leaf_done, st);
+    if (after_leaf) (*after_leaf)();
     const int r = T.r;
     const bool sr = smem_R(r);
     for (int c = 0; c < sp.nmid; ++c) {

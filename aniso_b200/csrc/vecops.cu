@@ -6,6 +6,7 @@
 #include <algorithm>
 
 #include "device.cuh"
+#include "peer_dev.cuh"
 
 namespace an {
 
@@ -211,7 +212,14 @@ __global__ void givens_step_kernel(int i, const double* __restrict__ h1, const d
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     double* __restrict__ col = H + (size_t)i * ldh;
     for (int k = 0; k <= i; ++k) col[k] = h2 ? __dadd_rn(h1[k], h2[k]) : h1[k];  // CGS2: H(:, i) = h1 + h2
-    col[i + 1] = sqrt(*norm2);
+    double n2;
+    if (norm2) n2 = *norm2;
+    else {  // two-reduction CGS2: w . w = |w'|^2 - |h2|^2, formed exactly as the last pass forms it
+        double q = 0;
+        for (int k = 0; k <= i; ++k) q = fma(h2[k], h2[k], q);
+        n2 = h2[i + 1] - q;
+    }
+    col[i + 1] = sqrt(n2);
     if (i == 0) s[0] = *beta;
     s[i + 1] = 0.0;
     for (int k = 0; k < i; ++k) dev_apply_rotation(col[k], col[k + 1], cs[k], sn[k]);
@@ -374,7 +382,9 @@ static constexpr int kCgsKU = CGS_KU;
 template <int MODE>
 __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, const double* __restrict__ h_in, const double* __restrict__ V,
                                                           size_t ldv, double* __restrict__ w, double* __restrict__ partial,
-                                                          double* __restrict__ out, unsigned int* __restrict__ counter) {
+                                                          double* __restrict__ out, unsigned int* __restrict__ counter,
+                                                          const __grid_constant__ PeerRed pr, double* __restrict__ vnext,
+                                                          double* __restrict__ vnext2) {
     extern __shared__ double cg_sm[];  // hs[nv] | wpart[nout][8]
     double* __restrict__ hs = cg_sm;
     double* __restrict__ wpart = cg_sm + nv;
@@ -386,6 +396,13 @@ __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, 
         for (int k = threadIdx.x; k < nv; k += blockDim.x) hs[k] = h_in[k];
     for (int k = threadIdx.x; k < nout * 8; k += blockDim.x) wpart[k] = 0.0;
     __syncthreads();
+    double nrm2 = 0, inv = 1.0;
+    if (MODE == 4) {  // |w - V h|^2 = |w|^2 - |h|^2 (see above); every thread forms it alike
+        double s = 0;
+        for (int k = 0; k < nv; ++k) s = fma(hs[k], hs[k], s);
+        nrm2 = h_in[nv] - s;
+        inv = 1.0 / sqrt(nrm2);  // gmres.cpp:122: dscal(1.0 / h, v)
+    }
     const int npair = n >> 1;
     const int per = (npair + gridDim.x - 1) / gridDim.x;
     const int p0 = blockIdx.x * per, p1 = min(npair, p0 + per);
@@ -414,9 +431,19 @@ __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, 
                     a[u].y = fma(hk, v[u].y, a[u].y);
                 }
             }
+            if (MODE == 4 && vnext) {  // the next basis vector, already normalised; w itself is not needed again
 #pragma unroll
-            for (int u = 0; u < CGS_U; ++u)
-                if (ok[u]) w2[idx[u]] = a[u];
+                for (int u = 0; u < CGS_U; ++u)
+                    if (ok[u]) {
+                        const double2 v = make_double2(a[u].x * inv, a[u].y * inv);
+                        reinterpret_cast<double2*>(vnext)[idx[u]] = v;
+                        if (vnext2) reinterpret_cast<double2*>(vnext2)[idx[u]] = v;
+                    }
+            } else {
+#pragma unroll
+                for (int u = 0; u < CGS_U; ++u)
+                    if (ok[u]) w2[idx[u]] = a[u];
+            }
         }
         if (MODE == 2 || MODE == 3) {
             double s = 0;
@@ -447,11 +474,7 @@ __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, 
         }
     }
     if (MODE == 4) {  // no reduction: the norm of the result follows from the values of the previous pass
-        if (blockIdx.x == 0 && threadIdx.x == 0) {
-            double s = 0;
-            for (int k = 0; k < nv; ++k) s = fma(hs[k], hs[k], s);
-            out[0] = h_in[nv] - s;
-        }
+        if (blockIdx.x == 0 && threadIdx.x == 0) out[0] = nrm2;
         return;
     }
     __syncthreads();
@@ -483,23 +506,29 @@ __global__ void __launch_bounds__(256, CGS_CTAS) cgs_pass_kernel(int n, int nv, 
         if (lane == 0) out[k] = s;
     }
     if (threadIdx.x == 0) *counter = 0;
+    if (pr.P) {  // sums over the ranks, inside the same launch
+        __syncthreads();
+        peer_allreduce_block(out, nout, pr);
+    }
 }
 
 bool cgs_pass_ok(int n, int nv, const double* V, size_t ldv, const double* w) {
     return n >= 2 && (n & 1) == 0 && (ldv & 1) == 0 && nv <= 512 && ((uintptr_t)V & 15) == 0 && ((uintptr_t)w & 15) == 0;
 }
 void launch_cgs_pass(int mode, int n, int nv, const double* h_in, const double* V, size_t ldv, double* w, double* out, double* partial,
-                     DotWork& wk, cudaStream_t st) {
+                     DotWork& wk, cudaStream_t st, const PeerRed* prp, double* vnext, double* vnext2) {
+    static const PeerRed none = PeerRed();
+    const PeerRed& pr = prp ? *prp : none;
     const int npair = n >> 1;
     int nb = std::min(std::min(148 * CGS_CTAS, wk.blocks), (npair + 256 * CGS_U - 1) / (256 * CGS_U));  // one balanced wave of resident CTAs
     if (nb < 1) nb = 1;
     const int nout = mode == 2 ? 1 : mode == 3 ? nv + 1 : mode == 4 ? 0 : nv;
     const size_t smem = (size_t)(nv + 8 * nout) * sizeof(double);
-    if (mode == 0) cgs_pass_kernel<0><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
-    else if (mode == 1) cgs_pass_kernel<1><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
-    else if (mode == 2) cgs_pass_kernel<2><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
-    else if (mode == 3) cgs_pass_kernel<3><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
-    else cgs_pass_kernel<4><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter);
+    if (mode == 0) cgs_pass_kernel<0><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter, pr, vnext, vnext2);
+    else if (mode == 1) cgs_pass_kernel<1><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter, pr, vnext, vnext2);
+    else if (mode == 2) cgs_pass_kernel<2><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter, pr, vnext, vnext2);
+    else if (mode == 3) cgs_pass_kernel<3><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter, pr, vnext, vnext2);
+    else cgs_pass_kernel<4><<<nb, 256, smem, st>>>(n, nv, h_in, V, ldv, w, partial, out, wk.counter, pr, vnext, vnext2);
 }
 
 }  // namespace an
