@@ -899,8 +899,10 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
         phase_mark(h, "[b]x_gathered+scaled", sb);
         p2p_on_bulk();
         if (peer) {
-            if (tot > cnt_leaf) LAUNCH(h, peer_push(pc, 1, (int)(em & 1), em, mch + own0, own0, tot - cnt_leaf, h->st));
-            LAUNCH(h, peer_wait(pc, 1, (int)(em & 1), em, h->st));   // levels above the leaves: the shallow M2L rows on `st`
+            if (tot > cnt_leaf) {  // levels above the leaves (none when the first level with M2L lists is the leaf level)
+                LAUNCH(h, peer_push(pc, 1, (int)(em & 1), em, mch + own0, own0, tot - cnt_leaf, h->st));
+                LAUNCH(h, peer_wait(pc, 1, (int)(em & 1), em, h->st));  // the shallow M2L rows on `st` read them
+            }
             LAUNCH(h, peer_wait(pc, 3, (int)(em & 1), em, sb));      // leaf level: the deepest M2L rows on `st_bulk`
             deep_gathered_on_bulk = m2l_deep_leaf_only;
             if (!deep_gathered_on_bulk) LAUNCH(h, peer_wait(pc, 3, (int)(em & 1), em, h->st));
