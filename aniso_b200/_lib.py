@@ -65,6 +65,7 @@ SIGNATURES = {
     "aniso_block_gmres": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
     "aniso_block_gmres_dev": (C.c_int, [_H, _V, _V, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
     "aniso_line_integral": (C.c_int, [_H, C.c_int, _dp, _dp]),
+    "aniso_line_integral_noalloc": (C.c_int, [_H, C.c_int, _dp, _dp]),
     "aniso_kernel_eval": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, _dp, _dp]),
     "aniso_stream": (C.c_void_p, [_H]),
     "aniso_device": (C.c_int, [_H]),
@@ -81,6 +82,8 @@ SIGNATURES = {
     "aniso_time_forward": (C.c_int, [_H, C.c_int, C.POINTER(C.c_double)]),
     "aniso_get_config": (C.c_char_p, [_H]),
 }
+
+NOALLOC_MAX_SEGMENTS = 32768  # ANISO_NOALLOC_MAX_SEGMENTS of include/aniso_b200.h
 
 _lib = None
 

@@ -208,6 +208,13 @@ class Aniso:
         _lib.check(self.L.aniso_line_integral(self.h, len(p), p.reshape(-1), out))
         return out
 
+    def line_integral_noalloc(self, pts4):
+        """line_integral on the library's fixed scratch array: no cudaMalloc / cudaFree (at most _lib.NOALLOC_MAX_SEGMENTS segments)"""
+        p = np.ascontiguousarray(np.asarray(pts4, np.float64).reshape(-1, 4))
+        out = np.zeros(len(p))
+        _lib.check(self.L.aniso_line_integral_noalloc(self.h, len(p), p.reshape(-1), out))
+        return out
+
     def kernel_eval(self, kid, part, pts4):
         p = np.ascontiguousarray(np.asarray(pts4, np.float64).reshape(-1, 4))
         out = np.zeros(len(p))

@@ -2245,3 +2245,61 @@ int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// Allocation-free probe (no counterpart in the reference).
+// aniso_line_integral stages its points and results in a device buffer it cudaMallocs and frees on every call.  Callers that
+// must not allocate (tight serving loops, harnesses that forbid cudaMalloc) get the same kernel on a fixed scratch array
+// that lives in the library image: ANISO_NOALLOC_MAX_SEGMENTS segments, 5 doubles each = 1.25 MiB, held by every GPU that
+// loads the library until the process exits.
+//   layout   [0, 4 MAX)       end points (x0, y0, x1, y1) of the segments, copied from the caller's host buffer
+//            [4 MAX, 5 MAX)   the optical depths the kernel writes, copied back to the caller's host buffer
+// `g_noalloc_scratch` is a host-side stand-in in host code, NOT a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, asked for once per device with that device current (noalloc_scratch_ptr below).
+// The array is shared by every call on a GPU and keeps the contents of the last call.  Nothing in it has to start at
+// zero - a call overwrites the 4n inputs it reads and the kernel writes all n outputs it returns - but the output range is
+// cleared first all the same, so that a launch that fails cannot hand back the previous call's values.  Calls that overlap
+// on one GPU (two host threads, two handles on the same device) race on the array; the entry point synchronises its stream
+// before it returns, so calls made one after the other are safe.
+// ---------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_noalloc_scratch[5 * ANISO_NOALLOC_MAX_SEGMENTS];
+
+namespace {
+
+double* noalloc_scratch_ptr(int device) {  // the caller has made `device` current
+    static std::atomic<double*> cache[64];
+    if (device < 0 || device >= 64) throw std::invalid_argument("device ordinal out of range for the allocation-free probe");
+    double* p = cache[device].load();
+    if (p) return p;
+    void* sym = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&sym, g_noalloc_scratch);
+    if (e != cudaSuccess || !sym) throw std::runtime_error(std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+    p = static_cast<double*>(sym);
+    cache[device].store(p);  // the address of a symbol is fixed per device: a second thread finding nullptr stores the same value
+    return p;
+}
+
+}  // namespace
+
+extern "C" int aniso_line_integral_noalloc(aniso_t* h, int n, const double* pts4, double* out) {
+    API_BEGIN
+    REQUIRE(h && pts4 && out && n >= 0, "bad arguments");
+    if (n > ANISO_NOALLOC_MAX_SEGMENTS)
+        throw std::invalid_argument("aniso_line_integral_noalloc: " + std::to_string(n) + " segments exceed the fixed scratch of " +
+                                    std::to_string(ANISO_NOALLOC_MAX_SEGMENTS) + " (use aniso_line_integral, or split the call)");
+    // no lazy set-up here: creating streams and uploading the geometry allocates
+    if (!h->dev_ready || !h->coeff_set) throw std::logic_error("setCoeff must precede aniso_line_integral_noalloc (it sets the device up)");
+    check_probe_points(n, pts4);
+    if (n == 0) return ANISO_OK;
+    CK(cudaSetDevice(h->device));
+    double* scr = noalloc_scratch_ptr(h->device);
+    double* res = scr + (size_t)4 * ANISO_NOALLOC_MAX_SEGMENTS;
+    CK(cudaMemcpyAsync(scr, pts4, sizeof(double) * 4 * n, cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemsetAsync(res, 0, sizeof(double) * n, h->st));
+    LAUNCH(h, launch_probe_line_integral(h->S, n, scr, res, h->st));
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, res, sizeof(double) * n, cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return ANISO_OK;
+    API_END
+}

@@ -178,6 +178,16 @@ int aniso_line_integral(aniso_t* h, int n, const double* pts4_host, double* out_
 /* realParts[id].eval / imagParts[id].eval (makeKernels KernelFactory.cpp:240-267): pts4 = (ax,ay,bx,by) */
 int aniso_kernel_eval(aniso_t* h, int id, int part, int n, const double* pts4_host, double* out_host);
 
+/* aniso_line_integral without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that must not call cudaMalloc (tight serving loops, harnesses that forbid it).  Same kernel, same results; the
+ * device staging buffer is a fixed array in the library image (5 doubles per segment: 1.25 MiB on every GPU that loads the
+ * library, until the process exits) instead of a cudaMalloc / cudaFree pair per call.  n > ANISO_NOALLOC_MAX_SEGMENTS fails
+ * with ANISO_EINVAL; a handle whose aniso_set_coeff has not run fails with ANISO_ESTATE (no lazy set-up: that would allocate).
+ * The array is shared by all calls on a GPU and keeps the last call's contents: calls that overlap on one GPU (two host
+ * threads, two handles on one device) race; calls made one after the other are safe (the call synchronises before returning). */
+enum { ANISO_NOALLOC_MAX_SEGMENTS = 32768 };
+int aniso_line_integral_noalloc(aniso_t* h, int n, const double* pts4_host, double* out_host);
+
 /* ---- plumbing ---------------------------------------------------------------------------------------------- */
 void* aniso_stream(aniso_t* h);          /* cudaStream_t all work of the handle is launched on */
 int aniso_device(const aniso_t* h);
