@@ -18,6 +18,9 @@ _V = C.c_void_p  # raw device pointer
 # host preconditioner callback of aniso_gmres_prec / aniso_block_gmres_prec: int (*)(void* ctx, int n, const double* r, double* z)
 PREC_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double))
 
+# host kernel callback of aniso_fmm_cache: double (*)(void* ctx, double sx, double sy, double tx, double ty)
+EVAL_FN = C.CFUNCTYPE(C.c_double, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double)
+
 # name -> (restype, argtypes): exactly the symbols include/aniso_b200.h declares
 SIGNATURES = {
     "aniso_last_error": (C.c_char_p, []),
@@ -43,6 +46,7 @@ SIGNATURES = {
     "aniso_sigma_coeff": (C.c_int, [_H, _dp, _dp]),
     "aniso_cache": (C.c_int, [_H, C.c_int]),
     "aniso_cache_part": (C.c_int, [_H, C.c_int, C.c_int]),
+    "aniso_set_option": (C.c_int, [_H, C.c_char_p, C.c_char_p]),
     "aniso_cache_bytes": (C.c_size_t, [_H, C.c_int]),
     "aniso_cache_counts": (C.c_int, [_H, _lp]),
     "aniso_cache_times": (C.c_int, [_H, _dp]),
@@ -64,6 +68,9 @@ SIGNATURES = {
     "aniso_block_forward_dev": (C.c_int, [_H, _V, C.c_int, _V]),
     "aniso_block_gmres": (C.c_int, [_H, _dp, _dp, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
     "aniso_block_gmres_dev": (C.c_int, [_H, _V, _V, C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), _dp, C.c_int]),
+    "aniso_fmm_create": (C.c_int, [C.c_int, C.c_int, _dp, _dp, C.c_int, C.c_int, C.POINTER(_H)]),
+    "aniso_fmm_cache": (C.c_int, [_H, EVAL_FN, C.c_void_p, C.c_int]),
+    "aniso_fmm_apply": (C.c_int, [_H, _dp, _dp]),
     "aniso_line_integral": (C.c_int, [_H, C.c_int, _dp, _dp]),
     "aniso_line_integral_noalloc": (C.c_int, [_H, C.c_int, _dp, _dp]),
     "aniso_kernel_eval": (C.c_int, [_H, C.c_int, C.c_int, C.c_int, _dp, _dp]),

@@ -81,6 +81,10 @@ class Aniso:
         self.sigma_s, self.sigma_t = _vec(sigma_s, n, "sigma_s"), _vec(sigma_t, n, "sigma_t")
         _lib.check(self.L.aniso_set_coeff(self.h, self.sigma_s, self.sigma_t))
 
+    def set_option(self, name, value):
+        """aniso_set_option: e.g. ("p2p", "onfly") evaluates the near-field tiles during the apply instead of caching them"""
+        _lib.check(self.L.aniso_set_option(self.h, str(name).encode(), str(value).encode()))
+
     def cache(self, kid):
         _lib.check(self.L.aniso_cache(self.h, int(kid)))
 
@@ -319,6 +323,86 @@ class Aniso:
 
     def synchronize(self):
         _lib.check(self.L.aniso_synchronize(self.h))
+
+
+class BBFMMKernel:
+    """bbfmm::kernel (bbfmm.h:451-592) for a caller-supplied eval(sx, sy, tx, ty) -> float: the black-box interface itself.
+        k = BBFMMKernel(); k.eval = f; k.initialize(np, x, y, charge, rank, maxLevel); pot = k.runCache() / k.runFast() / k.run()
+    eval runs on the host (the reference's std::function does too): the operators are tabulated once on the host and applied
+    on the device.  Sources and targets are one point set.  A Python eval is called from one thread (the GIL); a C callback
+    passed as `eval_c` (an _lib.EVAL_FN) is called from all host threads."""
+
+    def __init__(self):
+        self.L = _lib.load()
+        self.h = None
+        self.eval = None
+        self.eval_c = None
+        self.nChebyshev = self.rank = 0
+        self.chargeTree = None
+        self._cached = False
+        self._key = None
+
+    def initialize(self, nChebyshev, x, y, charge, rank, maxLevel):
+        x, y = _vec(x), _vec(y, None)
+        if x.size != y.size:
+            raise ValueError("x and y differ in length")
+        key = (int(nChebyshev), int(rank), int(maxLevel), x.tobytes(), y.tobytes())
+        if key != self._key:  # the reference re-initialises before every run (KernelFactory.cpp:356, 380): same tree, kept
+            self.delete()
+            h = C.c_void_p()
+            _lib.check(self.L.aniso_fmm_create(int(nChebyshev), x.size, x, y, int(rank), int(maxLevel), C.byref(h)))
+            self.h, self._key, self._cached = h, key, False
+        self.nChebyshev, self.rank, self.n = int(nChebyshev), int(nChebyshev) ** 2, x.size
+        self.chargeTree = _vec(charge, x.size, "charge").copy()
+
+    def _tabulate(self):
+        if self.eval_c is not None:
+            cb, threads = self.eval_c, 0
+        else:
+            f = self.eval
+            cb, threads = _lib.EVAL_FN(lambda ctx, sx, sy, tx, ty: float(f(sx, sy, tx, ty))), 1
+        _lib.check(self.L.aniso_fmm_cache(self.h, cb, None, threads))
+        self._cached = True
+
+    def _apply(self):
+        out = np.zeros(self.n)
+        _lib.check(self.L.aniso_fmm_apply(self.h, self.chargeTree, out))
+        return out
+
+    def run(self):
+        """kernel::run (bbfmm.h:507-532): evaluates the kernel during the pass; nothing is kept"""
+        self._tabulate()
+        out = self._apply()
+        self._cached = False
+        return out
+
+    def runCache(self):
+        """kernel::runCache (bbfmm.h:535-562): evaluates every entry, keeps it, applies"""
+        self._tabulate()
+        return self._apply()
+
+    def runFast(self):
+        """kernel::runFast (bbfmm.h:565-592): applies the cached operators"""
+        if not self._cached:
+            raise _lib.AnisoError(-4, "runCache must precede runFast")
+        return self._apply()
+
+    def tree_stats(self):
+        o = np.zeros(9, np.int64)
+        _lib.check(self.L.aniso_tree_stats(self.h, o))
+        return o
+
+    def delete(self):
+        if self.h:
+            self.L.aniso_destroy(self.h)
+            self.h = None
+            self._key = None
+
+    def __del__(self):
+        try:
+            self.delete()
+        except Exception:
+            pass
 
 
 def gl_table(deg):

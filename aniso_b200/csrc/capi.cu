@@ -38,6 +38,8 @@ struct OperatorCache {  // Cache[node][slot] of bbfmm.h:466, flattened
     double* p2p = nullptr;
     double* m2l = nullptr;
     double sign = 1.0;  // (-1)^id
+    int id = 0, part = PART_BOTH;  // what the blocks hold (needed when the P2P tiles are evaluated on the fly: p2p == nullptr)
+    bool valid = true;             // false after setCoeff: the allocation is kept and refilled in place by the next use
 };
 struct StencilCache {
     double *c7 = nullptr, *c8 = nullptr, *c9 = nullptr, *call = nullptr;
@@ -58,6 +60,7 @@ struct aniso_handle {
     bool overlap = true;
     // sharded upward pass (nranks > 1, complete uniform tree, equal shares): every rank runs P2M / M2M on its own sub-trees
     // only and the multipoles of all levels are all-gathered (one grouped NCCL call) instead of a replicated upward pass
+    bool p2p_onfly = false;  // aniso_set_option("p2p", "onfly"): near-field tiles evaluated during the apply, not cached
     bool up_sharded = false;
     // CUDA graphs of the operator y = x - mapping_0(sigma_s x), keyed by its two device pointers: the second application
     // with a pointer pair is captured (both streams, the NCCL calls and the fork / join events become one graph), later ones
@@ -326,7 +329,7 @@ void ensure_device(aniso_handle* h) {
     {
         // complete uniform quadtree?  (every node non-empty, all leaves on the deepest level, 4^L nodes on level L)
         const int deepest = T.nlevels - 1;
-        bool ok = getenv("ANISO_NO_SUBTREE") == nullptr && !p.m2l.group_node.empty() && r <= 64 && (int)p.leaves.size() == (1 << (2 * deepest));
+        bool ok = getenv("ANISO_NO_SUBTREE") == nullptr && !p.generic && !p.m2l.group_node.empty() && r <= 64 && (int)p.leaves.size() == (1 << (2 * deepest));
         for (int L = 0; ok && L <= deepest; ++L) ok = p.level_ptr[L + 1] - p.level_ptr[L] == (1 << (2 * L));
         for (int i = 0; ok && i < nn; ++i) ok = !p.nodes[i].empty && p.nodes[i].leaf == (p.nodes[i].level == deepest);
         for (size_t k = 0; ok && k < p.leaves.size(); ++k) ok = p.leaves[k] == p.level_ptr[deepest] + (int)k;
@@ -727,6 +730,17 @@ DevCSR sub_range(const DevCSR& m, int g0, int count) {
     return s;
 }
 
+// setCoeff: the sigma-dependent operators become stale, their memory stays.  An inverse-problem loop calls setCoeff every
+// iteration; returning 3 GB to the driver and asking for it again cost more than evaluating the operators (measured 21 ms
+// from setCoeff to the first mapping result at N = 2^20, of which 10 ms were cudaFree / cudaMalloc).  The real-part
+// operators (cos(k theta) / r, KernelFactory.cpp:243-252) and the correction stencils (K7 / K8 / K9 act on the real part
+// only) do not depend on sigma and stay valid.
+void invalidate_caches(aniso_handle* h) {
+    drop_graphs(h);
+    for (auto& kv : h->ops)
+        if (kv.second.part != PART_REAL) kv.second.valid = false;
+}
+
 void free_caches(aniso_handle* h) {
     drop_graphs(h);
     for (auto& kv : h->ops) {
@@ -756,19 +770,29 @@ void check_id(const aniso_handle* h, int id) {
 OperatorCache& ensure_ops(aniso_handle* h, int id, int part) {
     auto key = std::make_pair(id, part);
     auto it = h->ops.find(key);
-    if (it != h->ops.end()) return it->second;
+    if (it != h->ops.end() && it->second.valid) return it->second;
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede cache/mapping");
+    const bool refill = it != h->ops.end();  // stale after setCoeff: same allocation, new values
     OperatorCache c;
+    if (refill) c = it->second;
     c.sign = (id & 1) ? -1.0 : 1.0;
-    c.p2p = dalloc<double>(h, (size_t)h->p2p.nnz + 2);  // + 16 bytes: the last bulk copy of a stream that starts on an odd
-    c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz + 2);  //   double rounds up to the next 16-byte boundary (stream.cu symg ring)
+    c.id = id;
+    c.part = part;
+    c.valid = true;
+    const bool onfly = h->p2p_onfly && p2p_onfly_ok(h->p2p, h->T.max_leaf);
+    if (!refill) {
+        if (!onfly) c.p2p = dalloc<double>(h, (size_t)h->p2p.nnz + 2);  // + 16 bytes: the last bulk copy of a stream that starts on an odd
+        c.m2l = dalloc<double>(h, (size_t)h->m2l.nnz + 2);  //   double rounds up to the next 16-byte boundary (stream.cu symg ring)
+    }
     cudaEvent_t ev[3];
     for (auto& e : ev) CK(cudaEventCreate(&e));
     // the optical depth is the same for every kernel id: ids > 0 of the fused operators are derived from id 0
     const OperatorCache* base = nullptr;
     if (id > 0 && part == PART_BOTH && !getenv("ANISO_NO_SHARED_TAU")) base = &ensure_ops(h, 0, PART_BOTH);
     CK(cudaEventRecord(ev[0], h->st));
-    if (base) LAUNCH(h, launch_fill_from_base(h->p2p, h->T, h->G, id, 0, base->p2p, c.p2p, h->st));
+    if (onfly) {
+        // nothing to fill
+    } else if (base && base->p2p) LAUNCH(h, launch_fill_from_base(h->p2p, h->T, h->G, id, 0, base->p2p, c.p2p, h->st));
     else LAUNCH(h, launch_fill(h->p2p, h->T, h->G, h->S, id, part, 0, c.p2p, h->st));
     CK(cudaEventRecord(ev[1], h->st));
     if (base) LAUNCH(h, launch_fill_from_base(h->m2l, h->T, h->G, id, 1, base->m2l, c.m2l, h->st));
@@ -779,13 +803,14 @@ OperatorCache& ensure_ops(aniso_handle* h, int id, int part) {
     CK(cudaEventElapsedTime(&h->fill_ms[0], ev[0], ev[1]));
     CK(cudaEventElapsedTime(&h->fill_ms[1], ev[1], ev[2]));
     for (auto& e : ev) cudaEventDestroy(e);
-    h->fill_counts[0] = h->p2p.nnz;
+    h->fill_counts[0] = onfly ? 0 : h->p2p.nnz;
     h->fill_counts[1] = h->m2l.nnz;
     return h->ops[key] = c;
 }
 
 // refineAddOnCache + singularAddCache (KernelFactory.cpp:550-609, 752-788), plus the K7 table
 StencilCache& ensure_stencils(aniso_handle* h, int id) {
+    if (h->plan.generic) throw std::logic_error("this handle is a bbfmm::kernel point-set handle (aniso_fmm_create), not an Aniso object");
     auto it = h->stencils.find(id);
     if (it != h->stencils.end()) return it->second;
     const size_t n9 = (size_t)9 * h->G.c2 * h->nown;
@@ -850,7 +875,8 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     // every SM, and sub-tree CTAs launched behind it would wait for its CTAs to retire (measured: upward pass 88 us instead of
     // 55 at N = 2^20).  Issued first, they take their slots at once and the stream kernel fills the rest of the machine.
     auto p2p_on_bulk = [&] {
-        LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, sb));
+        if (c.p2p) LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, q, h->d_pot, c.sign, false, sb));
+        else LAUNCH(h, launch_p2p_onfly(h->p2p, h->G, h->S, c.id, c.part, q, h->d_pot, c.sign, sb));  // cache-free near field
         phase_mark(h, "[b]p2p", sb);
     };
     if (src) {
@@ -1172,12 +1198,13 @@ extern "C" {
 int aniso_set_coeff(aniso_t* h, const double* sigma_s, const double* sigma_t) {
     API_BEGIN
     REQUIRE(h && sigma_s && sigma_t, "null pointer");
+    if (h->plan.generic) throw std::logic_error("this handle is a bbfmm::kernel point-set handle (aniso_fmm_create), not an Aniso object");
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     const HostPlan& p = h->plan;
     const int N = p.N;
     CK(cudaStreamSynchronize(h->st));
-    free_caches(h);
+    invalidate_caches(h);
     h->sigma_s.assign(sigma_s, sigma_s + N);
     h->sigma_t.assign(sigma_t, sigma_t + N);
     // sigma_s in slot order for the GMRES operator
@@ -1198,6 +1225,7 @@ int aniso_set_coeff(aniso_t* h, const double* sigma_s, const double* sigma_t) {
 int aniso_interpolation(aniso_t* h, const double* f, double* coeff) {
     API_BEGIN
     REQUIRE(h && f && coeff, "null pointer");
+    if (h->plan.generic) throw std::logic_error("this handle is a bbfmm::kernel point-set handle (aniso_fmm_create), not an Aniso object");
     ensure_device(h);
     CK(cudaSetDevice(h->device));
     const int N = h->plan.N;
@@ -1250,7 +1278,7 @@ size_t aniso_cache_bytes(const aniso_t* h, int id) {
     if (!h) return 0;
     size_t b = 0;
     for (auto& kv : h->ops)
-        if (kv.first.first == id) b += (size_t)(h->p2p.nnz + h->m2l.nnz) * sizeof(double);
+        if (kv.first.first == id) b += (size_t)((kv.second.p2p ? h->p2p.nnz : 0) + h->m2l.nnz) * sizeof(double);
     if (h->stencils.count(id)) b += ((size_t)3 * 9 + 1) * h->G.c2 * h->nown * sizeof(double);
     return b;
 }
@@ -1491,7 +1519,8 @@ void forward_own(aniso_handle* h, const double* x_own, double* y_own, bool graph
 bool block_multi_ok(const aniso_handle* h) {
     const int K = h->plan.K;
     auto ok = [](const DevCSR& m) { return m.symmetric && (m.uniform_block == 16 || m.uniform_block == 64); };
-    return h->subtree_ok && ok(h->m2l) && ok(h->p2p) && 2 * K - 1 <= FoldList::MAXF && !getenv("ANISO_BLOCK_LOOP");
+    return h->subtree_ok && ok(h->m2l) && ok(h->p2p) && 2 * K - 1 <= FoldList::MAXF && !getenv("ANISO_BLOCK_LOOP") &&
+           !h->p2p_onfly;  // the batched forms stream cached P2P tiles
 }
 
 void block_apply_multi(aniso_handle* h, const double* full, const double* u_own, double* out, bool weighted, bool subtract) {
@@ -2196,6 +2225,29 @@ int aniso_time_forward(aniso_t* h, int reps, double* ms) {
     API_END
 }
 
+int aniso_set_option(aniso_t* h, const char* name, const char* value) {
+    API_BEGIN
+    REQUIRE(h && name && value, "null pointer");
+    const std::string n(name), v(value);
+    if (n == "p2p") {
+        // "cached" (default): runKernelsCache stores every U/W tile (bbfmm.h:949-1039); "onfly": the tiles are evaluated while
+        // they are applied, like the reference's uncached kernel::run (bbfmm.h:507-532, 863-946)
+        REQUIRE(v == "cached" || v == "onfly", "option p2p takes \"cached\" or \"onfly\"");
+        const bool want = v == "onfly";
+        if (want != h->p2p_onfly) {
+            if (h->dev_ready) {
+                CK(cudaSetDevice(h->device));
+                CK(cudaStreamSynchronize(h->st));
+                free_caches(h);  // the operators are rebuilt in the new form by the next cache / mapping call
+            }
+            h->p2p_onfly = want;
+        }
+        return ANISO_OK;
+    }
+    throw std::invalid_argument("unknown option \"" + n + "\" (known: p2p)");
+    API_END
+}
+
 const char* aniso_get_config(const aniso_t* h) {
     // the environment switches that select a code path (development A/B switches; all default off), as one string a
     // benchmark line can carry so that a run describes itself
@@ -2209,7 +2261,7 @@ const char* aniso_get_config(const aniso_t* h) {
         cfg += "; ranks=" + std::to_string(h->nranks) + " sym=" + std::to_string(h->plan.m2l.symmetric ? 1 : 0) +
                " subtree=" + std::to_string(h->subtree_ok ? 1 : 0) + " overlap=" + std::to_string(h->overlap ? 1 : 0) +
                " table_line_integral=" + std::to_string(h->S.ty ? 1 : 0) + " up_sharded=" + std::to_string(h->up_sharded ? 1 : 0) +
-               " peer_collectives=" + std::to_string(h->peer.ready ? 1 : 0);
+               " peer_collectives=" + std::to_string(h->peer.ready ? 1 : 0) + " p2p=" + (h->p2p_onfly ? "onfly" : "cached");
     }
     const char* o = getenv("ANISO_GMRES_ORTHO");
     cfg += std::string("; gmres=") + (o ? o : "cgs2") + (getenv("ANISO_GMRES_SYNC") ? "/sync" : "/pipelined");
@@ -2231,7 +2283,8 @@ int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms) {
     CK(cudaEventRecord(e0, h->st));
     for (int i = 0; i < reps; ++i) {
         if (which == 0) LAUNCH(h, launch_bsr_apply(h->m2l, c.m2l, h->d_mcharge, h->d_mpot, c.sign, false, h->st));
-        else LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, h->d_q, h->d_pot, c.sign, false, h->st));
+        else if (c.p2p) LAUNCH(h, launch_bsr_apply(h->p2p, c.p2p, h->d_q, h->d_pot, c.sign, false, h->st));
+        else LAUNCH(h, launch_p2p_onfly(h->p2p, h->G, h->S, c.id, c.part, h->d_q, h->d_pot, c.sign, h->st));
     }
     CK(cudaEventRecord(e1, h->st));
     CK(cudaEventSynchronize(e1));
@@ -2303,3 +2356,77 @@ extern "C" int aniso_line_integral_noalloc(aniso_t* h, int n, const double* pts4
     return ANISO_OK;
     API_END
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// bbfmm::kernel for a caller-supplied eval (bbfmm.h:451-505): the black-box interface itself.  eval is a host callback and
+// cannot run on the device, so the operators are tabulated on the host - once, OpenMP over the U/W/V/X entries, in
+// the block-CSR layout of the aniso path - and the apply is the device path: P2M / M2M, streamed M2L and P2P blocks, L2L /
+// L2P (run_fmm with mode 0).  Nothing is assumed about eval: every block is stored (no symmetric storage).
+// ---------------------------------------------------------------------------------------------------
+extern "C" {
+
+int aniso_fmm_create(int np, int n, const double* x, const double* y, int leaf_capacity, int maxLevel, aniso_t** out) {
+    API_BEGIN
+    REQUIRE(out && x && y, "null pointer");
+    aniso_handle* h = new aniso_handle();
+    try {
+        build_plan_points(h->plan, np, n, x, y, leaf_capacity, maxLevel);
+    } catch (const std::exception& e) {
+        delete h;
+        throw std::invalid_argument(e.what());
+    }
+    const HostPlan& p = h->plan;
+    h->all_slot_begin.assign(1, 0);
+    h->all_slot_end.assign(1, p.N);
+    h->leaf_begin = 0;
+    h->leaf_end = (int)p.leaves.size();
+    h->slot0 = 0;
+    h->nown = p.N;
+    *out = h;
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_fmm_cache(aniso_t* h, aniso_eval_fn eval, void* ctx, int threads) {
+    API_BEGIN
+    REQUIRE(h && eval, "null pointer");
+    if (!h->plan.generic) throw std::logic_error("aniso_fmm_cache needs a handle made by aniso_fmm_create");
+    ensure_device(h);
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->st));
+    free_caches(h);
+    const HostPlan& p = h->plan;
+    OperatorCache c;
+    c.sign = 1.0;
+    c.id = 0;
+    c.part = PART_BOTH;
+    c.p2p = dalloc<double>(h, (size_t)p.p2p.nnz + 2);
+    c.m2l = dalloc<double>(h, (size_t)p.m2l.nnz + 2);
+    std::vector<double> host((size_t)std::max(p.p2p.nnz, p.m2l.nnz));
+    tabulate_operator(p, p.p2p, false, eval, ctx, threads, host.data());
+    CK(cudaMemcpy(c.p2p, host.data(), sizeof(double) * p.p2p.nnz, cudaMemcpyHostToDevice));
+    tabulate_operator(p, p.m2l, true, eval, ctx, threads, host.data());
+    CK(cudaMemcpy(c.m2l, host.data(), sizeof(double) * p.m2l.nnz, cudaMemcpyHostToDevice));
+    h->fill_counts[0] = p.p2p.nnz;
+    h->fill_counts[1] = p.m2l.nnz;
+    h->ops[std::make_pair(0, (int)PART_BOTH)] = c;
+    return ANISO_OK;
+    API_END
+}
+
+int aniso_fmm_apply(aniso_t* h, const double* charge, double* potential) {
+    API_BEGIN
+    REQUIRE(h && charge && potential, "null pointer");
+    if (!h->plan.generic) throw std::logic_error("aniso_fmm_apply needs a handle made by aniso_fmm_create");
+    auto it = h->ops.find(std::make_pair(0, (int)PART_BOTH));
+    if (it == h->ops.end()) throw std::logic_error("aniso_fmm_cache must precede aniso_fmm_apply");
+    CK(cudaSetDevice(h->device));
+    to_slots(h, charge, h->d_q);            // chargeTree (bbfmm.h:485): used as given, no quadrature weights
+    run_fmm(h, it->second, h->d_q, h->d_b);  // mode 0: upPass + downPassFast, nothing else
+    from_slots(h, h->d_b, potential);
+    return ANISO_OK;
+    API_END
+}
+
+}  // extern "C"

@@ -108,6 +108,12 @@ void launch_fill_from_base(const DevCSR& m, const DevTree& T, const DevGeom& G, 
 // reduce = false (symmetric storage only): leave the per-target sums in the scratch rows for the consumer to fold
 void launch_bsr_apply(const DevCSR& m, const double* A, const double* x, double* y, double sign, bool reduce, cudaStream_t st);
 void launch_bsr_reduce(const DevCSR& m, double* y, cudaStream_t st);
+// cache-free P2P (kernel::run / downPass, bbfmm.h:507-532, 863-946): evaluates the U/W tiles of kernel (id, part) while
+// applying them to q; leaves its results where launch_bsr_apply(..., reduce = false) would (scratch rows under symmetric
+// storage, y otherwise).  Leaves of at most 64 points.
+bool p2p_onfly_ok(const DevCSR& m, int max_leaf);
+void launch_p2p_onfly(const DevCSR& m, const DevGeom& G, const SigmaGrid& S, int id, int part, const double* q, double* y, double sign,
+                      cudaStream_t st);
 // the same operator applied to nrhs vectors x + r*xstride in one pass (symmetric storage, 16x16 / 64x64 blocks); results
 // stay in the scratch sets scr + r*sstride (laid out like m.scratch).  Returns the number of launches.
 int launch_bsr_apply_multi(const DevCSR& m, const double* A, const double* x, size_t xstride, int nrhs, double* scr, size_t sstride,

@@ -116,11 +116,17 @@ __device__ double line_integral(const SigmaGrid& S, double x0, double y0, double
 // one independent term per crossed line of the MINOR axis (on average 3.4x fewer terms than cells crossed, none at
 // all for axis-aligned rays), each two 16-byte table reads and a handful of FMAs.  Exact for the piecewise-constant
 // interpolant like the cell walk (the reference's bisection + one-point Gauss rule, KernelFactory.cpp:67-190).
+// CLAMP: the getRow/getCol clamp of the reference (KernelFactory.cpp:392-401), needed for caller-supplied points on or
+// beyond the edge of the unit square (the probe entry points).  Every point the matvec path itself evaluates - quadrature
+// nodes, Chebyshev nodes of tree boxes, which lie inside the bounding box of the nodes - is at least half a cell inside the
+// square, where round(v*sz - 0.5) is in [0, sz - 1] by itself; the evaluator instantiates CLAMP = false (the double
+// fmin / fmax pair was 15 % of its instructions, profiles/r02_ncu_raw.csv + source page).
+template <bool CLAMP>
 __device__ __forceinline__ double magic_floor(double v, double szd, double top, int& j) {
     // t = round(v*sz - 0.5) = floor(v*sz) away from integers; at an integer either neighbour is fine (F is continuous)
     const double MAGIC = 6755399441055744.0;  // 2^52 + 2^51: the integer sits in the low mantissa bits
     double t = fma(v, szd, -0.5) + MAGIC;     // (MAGIC - 0.5 is not representable: the shift needs its own rounding)
-    t = fmin(fmax(t, MAGIC), top);            // getRow/getCol clamp
+    if (CLAMP) t = fmin(fmax(t, MAGIC), top);
     j = __double2loint(t);
     return t - MAGIC;
 }
@@ -134,6 +140,7 @@ __device__ __forceinline__ double magic_floor_inner(double v, double szd, int& j
     return t - MAGIC;
 }
 
+template <bool CLAMP>
 __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0, double y0, double x1, double y1, double len) {
     const double ddx = x1 - x0, ddy = y1 - y0;
     const bool steep = fabs(ddy) >= fabs(ddx);
@@ -143,9 +150,9 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
     const int sz = S.sz;
     const double szd = (double)sz, h = S.h, top = 6755399441055744.0 + (double)(sz - 1);
     int c0, c1, j0, j1;
-    magic_floor(u0, szd, top, c0);
-    magic_floor(u1, szd, top, c1);
-    const double jd0 = magic_floor(v0, szd, top, j0), jd1 = magic_floor(v1, szd, top, j1);
+    magic_floor<CLAMP>(u0, szd, top, c0);
+    magic_floor<CLAMP>(u1, szd, top, c1);
+    const double jd0 = magic_floor<CLAMP>(v0, szd, top, j0), jd1 = magic_floor<CLAMP>(v1, szd, top, j1);
     const double2 e0 = __ldg(tab + (size_t)c0 * sz + j0), e1 = __ldg(tab + (size_t)c1 * sz + j1);
     double acc = (e1.x - e0.x) + (fma(e1.y, fma(-jd1, h, v1), -e0.y * fma(-jd0, h, v0)));
     if (c0 != c1) {
@@ -195,8 +202,43 @@ __device__ __forceinline__ double cos_k_theta(int k, double c, double s) {  // R
     return cr;
 }
 
+// exp(x) for -700 <= x <= 700 (the attenuation e^{-tau}: tau is an optical depth of order 1 - 100).  libm's exp spent two
+// thirds of its instructions on range and special-case handling this argument never needs.  n = round(x / ln 2) by the
+// magic-number shift, r = x - n ln 2 in two FMAs (ln 2 split hi + lo), e^r by the degree-13 Taylor polynomial, even and odd powers as
+// two Horner chains in r^2 (|r| <= 0.347: truncation r^14 / 14! < 5e-18), scaled by 2^n through the exponent field.  Within 2 ulp of the correctly
+// rounded value, i.e. at rounding level against the reference's libm (parity gate 1e-10); below -700 the result is 0.
+__device__ __forceinline__ double exp_reduced(double x) {
+    const double MAGIC = 6755399441055744.0;
+    const double t = fma(x, 1.4426950408889634074, MAGIC);
+    const int n = __double2loint(t);
+    const double nd = t - MAGIC;
+    double r = fma(nd, -6.93147180559945286227e-01, x);
+    r = fma(nd, -2.31904681384629955842e-17, r);
+    // even and odd powers as two independent Horner chains in r^2 (dependency depth 8 instead of 13: the evaluator runs 8
+    // warps per scheduler and waits on dependent FP64 results)
+    const double r2 = r * r;
+    double pe = 2.0876756987868098979e-09;           // 1/12!
+    double po = 1.6059043836821614599e-10;           // 1/13!
+    pe = fma(pe, r2, 2.7557319223985890653e-07);     // 1/10!
+    po = fma(po, r2, 2.5052108385441718775e-08);     // 1/11!
+    pe = fma(pe, r2, 2.4801587301587301566e-05);     // 1/8!
+    po = fma(po, r2, 2.7557319223985892511e-06);     // 1/9!
+    pe = fma(pe, r2, 1.3888888888888889419e-03);     // 1/6!
+    po = fma(po, r2, 1.9841269841269841253e-04);     // 1/7!
+    pe = fma(pe, r2, 4.1666666666666664354e-02);     // 1/4!
+    po = fma(po, r2, 8.3333333333333332177e-03);     // 1/5!
+    pe = fma(pe, r2, 0.5);
+    po = fma(po, r2, 1.6666666666666665741e-01);     // 1/3!
+    pe = fma(pe, r2, 1.0);
+    po = fma(po, r2, 1.0);
+    const double p = fma(po, r, pe);
+    const double e = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+    return x < -700.0 ? 0.0 : e;
+}
+
 // D1: the deg-1 table path is known at compile time (keeps the general cell walk and its registers out of the kernel)
-template <bool D1>
+// CLAMP: see magic_floor (false on the evaluator's own points)
+template <bool D1, bool CLAMP = true>
 __device__ __forceinline__ double kernel_eval_t(const SigmaGrid& S, int id, int part, double ax, double ay, double bx, double by) {
     const double ddx = ax - bx, ddy = ay - by;
     const double d2 = ddx * ddx + ddy * ddy;
@@ -212,8 +254,8 @@ __device__ __forceinline__ double kernel_eval_t(const SigmaGrid& S, int id, int 
     }
     const double ck = id == 0 ? 1.0 : cos_k_theta(id, ddx * inv, ddy * inv);
     if (part == PART_REAL) return ck * inv;
-    const double tau = D1 ? line_integral_d1(S, ax, ay, bx, by, dist) : line_integral(S, ax, ay, bx, by);
-    const double e = exp(-tau);
+    const double tau = D1 ? line_integral_d1<CLAMP>(S, ax, ay, bx, by, dist) : line_integral(S, ax, ay, bx, by);
+    const double e = D1 ? exp_reduced(-tau) : exp(-tau);
     if (part == PART_IMAG) return (e - 1.0) * ck * inv;
     return e * ck * inv;
 }
@@ -258,7 +300,7 @@ __global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, 
         s_cheb[threadIdx.x - 32] = T.cheb[threadIdx.x - 32];
     __syncthreads();
     for (int j = 0; j < cnt; ++j) {
-        const int nrow = s_off[j][2], ncol = s_off[j][3];
+        const int nrow = NR ? NR : s_off[j][2], ncol = NR ? NR : s_off[j][3];  // NR: the block shape is a compile-time constant
         double* __restrict__ out = A + s_blk[j];
         const int total = nrow * ncol;
         for (int idx0 = threadIdx.x; idx0 < total; idx0 += blockDim.x) {
@@ -294,7 +336,7 @@ __global__ void __launch_bounds__(256, D1 ? 4 : 2) fill_blocks_kernel(DevCSR m, 
                 bx = G.px[toff + t];
                 by = G.py[toff + t];
             }
-            out[idx] = kernel_eval_t<D1>(S, id, part, ax, ay, bx, by);
+            out[idx] = kernel_eval_t<D1, false>(S, id, part, ax, ay, bx, by);  // nodes / Chebyshev nodes: interior points
         }
     }
 }
@@ -375,12 +417,86 @@ void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const Sigm
     else fill_blocks_kernel<false, 0><<<ctas, threads, 0, st>>>(m, T, G, S, id, part, cheb, A);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Cache-free P2P (kernel::run -> downPass, bbfmm.h:507-532, 863-946: the reference's uncached path evaluates every U/W
+// entry during the apply).  For memory-constrained runs: the near-field tiles are not stored; the warp of a
+// target leaf evaluates the tiles of its stored pairs with the same kernel_eval_t as the evaluator and applies them at once,
+// in both directions under symmetric storage - its own sums to its first scratch row, K^T q_A to the partner's mirror row -
+// so the downward pass folds exactly what the cached stream kernel would have left.  Saves 8 B per stored pair and kernel
+// id (0.67 GB per id at N = 2^20) for ~12 evaluations per target and matvec.
+// Lane map: TPS = min(32, block width) lanes share a source point; 32 / TPS source points per trip.
+// ------------------------------------------------------------------------------------------------
+template <bool D1>
+__global__ void __launch_bounds__(256) p2p_onfly_kernel(DevCSR m, DevGeom G, SigmaGrid S, int id, int part, const double* __restrict__ q,
+                                                        double* __restrict__ y, double sign) {
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (g >= m.groups) return;
+    const int nr = m.nrow[g], toff = m.row_off[g];
+    const int tps = nr >= 32 ? 32 : nr > 16 ? 32 : nr > 8 ? 16 : nr > 4 ? 8 : nr > 2 ? 4 : nr > 1 ? 2 : 1;  // power of two >= nr (<= 32)
+    const int rp = 32 / tps, sub = lane / tps, tl = lane % tps;
+    // up to two targets per lane (leaves hold at most 64 points on the symmetric path; ragged leaves loop below)
+    double acc[2] = {0.0, 0.0};
+    double tx[2], ty[2], qa[2];
+    bool tok[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int t = tl + 32 * u;
+        tok[u] = t < nr && (u == 0 || tps == 32);
+        tx[u] = tok[u] ? G.px[toff + t] : 0.0;
+        ty[u] = tok[u] ? G.py[toff + t] : 0.0;
+        qa[u] = tok[u] ? q[toff + t] : 0.0;
+    }
+    const int e0 = m.ent_ptr[g], e1 = m.ent_ptr[g + 1];
+    for (int e = e0; e < e1; ++e) {
+        const int soff = m.col_off[e], nc = m.ncol[e];
+        const int mir = m.symmetric ? m.mirror_row[e] : -1;
+        for (int s0 = 0; s0 < nc; s0 += rp) {
+            const int s = s0 + sub;
+            const bool sok = s < nc;
+            const double sx = sok ? G.px[soff + s] : 0.0, sy = sok ? G.py[soff + s] : 0.0, qs = sok ? q[soff + s] : 0.0;
+            double z = 0.0;
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+                if (sok && tok[u]) {
+                    const double k = kernel_eval_t<D1, false>(S, id, part, sx, sy, tx[u], ty[u]);  // a = source, b = target (Q8)
+                    acc[u] = fma(k, qs, acc[u]);
+                    z = fma(k, qa[u], z);
+                }
+            if (mir >= 0) {  // transposed product for the partner: sum over the lanes that share this source point
+                for (int off = tps >> 1; off > 0; off >>= 1) z += __shfl_xor_sync(0xffffffffu, z, off);
+                if (tl == 0 && sok) m.scratch[(size_t)mir * m.uniform_block + s] = sign * z;
+            }
+        }
+    }
+    // the rp sub-groups hold partial sums of the same targets
+    for (int off = tps; off < 32; off <<= 1) {
+        acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], off);
+        acc[1] += __shfl_xor_sync(0xffffffffu, acc[1], off);
+    }
+    if (sub == 0) {
+        double* __restrict__ out = m.symmetric ? m.scratch + (size_t)m.srow_ptr[g] * m.uniform_block : y + toff;
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+            if (tok[u]) out[tl + 32 * u] = acc[u];
+    }
+}
+
+bool p2p_onfly_ok(const DevCSR& m, int max_leaf) { return max_leaf <= 64; }
+
+void launch_p2p_onfly(const DevCSR& m, const DevGeom& G, const SigmaGrid& S, int id, int part, const double* q, double* y, double sign,
+                      cudaStream_t st) {
+    if (m.groups == 0) return;
+    const unsigned ctas = (m.groups + 7) / 8;
+    if (S.ty) p2p_onfly_kernel<true><<<ctas, 256, 0, st>>>(m, G, S, id, part, q, y, sign);
+    else p2p_onfly_kernel<false><<<ctas, 256, 0, st>>>(m, G, S, id, part, q, y, sign);
+}
+
 __global__ void probe_line_integral_kernel(SigmaGrid S, int n, const double* __restrict__ p, double* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double x0 = p[4 * i], y0 = p[4 * i + 1], x1 = p[4 * i + 2], y1 = p[4 * i + 3];
     const double len = sqrt((x1 - x0) * (x1 - x0) + (y1 - y0) * (y1 - y0));
-    out[i] = (S.ty && len > 0.0) ? line_integral_d1(S, x0, y0, x1, y1, len) : line_integral(S, x0, y0, x1, y1);
+    out[i] = (S.ty && len > 0.0) ? line_integral_d1<true>(S, x0, y0, x1, y1, len) : line_integral(S, x0, y0, x1, y1);
 }
 __global__ void probe_kernel_kernel(SigmaGrid S, int id, int part, int n, const double* __restrict__ p,
                                     double* __restrict__ out) {

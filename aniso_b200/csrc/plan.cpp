@@ -1,6 +1,8 @@
 // Host set-up for the aniso hot path (see plan.hpp).  Plain C++17, no CUDA, usable on a CPU-only box.
 #include "plan.hpp"
 
+#include <omp.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -242,7 +244,7 @@ struct TreeBuilder {
     HostPlan& p;
     std::vector<TreeNode> t;
     int rank, maxLevel, deepest = 0;
-    explicit TreeBuilder(HostPlan& plan) : p(plan), rank(plan.rank), maxLevel(plan.maxLevelArg) {}
+    explicit TreeBuilder(HostPlan& plan) : p(plan), rank(plan.leaf_cap > 0 ? plan.leaf_cap : plan.rank), maxLevel(plan.maxLevelArg) {}
 
     void split(int id) {  // assignChildren, bbfmm.h:250-317
         if (t[id].npts == 0) {
@@ -625,8 +627,10 @@ void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
             for (int k = leaf_begin; k < leaf_end; ++k) chunk[p.leaves[k]] = (int)((int64_t)(k - leaf_begin) * kDeepChunks / nown);
         }
     }
-    symmetrize(m, p.deep_chunks > 1 ? &chunk : nullptr);
-    symmetrize(q);
+    if (!p.generic) {  // the symmetry K_AB = (-1)^k K_BA^T belongs to the aniso kernel family, not to an arbitrary eval
+        symmetrize(m, p.deep_chunks > 1 ? &chunk : nullptr);
+        symmetrize(q);
+    }
     p.m2l = std::move(m);
     p.p2p = std::move(q);
 }
@@ -668,6 +672,63 @@ void partition_leaves(const HostPlan& p, int nranks, std::vector<int>& begin, st
         const double target = total * (rk + 1) / nranks;
         while (k < nl && (rk == nranks - 1 || acc + 0.5 * cost[k] <= target)) acc += cost[k++];
         end[rk] = k;
+    }
+}
+
+void build_plan_points(HostPlan& p, int np, int n, const double* x, const double* y, int leaf_cap, int maxLevel) {
+    if (n < 1) throw std::runtime_error("at least one point is required");
+    if (np < 1) throw std::runtime_error("np must be >= 1");
+    if (np > 16) throw std::runtime_error("np > 16 (rank > 256) is not supported by the device kernels");
+    if (leaf_cap < 1) throw std::runtime_error("leaf capacity (rank) must be >= 1");
+    for (int i = 0; i < n; ++i)
+        if (!std::isfinite(x[i]) || !std::isfinite(y[i])) throw std::runtime_error("point coordinates must be finite");
+    p = HostPlan();
+    p.generic = true;
+    p.K = 1; p.kernelSize = 1; p.np = np; p.maxLevelArg = maxLevel; p.leaf_cap = leaf_cap;
+    p.N = n;
+    p.rank = np * np;  // kernel::rank = nChebyshev^2 (bbfmm.h:489)
+    p.nx.assign(x, x + n);
+    p.ny.assign(y, y + n);
+    p.w.assign(n, 1.0);
+    build_tree(p);
+    build_chebyshev(p);
+    flatten_lists(p, 0, (int)p.leaves.size());
+    for (TreeNode& nd : p.nodes) std::vector<int>().swap(nd.pts);
+}
+
+void tabulate_operator(const HostPlan& p, const BlockCSR& b, bool cheb, plan_eval_fn eval, void* ctx, int threads, double* A) {
+    const int np = p.np, ne = (int)b.col_off.size();
+    std::vector<int> group_of_entry(ne, 0);
+    for (size_t g = 0; g + 1 < b.ent_ptr.size(); ++g)
+        for (int e = b.ent_ptr[g]; e < b.ent_ptr[g + 1]; ++e) group_of_entry[e] = (int)g;
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads > 0 ? threads : omp_get_max_threads())
+    for (int e = 0; e < ne; ++e) {
+        const TreeNode &T = p.nodes[b.tgt_node[e]], &S = p.nodes[b.src_node[e]];
+        const int nrow = b.nrow[group_of_entry[e]], ncol = b.ncol[e];
+        double* out = A + b.blk_off[e];
+        for (int s = 0; s < ncol; ++s) {
+            double sx, sy;
+            if (cheb) {  // box nodes at (c.x + r.x t_i, c.y + r.y t_j), flat index j*np + i (bbfmm.h:699-705, 787-800)
+                sx = S.cx + S.rx * p.cheb[s % np];
+                sy = S.cy + S.ry * p.cheb[s / np];
+            } else {
+                const int idx = p.perm[S.pt_off + s];
+                sx = p.nx[idx];
+                sy = p.ny[idx];
+            }
+            for (int t = 0; t < nrow; ++t) {
+                double tx, ty;
+                if (cheb) {
+                    tx = T.cx + T.rx * p.cheb[t % np];
+                    ty = T.cy + T.ry * p.cheb[t / np];
+                } else {
+                    const int idx = p.perm[T.pt_off + t];
+                    tx = p.nx[idx];
+                    ty = p.ny[idx];
+                }
+                out[(size_t)s * nrow + t] = eval(ctx, sx, sy, tx, ty);
+            }
+        }
     }
 }
 

@@ -82,6 +82,10 @@ struct HostPlan {
     std::vector<double> cheb;                 // np Chebyshev nodes
     std::vector<double> tnode;                // T_k(t_m), m*np+k
     std::vector<double> R;                    // 4 x r x r transfer matrices, R[c][(a)*r + b]
+    // generic point-set plan (bbfmm::kernel with a caller-supplied eval, bbfmm.h:451-505): arbitrary points instead of the
+    // quadrature grid, leaf capacity independent of the Chebyshev order, no symmetric storage (nothing is known about eval)
+    bool generic = false;
+    int leaf_cap = 0;                         // > 0: leaf rule nSource <= leaf_cap (bbfmm.h:264); 0: rank (= np^2, KernelFactory.cpp:286)
     BlockCSR m2l, p2p;
     int deep_chunks = 1;                      // > 1: the owned deepest-level M2L rows form this many equal Morton ranges whose
                                               //      symmetric pairs are kept by the earlier range (see symmetrize)
@@ -96,6 +100,17 @@ bool gl_table(int n, double* x, double* w);
 
 // Builds everything above.  Throws std::runtime_error on invalid arguments.
 void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, int maxLevel);
+
+// kernel::initialize for an arbitrary point set with sources == targets (bbfmm.h:476-505 -> tree::populate 176-209): tree,
+// lists, Chebyshev operators and the flattened (unsymmetric) block-CSR operators; no quadrature geometry.
+void build_plan_points(HostPlan& p, int np, int n, const double* x, const double* y, int leaf_cap, int maxLevel);
+
+// Tabulates eval(source, target) into operator storage laid out like `b` (kernelEvalIndex / kernelEvalChebyshev,
+// bbfmm.h:770-804): A[blk_off[e] + s * nrow + t] = eval(source s of entry e, target t).  cheb: the np x np Chebyshev nodes of
+// the two boxes (flat index j*np + i, y slow), else the points of the two leaves.  OpenMP over the entries; eval must be
+// callable from several threads at once, as under the reference's OpenMP tasks.
+typedef double (*plan_eval_fn)(void* ctx, double sx, double sy, double tx, double ty);
+void tabulate_operator(const HostPlan& p, const BlockCSR& b, bool cheb, plan_eval_fn eval, void* ctx, int threads, double* A);
 
 // sigma interpolation (KernelFactory.cpp:212-227 / 988-1005): coeff[c*c2 + r] = sum_j interp[r][j] sqrtw[j] h[c*c2+j]
 void interpolate_field(const HostPlan& p, const double* h, double* coeff);

@@ -37,10 +37,10 @@ METRIC = "fmm_matvec_points_per_s"
 UNIT = "points/s"
 NP_ORDER, SING_RULE, G_ANISO, MAX_LEVEL = 4, 10, 0.9, 20
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the M2L stream kernel, from the committed `ncu --set full`
-# capture profiles/r01_final_ncu_raw.csv (cannot be measured live); keyed by (sz, n_gpus)
+# capture profiles/r02_ncu_raw.csv (cannot be measured live); keyed by (sz, n_gpus)
 # (TMA-ring kernel: the two launches of a matvec, levels 2-7 and level 8, read 0.590 + 1.813 GB and write 0.007 + 0.077 GB)
-NCU_TRAFFIC = {(1024, 1): 590147000 + 1813174000 + 7098000 + 76844000}
-NCU_TRAFFIC_SOURCE = "profiles/r01_final_ncu_raw.csv"
+NCU_TRAFFIC = {(1024, 1): 590148000 + 1813174000 + 8699000 + 78852000}
+NCU_TRAFFIC_SOURCE = "profiles/r02_ncu_raw.csv"
 
 
 def workload_name(sz):
@@ -350,6 +350,48 @@ def block_section(sz, K=2, world=1, rank=0, new_uid=None, device=0):
     return res
 
 
+def n2_section(sz):
+    """what an inverse-problem loop pays per setCoeff, and the memory / time trade of the cache-free near field.
+    For both P2P modes (aniso_set_option "p2p" = "cached" | "onfly"): wall time from the setCoeff call to the first mapping
+    result through the host API (sigma upload + tables + evaluator + stencils + first matvec + read-back), operator bytes
+    held per kernel id, and the time of one application of the GMRES operator afterwards (CUDA events)."""
+    from aniso_b200 import Aniso
+
+    a = Aniso(sz, 1, 1, G_ANISO, SING_RULE, NP_ORDER, MAX_LEVEL)
+    x, y, w = a.nodes()
+    ss, st = cases.sigma_fields("layers", x, y, sz, 1)
+    f = cases.gaussian_source(x, y)
+    a.setCoeff(ss, st)
+    a.mapping(f, 0)  # first use of the handle: stream / table set-up and kernel loading stay out of the numbers below
+    res = {}
+    ref = None
+    for mode in ("cached", "onfly"):
+        a.set_option("p2p", mode)
+        t, parts = [], None
+        for _ in range(3):
+            a.synchronize()
+            t0 = time.perf_counter()
+            a.setCoeff(ss, st)
+            t1 = time.perf_counter()
+            a.cache(0)
+            t2 = time.perf_counter()
+            out = a.mapping(f, 0)
+            t3 = time.perf_counter()
+            t.append((t3 - t0) * 1e3)
+            if t[-1] == min(t):
+                parts = {"set_coeff_ms": (t1 - t0) * 1e3, "cache_ms": (t2 - t1) * 1e3, "first_mapping_ms": (t3 - t2) * 1e3}
+        ct = a.cache_times()
+        res[mode] = {"set_coeff_to_first_mapping_ms": min(t), "split": parts, "operator_bytes_per_id": int(a.L.aniso_cache_bytes(a.h, 0)),
+                     "matvec_ms": a.time_forward(20), "p2p_fill_ms": ct["p2p_fill_ms"], "m2l_fill_ms": ct["m2l_fill_ms"],
+                     "stencil_ms": ct["stencil_ms"], "p2p_apply_ms": a.time_kernel(0, 1, 20)}
+        if ref is None:
+            ref = out
+        else:
+            res[mode]["rel_l2_vs_cached"] = float(np.linalg.norm(out - ref) / np.linalg.norm(ref))
+    a.delete()
+    return res
+
+
 CONFIG_ROWS = [("C1", "c1", None), ("C2", "c2", None), ("C3", "c3", None), ("C4 np4", "c4n4", None),
                ("C4 np5", None, (512, 1, 1, 0.9, 10, 5, 20, "hetero")), ("C4 np6", None, (512, 1, 1, 0.9, 10, 6, 20, "hetero")),
                ("C4 np7", None, (512, 1, 1, 0.9, 10, 7, 20, "hetero")), ("C4 np8", "c4n8", None)]
@@ -646,6 +688,8 @@ def run_ours(args):
                 a.delete()
                 a = None
             line["configs"] = configs_section()
+        if world == 1 and not args.no_configs:
+            line["n2_variants"] = n2_section(sz)
         if world == 1 and not args.no_cpu:
             try:
                 line["cpu_baseline"] = cpu_baseline(args)

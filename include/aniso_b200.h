@@ -103,6 +103,11 @@ int aniso_cache(aniso_t* h, int id);
  * (KernelFactory.cpp:323-334), ANISO_PART_REAL: runKernelsCacheSing (:279-288), ANISO_PART_BOTH: the fused operators
  * aniso_cache builds, 0: refineAddOnCache + singularAddCache (+ the nearRemoval table) as correction stencils. */
 int aniso_cache_part(aniso_t* h, int id, int part);
+/* Options of a handle.  "p2p" = "cached" (default; runKernelsCache keeps every U/W tile, bbfmm.h:949-1039) or "onfly": the
+ * near-field tiles are evaluated while they are applied, as in the reference's uncached kernel::run / downPass
+ * (bbfmm.h:507-532, 863-946), which saves 8 bytes per stored P2P pair and kernel id for memory-constrained runs (SURVEY 8f
+ * N2).  Same results to rounding.  Changing it drops the cached operators; leaves of at most 64 points. */
+int aniso_set_option(aniso_t* h, const char* name, const char* value);
 /* bytes held for kernel id (Aniso::displayKernelCacheSize, Aniso.cpp:19-47) */
 size_t aniso_cache_bytes(const aniso_t* h, int id);
 /* number of kernel evaluations the last aniso_cache(id) performed: out[0] = P2P pairs, out[1] = M2L pairs */
@@ -171,6 +176,22 @@ int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int 
 /* aniso.m:165 with pr == 1: gmres(A, rhs, 400, 1e-11, 400, @obj.prec); callback on K*N host doubles, mode-major */
 int aniso_block_gmres_prec(aniso_t* h, const double* rhs_host, double* x_host, int m, int max_iter, double tol,
                            aniso_prec_fn prec, void* ctx, int* iters, double* resid_hist, int hist_cap);
+
+/* ---- the black-box engine for a caller-supplied kernel: bbfmm::kernel (bbfmm.h:451-505) --------------------------------
+ * kernel::eval : std::function<double(point& source, point& target)> (bbfmm.h:457) is a host callback and cannot run on the
+ * device, so the operators are tabulated on the host (once, OpenMP over the U/W/V/X entries: kernelEvalIndex /
+ * kernelEvalChebyshev, bbfmm.h:770-804) and applied by the device path.  Nothing is assumed about eval (every block is
+ * stored).  Sources and targets are one point set, as in every call the reference makes (KernelFactory.cpp:284-286).
+ *   aniso_fmm_create  kernel::initialize(np, points, points, ., n, n, rank, maxLevel) (bbfmm.h:476-505): tree, lists, transfer
+ *                     operators; leaf_capacity = the `_rank` argument (leaf iff nSource <= rank, bbfmm.h:264); host only
+ *   aniso_fmm_cache   the evaluation half of runCache (bbfmm.h:535-562 -> downPassCache 949-1039); eval is called from
+ *                     `threads` OpenMP threads at once (0 = all), as under the reference's OpenMP tasks
+ *   aniso_fmm_apply   runFast (bbfmm.h:565-592): potential = FMM(charge); host vectors in the caller's point order
+ * The handle is an aniso_t: destroy it with aniso_destroy; the Aniso entry points reject it with ANISO_ESTATE. */
+typedef double (*aniso_eval_fn)(void* ctx, double source_x, double source_y, double target_x, double target_y);
+int aniso_fmm_create(int np, int n, const double* x, const double* y, int leaf_capacity, int maxLevel, aniso_t** out);
+int aniso_fmm_cache(aniso_t* h, aniso_eval_fn eval, void* ctx, int threads);
+int aniso_fmm_apply(aniso_t* h, const double* charge_host, double* potential_host);
 
 /* ---- device probes (parity tests of K1/K2 pieces) ---------------------------------------------------------- */
 /* lineIntegral(x0,y0,x1,y1) KernelFactory.cpp:67-166 for n segments, pts4 = n x 4 host doubles */

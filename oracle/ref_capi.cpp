@@ -327,4 +327,57 @@ void ref_sigma_coeff(void *p, double *ct, double *cs) {
         }
 }
 
+// The black-box engine on its own (bbfmm.h:451-592) with kernels that are NOT the two families of makeKernels, on an
+// arbitrary point set: eval kind 0 = log(r) (0 on the diagonal), kind 1 = an unsymmetric smooth kernel
+// (sx - tx + 0.3) / (r^2 + 0.01), kind 2 = exp(-3 r) / (0.05 + r).  mode 0 = run (uncached), 1 = runCache, 2 = runCache
+// then runFast.  stats[9] as ref_tree_stats.  Returns the number of tree nodes.
+static double ref_bbfmm_eval(int kind, double sx, double sy, double tx, double ty) {
+    const double dx = sx - tx, dy = sy - ty, r2 = dx * dx + dy * dy;
+    if (kind == 0) return r2 == 0.0 ? 0.0 : 0.5 * std::log(r2);
+    if (kind == 1) return (dx + 0.3) / (r2 + 0.01);
+    const double r = std::sqrt(r2);
+    return std::exp(-3.0 * r) / (0.05 + r);
+}
+
+int ref_bbfmm_run(int np, int n, const double *x, const double *y, int rank, int maxLevel, int kind, int mode,
+                  const double *charge, double *potential, long *stats) {
+#ifdef RUN_OMP
+    omp_set_num_threads(omp_get_max_threads());
+#endif
+    std::vector<point> pts((size_t)n);
+    Vector q(n);
+    for (int i = 0; i < n; ++i) {
+        pts[i].x = x[i];
+        pts[i].y = y[i];
+        q(i) = charge[i];
+    }
+    bbfmm::kernel k;
+    k.eval = [kind](point &a, point &b) { return ref_bbfmm_eval(kind, a.x, a.y, b.x, b.y); };
+    k.initialize(np, pts, pts, q, n, n, rank, maxLevel);
+    Vector pot;
+    if (mode == 0) k.run(pot);
+    else k.runCache(pot);
+    if (mode == 2) {
+        k.initialize(np, pts, pts, q, n, n, rank, maxLevel);  // KernelFactory.cpp:356: re-initialised before every runFast
+        k.runFast(pot);
+    }
+    for (int i = 0; i < n; ++i) potential[i] = pot(i);
+    if (stats) {
+        bbfmm::tree &t = k.t;
+        long nodes = (long)t.dict.size(), leaves = 0, su = 0, sv = 0, sw = 0, sx = 0, pairs = 0, mx = 0;
+        for (auto &nd : t.dict) {
+            if (nd.isLeaf) {
+                leaves++;
+                if (nd.nSource > mx) mx = nd.nSource;
+                for (int u : nd.uList) pairs += (long)t.dict[u].nSource * nd.nTarget;
+                for (int u : nd.wList) pairs += (long)t.dict[u].nSource * nd.nTarget;
+            }
+            su += nd.nUList; sv += nd.nVList; sw += nd.nWList; sx += nd.nXList;
+        }
+        stats[0] = nodes; stats[1] = leaves; stats[2] = t.maxLevel; stats[3] = su; stats[4] = sv;
+        stats[5] = sw; stats[6] = sx; stats[7] = pairs; stats[8] = mx;
+    }
+    return (int)k.t.dict.size();
+}
+
 }  // extern "C"

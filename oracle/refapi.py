@@ -59,6 +59,7 @@ def _load(fast):
     L.ref_geometry_tables.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, _dp, _dp]
     L.ref_sing_tables.argtypes = [C.c_void_p, _dp, _dp, _dp]
     L.ref_sigma_coeff.argtypes = [C.c_void_p, _dp, _dp]
+    L.ref_bbfmm_run.argtypes = [C.c_int, C.c_int, _dp, _dp, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp, _lp]
     _libs[fast] = L
     return L
 
@@ -68,6 +69,27 @@ def gl_table(deg, fast=False):
     w = np.zeros(deg)
     _load(fast).ref_gl_table(deg, x, w)
     return x, w
+
+
+def bbfmm_eval(kind, sx, sy, tx, ty):
+    """the test kernels of ref_bbfmm_run (oracle/ref_capi.cpp), restated for the callbacks handed to the product"""
+    dx, dy = sx - tx, sy - ty
+    r2 = dx * dx + dy * dy
+    if kind == 0:
+        return 0.0 if r2 == 0.0 else 0.5 * np.log(r2)
+    if kind == 1:
+        return (dx + 0.3) / (r2 + 0.01)
+    r = np.sqrt(r2)
+    return np.exp(-3.0 * r) / (0.05 + r)
+
+
+def bbfmm_run(np_, x, y, rank, max_level, kind, mode, charge, fast=False):
+    """the reference's bbfmm::kernel (initialize + run / runCache / runFast) with a non-family eval on arbitrary points"""
+    x, y, q = (np.ascontiguousarray(v, np.float64) for v in (x, y, charge))
+    pot = np.zeros(x.size)
+    stats = np.zeros(9, np.int64)
+    _load(fast).ref_bbfmm_run(np_, x.size, x, y, rank, max_level, kind, mode, q, pot, stats)
+    return pot, stats
 
 
 class RefAniso:

@@ -60,7 +60,7 @@ def test_block_gmres_vs_reference_golden(golden, name):
     xs, rc, it, hist = a.solve(charge)  # rhs = forward(charge); GMRES(400, 1e-11, 400) on I - mforward
     ref_it = int(g["gm_iters"])
     assert rc == int(g["gm_rc"]) == 0
-    assert abs(it - ref_it) <= 1, (it, ref_it, hist[-3:], g["gm_hist"][-3:])
+    assert it == ref_it, (it, ref_it, hist[-3:], g["gm_hist"][-3:])  # 43 / 44 / 55 with every orthogonalisation form (profiles/r02_gmres_gate.txt)
     assert rel(xs, g["gm_x"]) < 1e-8
     m = min(it, ref_it) - 2
     np.testing.assert_allclose(hist[:m], g["gm_hist"][:m], rtol=5e-3, atol=1e-8)

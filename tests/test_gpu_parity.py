@@ -101,18 +101,21 @@ def test_gmres_vs_reference_golden(golden, name):
     a.cache(0)
     b = a.mapping(cases.gaussian_source(x, y), 0)
     assert np.linalg.norm(b[::stride] - g["gm_b"]) / np.linalg.norm(g["gm_b"]) < TOL
-    # Gate: same iteration count.  One documented exception: when the reference's run ends while its residual is
-    # stalling at rounding level (a16: 4.7e-12, 1.7e-12, <1e-12 over its last three steps; the recurrence residual
-    # |s(i+1)|/||b|| then moves by O(1) relative under a 1e-15 perturbation of b or of the dot-product order, see
-    # tests/test_oracle.py::test_gmres), the count may differ by at most 2 provided our residual at the reference's
-    # last step is within 10x of tol (measured: 5.3e-12 with the prefix-table line integral, 4.4e-12 with the cell walk).  test_gmres_count_sensitivity_of_the_oracle shows the CPU oracle itself moving
-    # from 32 to 34 iterations on a16 under such a perturbation.
+    # Gate: the SAME iteration count as the compiled reference, on every fixture and every BASELINE configuration.
+    # profiles/r02_gmres_gate.txt records the counts of all orthogonalisation forms of the device GMRES: they equal the
+    # reference's everywhere, with one exception that does not depend on the form - a16, where the reference's run ends while
+    # its residual stalls at rounding level (4.7e-12, 1.7e-12, < 1e-12 over its last three steps) and the device operator,
+    # equal to the reference's to 2e-14, needs 34 steps instead of 32 with the reference's own modified Gram-Schmidt too.
+    # tests/test_oracle.py::test_gmres shows the CPU oracle itself moving from 32 to 34 under a 1e-15 perturbation of b.
     if stride == 1:
         b = g["gm_b"]
     xs, rc, it, hist = a.gmres(b, m=80, max_iter=400, tol=1e-12)
     ref_it = int(g["gm_iters"])
     assert rc == int(g["gm_rc"]) == 0
-    assert it == ref_it or (abs(it - ref_it) <= 2 and hist[min(it, ref_it)] < 1e-11), (it, ref_it, hist[-4:])
+    if name == "a16":
+        assert it == 34 and ref_it == 32 and hist[ref_it] < 1e-11, (it, ref_it, hist[-4:])
+    else:
+        assert it == ref_it, (it, ref_it, hist[-4:])
     assert abs(np.linalg.norm(xs) / float(g["gm_x_norm"]) - 1) < 1e-8
     assert np.linalg.norm(xs[::stride] - g["gm_x"]) / np.linalg.norm(g["gm_x"]) < 1e-8
     n = min(it, len(g["gm_hist"])) - 2
@@ -331,3 +334,101 @@ def test_stream_kernel_variants_agree(cfg, monkeypatch):
     assert rel(run(("ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS")), ring) < 1e-13
     if np_ in (5, 6):  # transposed product of a piece on the FP64 tensor cores (default) vs the shuffle butterfly
         assert rel(run(("ANISO_SYMG_NO_DMMA",)), ring) < 1e-13
+
+
+@pytest.mark.parametrize("name", ["a16", "b8d3", "nu6d5", "ml12d2", "h32", "c2"])
+def test_onfly_p2p_vs_reference_golden(golden, name):
+    """aniso_set_option("p2p", "onfly") (SURVEY 8f N2; the reference's uncached kernel::run / downPass, bbfmm.h:507-532,
+    863-946): near-field tiles evaluated during the apply instead of cached.  Same gates as the cached mode against the
+    compiled reference: fused matvec and the two FMM stages, every fixture kernel id (odd ids: sign of the transposed
+    tiles), uniform / deg 3 / ragged (non-symmetric storage) / maxLevel-capped / np 6 trees; no P2P bytes are held."""
+    g = golden(name)
+    a, x, y, w = make(name)
+    a.set_option("p2p", "onfly")
+    assert "p2p=onfly" in a.config()
+    stride = int(g["stride"])
+    f = {"f1": cases.tilted_source(x, y), "f2": cases.random_source(a.numberOfNodes, 1)}
+    for kid in g["ids"]:
+        kid = int(kid)
+        a.cache(kid)
+        assert a.cache_counts()["p2p"] == 0
+        for tag in ("f1", "f2"):
+            got = {"out": a.mapping(f[tag], kid), "imag_fmm": a.runKernelsFast(kid, f[tag] * w), "real_fmm": a.runKernelsFastSing(kid, f[tag] * w)}
+            for k, v in got.items():
+                key = "%s_id%d_%s" % (tag, kid, k)
+                err = np.linalg.norm(v[::stride] - g[key]) * np.sqrt(stride) / float(g[key + "_norm"])
+                assert err < TOL, (name, tag, kid, k, err)
+    a.set_option("p2p", "cached")  # drops the operators; the next call rebuilds them with cached tiles
+    a.cache(0)
+    cached_bytes, stored = a.displayKernelCacheSize()[0], a.cache_counts()["p2p"]
+    assert stored > 0
+    a.set_option("p2p", "onfly")
+    a.cache(0)  # the same single operator set, without the P2P tiles
+    assert abs(a.displayKernelCacheSize()[0] - (cached_bytes - 8e-6 * stored)) < 1e-9
+    a.set_option("p2p", "cached")
+    a.cache(0)
+    assert rel(a.mapping(f["f2"], 0)[::stride], g["f2_id0_out"]) < TOL
+    with pytest.raises(Exception):
+        a.set_option("p2p", "sometimes")
+    a.delete()
+
+
+@pytest.mark.parametrize("cfg", [(256, 1, 2, 0.9, 10, 8, 20, "hetero"), (512, 1, 2, 0.9, 10, 4, 20, "layers")])
+def test_onfly_p2p_matches_cached_at_size(cfg):
+    """64-point leaves (np 8: two targets per lane) and N = 2^18: on-the-fly against cached tiles of the same library, GMRES
+    included (same iteration count), and the block operator, which falls back to its loop form in this mode."""
+    from aniso_b200 import Aniso
+
+    sz, deg, K, g, sr, np_, ml, kind = cfg
+    a = Aniso(sz, deg, K, g, sr, np_, ml)
+    x, y, w = a.nodes()
+    ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+    a.setCoeff(ss, st)
+    f = cases.random_source(x.size, 9) * cases.gaussian_source(x, y) + 0.1 * cases.tilted_source(x, y)
+    u = cases.random_source(K * x.size, 5)
+    res = {}
+    for mode in ("cached", "onfly"):
+        a.set_option("p2p", mode)
+        for kid in range(a.kernelSize):
+            a.cache(kid)
+        b = a.mapping(cases.gaussian_source(x, y), 0)
+        res[mode] = ([a.mapping(f, kid) for kid in range(a.kernelSize)], a.gmres(b), a.mforward(u))
+    for kid in range(a.kernelSize):
+        assert rel(res["onfly"][0][kid], res["cached"][0][kid]) < 1e-12
+    assert res["onfly"][1][1] == res["cached"][1][1] == 0 and res["onfly"][1][2] == res["cached"][1][2]
+    assert rel(res["onfly"][1][0], res["cached"][1][0]) < 1e-9
+    assert rel(res["onfly"][2], res["cached"][2]) < 1e-11
+    a.delete()
+
+
+@pytest.mark.parametrize("name", ["a16", "b8d3"])
+def test_set_coeff_refills_operators_in_place(golden, name):
+    """setCoeff keeps the operator allocations and marks the sigma-dependent ones stale (an inverse-problem loop calls it every
+    iteration); the next use refills them in place.  A handle that first held the operators of ANOTHER sigma must give the
+    reference's results for the fixture's sigma - fused matvec, every stage (the real-part operators and the correction
+    stencils do not depend on sigma and are kept), GMRES - and go back and forth between the two fields reproducibly."""
+    g = golden(name)
+    a, x, y, w = make(name)          # fixture sigma, nothing cached yet
+    sz, deg = a.sz, a.deg
+    ss, st = cases.sigma_fields(cases.CASES[name][7], x, y, sz, deg)
+    other_s, other_t = 3.0 + 2.0 * np.sin(5 * x) * np.cos(3 * y), 6.5 + 2.0 * np.sin(5 * x) * np.cos(3 * y) + y
+    f = cases.random_source(a.numberOfNodes, 1)
+    a.setCoeff(other_s, other_t)
+    for kid in (0, 1):
+        a.cache(kid)
+    y_other = a.mapping(f, 0)
+    stages_other = a.mapping_stages(f, 1)
+    a.setCoeff(ss, st)               # stale; refilled by the calls below
+    for kid in (0, 1):
+        s = a.mapping_stages(f, kid)
+        s["fused"] = a.mapping(f, kid)
+        for k in STAGES + ("fused",):
+            key = "f2_id%d_%s" % (kid, "out" if k == "fused" else k)
+            assert rel(s[k], g[key]) < TOL, (name, kid, k, rel(s[k], g[key]))
+    assert rel(y_other, g["f2_id0_out"]) > 1e-3  # the two fields really differ
+    xs, rc, it, hist = a.gmres(g["gm_b"])
+    assert rc == 0 and rel(xs, g["gm_x"]) < 1e-8
+    a.setCoeff(other_s, other_t)
+    assert np.array_equal(a.mapping(f, 0), y_other)
+    assert np.array_equal(a.mapping_stages(f, 1)["real_fmm"], stages_other["real_fmm"])
+    a.delete()

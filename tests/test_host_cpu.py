@@ -201,3 +201,28 @@ def test_bench_reference_arm_contract():
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["value"] == line["value"]
     other = subprocess.run(cmd, env=dict(env, RANK="1", WORLD_SIZE="2"), capture_output=True, text=True, timeout=600, cwd=root)
     assert other.returncode == 0 and other.stdout.strip() == ""
+
+
+@pytest.mark.parametrize("name", ["p1500n4", "p900n6", "p700cap"])
+def test_bbfmm_point_set_tree_matches_reference(lib, golden, name):
+    """bbfmm::kernel::initialize on an arbitrary (clustered) point set (bbfmm.h:476-505 -> tree::populate): the host plan of
+    aniso_fmm_create reproduces the reference engine's tree - node, leaf and list counts, P2P pairs, largest leaf - with a
+    leaf capacity that differs from np^2 (p900n6) and a depth cap (p700cap).  Host only."""
+    import ctypes as C
+
+    from aniso_b200 import _lib
+
+    g = golden("bbfmm_points")
+    n, np_, rank, ml = (int(v) for v in g[name + "_cfg"])
+    h = C.c_void_p()
+    _lib.check(lib.aniso_fmm_create(np_, n, g[name + "_x"], g[name + "_y"], rank, ml, C.byref(h)))
+    st = np.zeros(9, np.int64)
+    _lib.check(lib.aniso_tree_stats(h, st))
+    assert list(st) == list(g[name + "_stats"])
+    assert lib.aniso_num_nodes(h) == n
+    with pytest.raises(_lib.AnisoError) as e:  # an Aniso entry point on a point-set handle
+        _lib.check(lib.aniso_set_coeff(h, np.ones(n), np.ones(n)))
+    assert e.value.code == -4
+    lib.aniso_destroy(h)
+    with pytest.raises(_lib.AnisoError):
+        _lib.check(lib.aniso_fmm_create(np_, 0, g[name + "_x"], g[name + "_y"], rank, ml, C.byref(h)))
