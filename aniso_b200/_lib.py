@@ -29,6 +29,7 @@ SIGNATURES = {
     "aniso_create_sharded": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int,
                                         C.c_int, C.c_void_p, C.c_int, C.POINTER(_H)]),
     "aniso_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "aniso_create_multi": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, _ip, C.POINTER(_H)]),
     "aniso_destroy": (C.c_int, [_H]),
     "aniso_num_nodes": (C.c_int, [_H]),
     "aniso_kernel_size": (C.c_int, [_H]),

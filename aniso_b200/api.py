@@ -25,12 +25,17 @@ class Aniso:
     """Aniso(ds, qr, ks, as, sr, fn, fm) == Aniso(geometry_size, geometry_degree, kernel_size, kernel_g,
     kernel_degree, np, maxLevel) (Aniso.h:14-15)."""
 
-    def __init__(self, ds, qr, ks, g, sr, fn, fm, nranks=1, rank=0, nccl_uid=None, device=-1):
+    def __init__(self, ds, qr, ks, g, sr, fn, fm, nranks=1, rank=0, nccl_uid=None, device=-1, devices=None):
+        """devices=[0, 1, ...]: one process drives these GPUs (aniso_create_multi); nranks / rank / nccl_uid: this process is
+        one rank of a process-per-GPU job (aniso_create_sharded)."""
         self.L = _lib.load()
         h = C.c_void_p()
         # MEX passes doubles and truncates with int(*p) (AnisoWrapper.cpp:22-24)
         args = (int(ds), int(qr), int(ks), float(g), int(sr), int(fn), int(fm))
-        if nranks == 1:
+        if devices is not None:
+            devs = np.ascontiguousarray(devices, np.int32)
+            _lib.check(self.L.aniso_create_multi(*args, devs.size, devs, C.byref(h)))
+        elif nranks == 1:
             _lib.check(self.L.aniso_create(*args, C.byref(h)))
         else:
             buf = C.create_string_buffer(bytes(nccl_uid), 128)

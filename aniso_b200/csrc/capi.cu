@@ -10,6 +10,7 @@
 #include <functional>
 #include <map>
 #include <stdexcept>
+#include <thread>
 #include <string>
 #include <utility>
 #include <vector>
@@ -27,6 +28,23 @@ static int fail(int code, const std::string& msg) {
     g_err = msg;
     return code;
 }
+// group handles (aniso_create_multi) --------------------------------------------------------------
+// fn(rank index, rank handle) on every rank at once, one thread each; the first failing rank's code and message are returned.
+// Like any SPMD program the ranks must fail or succeed together: the arguments are the same on all of them, so argument and
+// state errors are; a resource failure on one rank only (out of memory) would leave the others waiting in a collective.
+template <class F>
+static int multi_all(aniso_handle* h, F&& fn);
+#define MULTI_ALL(h, call)                                                                        \
+    if ((h) && !(h)->multi.empty()) return multi_all((h), [&](int rank_, aniso_t* r_) -> int {    \
+        (void)rank_;                                                                              \
+        return call;                                                                              \
+    })
+#define MULTI_R0(h) \
+    if ((h) && !(h)->multi.empty()) h = (h)->multi[0]
+#define MULTI_REJECT(h, what)                                                                                         \
+    if ((h) && !(h)->multi.empty())                                                                                    \
+    return fail(ANISO_EINVAL, what " takes device pointers of one rank: not available on a single-process multi-GPU handle")
+
 #define CK(call)                                                                                         \
     do {                                                                                                 \
         cudaError_t e_ = (call);                                                                         \
@@ -60,6 +78,11 @@ struct aniso_handle {
     bool overlap = true;
     // sharded upward pass (nranks > 1, complete uniform tree, equal shares): every rank runs P2M / M2M on its own sub-trees
     // only and the multipoles of all levels are all-gathered (one grouped NCCL call) instead of a replicated upward pass
+    // Single-process multi-GPU (aniso_create_multi): this handle is a GROUP that owns one sharded rank handle per device; it
+    // has no plan and no device state of its own.  Collective entry points run on all ranks at once, one host thread each
+    // (the rank handles talk NCCL to each other exactly as ranks in separate processes do); host-only getters go to rank 0.
+    std::vector<aniso_handle*> multi;
+    bool in_group = false;  // this is a rank handle of a group: its peers are threads of the same process
     bool p2p_onfly = false;  // aniso_set_option("p2p", "onfly"): near-field tiles evaluated during the apply, not cached
     bool up_sharded = false;
     // CUDA graphs of the operator y = x - mapping_0(sigma_s x), keyed by its two device pointers: the second application
@@ -421,6 +444,8 @@ void ensure_device(aniso_handle* h) {
             PeerComm& pc = h->peer;
             pc.P = h->nranks;
             pc.me = h->rank;
+            pc.in_process = h->in_group;
+            pc.device = h->device;
             peer_layout(pc, (size_t)N, (size_t)T.pack_tot * r * h->nranks, 1024);
             int ok = 1;
             try {
@@ -577,6 +602,11 @@ int aniso_create(int sz, int deg, int K, double g, int sr, int np, int maxLevel,
 }
 
 int aniso_destroy(aniso_t* h) {
+    if (h && !h->multi.empty()) {  // every rank leaves its communicator at the same time
+        multi_all(h, [&](int, aniso_t* r_) -> int { return aniso_destroy(r_); });
+        delete h;
+        return ANISO_OK;
+    }
     if (!h) return ANISO_OK;
     if (h->dev_ready) {
         cudaSetDevice(h->device);
@@ -617,10 +647,17 @@ int aniso_destroy(aniso_t* h) {
     return ANISO_OK;
 }
 
-int aniso_num_nodes(const aniso_t* h) { return h ? h->plan.N : fail(ANISO_EINVAL, "null handle"); }
-int aniso_kernel_size(const aniso_t* h) { return h ? h->plan.kernelSize : fail(ANISO_EINVAL, "null handle"); }
+int aniso_num_nodes(const aniso_t* h) {
+    MULTI_R0(h);
+    return h ? h->plan.N : fail(ANISO_EINVAL, "null handle");
+}
+int aniso_kernel_size(const aniso_t* h) {
+    MULTI_R0(h);
+    return h ? h->plan.kernelSize : fail(ANISO_EINVAL, "null handle");
+}
 
 int aniso_get_nodes(const aniso_t* h, double* x, double* y, double* w) {
+    MULTI_R0(h);
     if (!h) return fail(ANISO_EINVAL, "null handle");
     const size_t b = sizeof(double) * h->plan.N;
     if (x) std::memcpy(x, h->plan.nx.data(), b);
@@ -631,6 +668,7 @@ int aniso_get_nodes(const aniso_t* h, double* x, double* y, double* w) {
 
 int aniso_geometry_tables(const aniso_t* h, double* interp, double* nearMap, double* lnorm, double* rx, double* ry,
                           double* rw) {
+    MULTI_R0(h);
     if (!h) return fail(ANISO_EINVAL, "null handle");
     const HostPlan& p = h->plan;
     auto cp = [](double* d, const std::vector<double>& v) {
@@ -641,6 +679,7 @@ int aniso_geometry_tables(const aniso_t* h, double* interp, double* nearMap, dou
 }
 
 int aniso_sing_tables(const aniso_t* h, double* sx, double* sy, double* sw) {
+    MULTI_R0(h);
     if (!h) return fail(ANISO_EINVAL, "null handle");
     const HostPlan& p = h->plan;
     if (sx) std::memcpy(sx, p.singX.data(), p.singX.size() * sizeof(double));
@@ -650,12 +689,14 @@ int aniso_sing_tables(const aniso_t* h, double* sx, double* sy, double* sw) {
 }
 
 int aniso_tree_stats(const aniso_t* h, int64_t out[9]) {
+    MULTI_R0(h);
     if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
     for (int i = 0; i < 9; ++i) out[i] = h->plan.stats[i];
     return ANISO_OK;
 }
 
 int aniso_tree_nodes(const aniso_t* h, int cap, double* geom, int* info) {
+    MULTI_R0(h);
     if (!h) return fail(ANISO_EINVAL, "null handle");
     const HostPlan& p = h->plan;
     const int nn = (int)p.nodes.size();
@@ -668,6 +709,7 @@ int aniso_tree_nodes(const aniso_t* h, int cap, double* geom, int* info) {
 }
 
 int aniso_node_lists(const aniso_t* h, int node, int cap, int* ids, int* kinds) {
+    MULTI_R0(h);
     if (!h || node < 0 || node >= (int)h->plan.nodes.size()) return fail(ANISO_EINVAL, "bad node");
     const TreeNode& n = h->plan.nodes[node];
     int c = 0;
@@ -684,12 +726,14 @@ int aniso_node_lists(const aniso_t* h, int node, int cap, int* ids, int* kinds) 
 }
 
 int aniso_slot_permutation(const aniso_t* h, int* perm) {
+    MULTI_R0(h);
     if (!h || !perm) return fail(ANISO_EINVAL, "null pointer");
     std::memcpy(perm, h->plan.perm.data(), sizeof(int) * h->plan.N);
     return ANISO_OK;
 }
 
 int aniso_partition(const aniso_t* h, int nranks, int rank, int* slot_begin, int* slot_end, int* nleaves) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h && nranks >= 1 && rank >= 0 && rank < nranks, "bad arguments");
     std::vector<int> lb, le;
@@ -705,6 +749,11 @@ int aniso_partition(const aniso_t* h, int nranks, int rank, int* slot_begin, int
 }
 
 int aniso_owned_range(const aniso_t* h, int* slot_begin, int* slot_end) {
+    if (h && !h->multi.empty()) {  // one process holds every row
+        if (slot_begin) *slot_begin = 0;
+        if (slot_end) *slot_end = h->multi[0]->plan.N;
+        return ANISO_OK;
+    }
     if (!h) return fail(ANISO_EINVAL, "null handle");
     if (slot_begin) *slot_begin = h->slot0;
     if (slot_end) *slot_end = h->slot0 + h->nown;
@@ -1196,6 +1245,7 @@ void from_slots(aniso_handle* h, const double* dev_own, double* host) {
 extern "C" {
 
 int aniso_set_coeff(aniso_t* h, const double* sigma_s, const double* sigma_t) {
+    MULTI_ALL(h, aniso_set_coeff(r_, sigma_s, sigma_t));
     API_BEGIN
     REQUIRE(h && sigma_s && sigma_t, "null pointer");
     if (h->plan.generic) throw std::logic_error("this handle is a bbfmm::kernel point-set handle (aniso_fmm_create), not an Aniso object");
@@ -1223,6 +1273,7 @@ int aniso_set_coeff(aniso_t* h, const double* sigma_s, const double* sigma_t) {
 }
 
 int aniso_interpolation(aniso_t* h, const double* f, double* coeff) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h && f && coeff, "null pointer");
     if (h->plan.generic) throw std::logic_error("this handle is a bbfmm::kernel point-set handle (aniso_fmm_create), not an Aniso object");
@@ -1239,6 +1290,7 @@ int aniso_interpolation(aniso_t* h, const double* f, double* coeff) {
 }
 
 int aniso_sigma_coeff(aniso_t* h, double* ct, double* cs) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h, "null handle");
     if (!h->coeff_set) throw std::logic_error("setCoeff has not been called");
@@ -1249,6 +1301,7 @@ int aniso_sigma_coeff(aniso_t* h, double* ct, double* cs) {
 }
 
 int aniso_cache(aniso_t* h, int id) {
+    MULTI_ALL(h, aniso_cache(r_, id));
     API_BEGIN
     REQUIRE(h, "null handle");
     check_id(h, id);
@@ -1262,6 +1315,7 @@ int aniso_cache(aniso_t* h, int id) {
 }
 
 int aniso_cache_part(aniso_t* h, int id, int part) {
+    MULTI_ALL(h, aniso_cache_part(r_, id, part));
     API_BEGIN
     REQUIRE(h && part >= 0 && part <= 3, "bad arguments");
     check_id(h, id);
@@ -1275,6 +1329,11 @@ int aniso_cache_part(aniso_t* h, int id, int part) {
 }
 
 size_t aniso_cache_bytes(const aniso_t* h, int id) {
+    if (h && !h->multi.empty()) {
+        size_t b = 0;
+        for (const aniso_handle* r : h->multi) b += aniso_cache_bytes(r, id);
+        return b;
+    }
     if (!h) return 0;
     size_t b = 0;
     for (auto& kv : h->ops)
@@ -1284,6 +1343,7 @@ size_t aniso_cache_bytes(const aniso_t* h, int id) {
 }
 
 int aniso_cache_counts(const aniso_t* h, int64_t out[2]) {
+    MULTI_R0(h);
     if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
     out[0] = h->fill_counts[0];
     out[1] = h->fill_counts[1];
@@ -1291,12 +1351,14 @@ int aniso_cache_counts(const aniso_t* h, int64_t out[2]) {
 }
 
 int aniso_cache_times(const aniso_t* h, double out[3]) {
+    MULTI_R0(h);
     if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
     for (int i = 0; i < 3; ++i) out[i] = h->fill_ms[i];
     return ANISO_OK;
 }
 
 int aniso_mapping_dev(aniso_t* h, const double* charge_dev, int id, double* out_dev) {
+    MULTI_REJECT(h, "aniso_mapping_dev");
     API_BEGIN
     REQUIRE(h && charge_dev && out_dev, "null pointer");
     check_id(h, id);
@@ -1308,6 +1370,7 @@ int aniso_mapping_dev(aniso_t* h, const double* charge_dev, int id, double* out_
 }
 
 int aniso_forward_dev(aniso_t* h, const double* x_dev, double* y_dev) {
+    MULTI_REJECT(h, "aniso_forward_dev");
     API_BEGIN
     REQUIRE(h && x_dev && y_dev, "null pointer");
     ensure_device(h);
@@ -1320,6 +1383,7 @@ int aniso_forward_dev(aniso_t* h, const double* x_dev, double* y_dev) {
 }
 
 int aniso_mapping(aniso_t* h, const double* charge, int id, double* out) {
+    MULTI_ALL(h, aniso_mapping(r_, charge, id, out));
     API_BEGIN
     REQUIRE(h && charge && out, "null pointer");
     check_id(h, id);
@@ -1333,6 +1397,7 @@ int aniso_mapping(aniso_t* h, const double* charge, int id, double* out) {
 }
 
 static int stage_fmm(aniso_t* h, int id, int part, const double* f, double* ret) {
+    MULTI_ALL(h, stage_fmm(r_, id, part, f, ret));
     API_BEGIN
     REQUIRE(h && f && ret, "null pointer");
     check_id(h, id);
@@ -1349,6 +1414,7 @@ int aniso_run_kernels_fast(aniso_t* h, int id, const double* f, double* ret) { r
 int aniso_run_kernels_fast_sing(aniso_t* h, int id, const double* f, double* ret) { return stage_fmm(h, id, PART_REAL, f, ret); }
 
 static int stage_stencil(aniso_t* h, int id, int which, const double* f, double* ret) {
+    MULTI_ALL(h, stage_stencil(r_, id, which, f, ret));
     API_BEGIN
     REQUIRE(h && f && ret, "null pointer");
     check_id(h, id);
@@ -1372,6 +1438,7 @@ int aniso_refine_add_on_fast(aniso_t* h, int id, const double* f, double* ret) {
 int aniso_singular_add_fast(aniso_t* h, int id, const double* fc, double* ret) { return stage_stencil(h, id, 9, fc, ret); }
 
 int aniso_line_integral(aniso_t* h, int n, const double* pts4, double* out) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h && pts4 && out && n >= 0, "bad arguments");
     ensure_device(h);
@@ -1389,6 +1456,7 @@ int aniso_line_integral(aniso_t* h, int n, const double* pts4, double* out) {
 }
 
 int aniso_kernel_eval(aniso_t* h, int id, int part, int n, const double* pts4, double* out) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h && pts4 && out && n >= 0 && part >= 1 && part <= 3, "bad arguments");
     check_id(h, id);
@@ -1998,6 +2066,7 @@ extern "C" {
 
 int aniso_gmres_dev(aniso_t* h, const double* b, double* x, int m, int max_iter, double tol, int* iters, double* hist,
                     int hist_cap) {
+    MULTI_REJECT(h, "aniso_gmres_dev");
     API_BEGIN
     REQUIRE(h && b && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
     ensure_device(h);
@@ -2013,6 +2082,17 @@ int aniso_gmres_dev(aniso_t* h, const double* b, double* x, int m, int max_iter,
 
 int aniso_gmres_prec(aniso_t* h, const double* b, double* x, int m, int max_iter, double tol, aniso_prec_fn prec, void* ctx,
                      int* iters, double* hist, int hist_cap) {
+    if (h && !h->multi.empty()) {
+        if (prec) return fail(ANISO_EINVAL, "a preconditioner callback on a single-process multi-GPU handle would be called from every rank's thread at once: not supported");
+        std::vector<int> its(h->multi.size(), 0);
+        std::vector<std::vector<double>> hs(h->multi.size(), std::vector<double>(hist ? (size_t)std::max(hist_cap, 0) : 0));
+        const int rc = multi_all(h, [&](int k, aniso_t* r_) -> int {
+            return aniso_gmres_prec(r_, b, x, m, max_iter, tol, nullptr, nullptr, &its[k], hist ? hs[k].data() : nullptr, hist_cap);
+        });
+        if (iters) *iters = its[0];
+        if (hist && hist_cap > 0) std::memcpy(hist, hs[0].data(), sizeof(double) * hist_cap);
+        return rc;
+    }
     API_BEGIN
     REQUIRE(h && b && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
     ensure_device(h);
@@ -2043,6 +2123,7 @@ int aniso_gmres(aniso_t* h, const double* b, double* x, int m, int max_iter, dou
 }
 
 int aniso_block_forward_dev(aniso_t* h, const double* u_dev, int weighted, double* out_dev) {
+    MULTI_REJECT(h, "aniso_block_forward_dev");
     API_BEGIN
     REQUIRE(h && u_dev && out_dev, "null pointer");
     ensure_device(h);
@@ -2054,6 +2135,7 @@ int aniso_block_forward_dev(aniso_t* h, const double* u_dev, int weighted, doubl
 }
 
 int aniso_block_forward(aniso_t* h, const double* u, int weighted, double* out) {
+    MULTI_ALL(h, aniso_block_forward(r_, u, weighted, out));
     API_BEGIN
     REQUIRE(h && u && out, "null pointer");
     ensure_device(h);
@@ -2094,11 +2176,23 @@ static int block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int
 
 int aniso_block_gmres_dev(aniso_t* h, const double* rhs_dev, double* x_dev, int m, int max_iter, double tol, int* iters,
                           double* hist, int hist_cap) {
+    MULTI_REJECT(h, "aniso_block_gmres_dev");
     return block_gmres_dev(h, rhs_dev, x_dev, m, max_iter, tol, nullptr, nullptr, iters, hist, hist_cap);
 }
 
 int aniso_block_gmres_prec(aniso_t* h, const double* rhs, double* x, int m, int max_iter, double tol, aniso_prec_fn prec, void* ctx,
                            int* iters, double* hist, int hist_cap) {
+    if (h && !h->multi.empty()) {
+        if (prec) return fail(ANISO_EINVAL, "a preconditioner callback on a single-process multi-GPU handle would be called from every rank's thread at once: not supported");
+        std::vector<int> its(h->multi.size(), 0);
+        std::vector<std::vector<double>> hs(h->multi.size(), std::vector<double>(hist ? (size_t)std::max(hist_cap, 0) : 0));
+        const int rc = multi_all(h, [&](int k, aniso_t* r_) -> int {
+            return aniso_block_gmres_prec(r_, rhs, x, m, max_iter, tol, nullptr, nullptr, &its[k], hist ? hs[k].data() : nullptr, hist_cap);
+        });
+        if (iters) *iters = its[0];
+        if (hist && hist_cap > 0) std::memcpy(hist, hs[0].data(), sizeof(double) * hist_cap);
+        return rc;
+    }
     API_BEGIN
     REQUIRE(h && rhs && x && iters && m >= 1 && max_iter >= 0, "bad arguments");
     ensure_device(h);
@@ -2127,9 +2221,16 @@ int aniso_block_gmres(aniso_t* h, const double* rhs, double* x, int m, int max_i
     return aniso_block_gmres_prec(h, rhs, x, m, max_iter, tol, nullptr, nullptr, iters, hist, hist_cap);
 }
 
-void* aniso_stream(aniso_t* h) { return h ? (void*)h->st : nullptr; }
-int aniso_device(const aniso_t* h) { return h ? h->device : fail(ANISO_EINVAL, "null handle"); }
+void* aniso_stream(aniso_t* h) {
+    if (h && !h->multi.empty()) return nullptr;  // a group has one stream per rank
+    return h ? (void*)h->st : nullptr;
+}
+int aniso_device(const aniso_t* h) {
+    MULTI_R0(h);
+    return h ? h->device : fail(ANISO_EINVAL, "null handle");
+}
 int aniso_synchronize(aniso_t* h) {
+    MULTI_ALL(h, aniso_synchronize(r_));
     API_BEGIN
     REQUIRE(h, "null handle");
     if (h->dev_ready) CK(cudaStreamSynchronize(h->st));
@@ -2138,6 +2239,7 @@ int aniso_synchronize(aniso_t* h) {
     API_END
 }
 int aniso_dev_alloc(aniso_t* h, size_t bytes, void** out) {
+    MULTI_REJECT(h, "aniso_dev_alloc");
     API_BEGIN
     REQUIRE(h && out, "null pointer");
     ensure_device(h);
@@ -2147,6 +2249,7 @@ int aniso_dev_alloc(aniso_t* h, size_t bytes, void** out) {
     API_END
 }
 int aniso_dev_free(aniso_t* h, void* p) {
+    MULTI_REJECT(h, "aniso_dev_free");
     API_BEGIN
     REQUIRE(h, "null handle");
     CK(cudaSetDevice(h->device));
@@ -2155,6 +2258,7 @@ int aniso_dev_free(aniso_t* h, void* p) {
     API_END
 }
 int aniso_host_alloc(aniso_t* h, size_t bytes, void** out) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h && out, "null pointer");
     ensure_device(h);
@@ -2164,6 +2268,7 @@ int aniso_host_alloc(aniso_t* h, size_t bytes, void** out) {
     API_END
 }
 int aniso_host_free(aniso_t* h, void* p) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h, "null handle");
     if (p) CK(cudaFreeHost(p));
@@ -2171,6 +2276,7 @@ int aniso_host_free(aniso_t* h, void* p) {
     API_END
 }
 int aniso_to_slots(aniso_t* h, const double* host, double* dev) {
+    MULTI_REJECT(h, "aniso_to_slots");
     API_BEGIN
     REQUIRE(h && host && dev, "null pointer");
     ensure_device(h);
@@ -2180,6 +2286,7 @@ int aniso_to_slots(aniso_t* h, const double* host, double* dev) {
     API_END
 }
 int aniso_from_slots(aniso_t* h, const double* dev, double* host) {
+    MULTI_REJECT(h, "aniso_from_slots");
     API_BEGIN
     REQUIRE(h && host && dev, "null pointer");
     ensure_device(h);
@@ -2188,8 +2295,16 @@ int aniso_from_slots(aniso_t* h, const double* dev, double* host) {
     return ANISO_OK;
     API_END
 }
-int64_t aniso_launch_count(const aniso_t* h) { return h ? h->launches : 0; }
+int64_t aniso_launch_count(const aniso_t* h) {
+    if (h && !h->multi.empty()) {
+        int64_t n = 0;
+        for (const aniso_handle* r : h->multi) n += r->launches;
+        return n;
+    }
+    return h ? h->launches : 0;
+}
 int aniso_apply_bytes(const aniso_t* h, int64_t out[3]) {
+    MULTI_R0(h);
     if (!h || !out) return fail(ANISO_EINVAL, "null pointer");
     // bytes the streaming kernels must move per matvec: stored operator blocks (half of the pairs under symmetric
     // storage) plus one scratch row (8R bytes) written per target and per dropped block
@@ -2199,6 +2314,7 @@ int aniso_apply_bytes(const aniso_t* h, int64_t out[3]) {
     return ANISO_OK;
 }
 int aniso_time_forward(aniso_t* h, int reps, double* ms) {
+    MULTI_REJECT(h, "aniso_time_forward");
     API_BEGIN
     REQUIRE(h && ms && reps >= 1, "bad arguments");
     ensure_device(h);
@@ -2226,6 +2342,7 @@ int aniso_time_forward(aniso_t* h, int reps, double* ms) {
 }
 
 int aniso_set_option(aniso_t* h, const char* name, const char* value) {
+    MULTI_ALL(h, aniso_set_option(r_, name, value));
     API_BEGIN
     REQUIRE(h && name && value, "null pointer");
     const std::string n(name), v(value);
@@ -2249,6 +2366,7 @@ int aniso_set_option(aniso_t* h, const char* name, const char* value) {
 }
 
 const char* aniso_get_config(const aniso_t* h) {
+    MULTI_R0(h);
     // the environment switches that select a code path (development A/B switches; all default off), as one string a
     // benchmark line can carry so that a run describes itself
     static thread_local std::string cfg;
@@ -2271,6 +2389,7 @@ const char* aniso_get_config(const aniso_t* h) {
 }
 
 int aniso_time_kernel(aniso_t* h, int id, int which, int reps, double* ms) {
+    MULTI_REJECT(h, "aniso_time_kernel");
     API_BEGIN
     REQUIRE(h && ms && reps >= 1 && (which == 0 || which == 1), "bad arguments");
     check_id(h, id);
@@ -2335,6 +2454,7 @@ double* noalloc_scratch_ptr(int device) {  // the caller has made `device` curre
 }  // namespace
 
 extern "C" int aniso_line_integral_noalloc(aniso_t* h, int n, const double* pts4, double* out) {
+    MULTI_R0(h);
     API_BEGIN
     REQUIRE(h && pts4 && out && n >= 0, "bad arguments");
     if (n > ANISO_NOALLOC_MAX_SEGMENTS)
@@ -2389,6 +2509,7 @@ int aniso_fmm_create(int np, int n, const double* x, const double* y, int leaf_c
 }
 
 int aniso_fmm_cache(aniso_t* h, aniso_eval_fn eval, void* ctx, int threads) {
+    MULTI_REJECT(h, "aniso_fmm_cache");
     API_BEGIN
     REQUIRE(h && eval, "null pointer");
     if (!h->plan.generic) throw std::logic_error("aniso_fmm_cache needs a handle made by aniso_fmm_create");
@@ -2416,6 +2537,7 @@ int aniso_fmm_cache(aniso_t* h, aniso_eval_fn eval, void* ctx, int threads) {
 }
 
 int aniso_fmm_apply(aniso_t* h, const double* charge, double* potential) {
+    MULTI_REJECT(h, "aniso_fmm_apply");
     API_BEGIN
     REQUIRE(h && charge && potential, "null pointer");
     if (!h->plan.generic) throw std::logic_error("aniso_fmm_apply needs a handle made by aniso_fmm_create");
@@ -2430,3 +2552,58 @@ int aniso_fmm_apply(aniso_t* h, const double* charge, double* potential) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// Single-process multi-GPU (SURVEY 5 / 8b "one process, 8 streams"; aniso_create_sharded(..., ndev, devs) of the required
+// export list): main.cpp:7-150 and AnisoWrapper.cpp:10-138 are single-process callers, so a handle that needs one process
+// per GPU leaves them on one device.  A group handle owns one sharded rank handle per device; each collective call is run
+// by one host thread per rank (CUDA device bound per thread), and the ranks exchange over NCCL exactly as in the
+// process-per-GPU form (CUDA IPC cannot map a buffer into the process that owns it, so the peer-memory collectives fall
+// back to NCCL here).  Host vectors are shared: inputs are read by every rank, each rank writes its own rows of an output.
+// ---------------------------------------------------------------------------------------------------
+template <class F>
+static int multi_all(aniso_handle* h, F&& fn) {
+    const int P = (int)h->multi.size();
+    std::vector<int> rc(P, 0);
+    std::vector<std::string> msg(P);
+    std::vector<std::thread> th;
+    th.reserve(P);
+    for (int k = 0; k < P; ++k)
+        th.emplace_back([&, k] {
+            if (h->multi[k] && h->multi[k]->device >= 0) cudaSetDevice(h->multi[k]->device);
+            rc[k] = fn(k, h->multi[k]);
+            if (rc[k] < 0) msg[k] = aniso_last_error();
+        });
+    for (auto& t : th) t.join();
+    for (int k = 0; k < P; ++k)
+        if (rc[k] < 0) return fail(rc[k], "rank " + std::to_string(k) + ": " + msg[k]);
+    return rc[0];
+}
+
+extern "C" int aniso_create_multi(int sz, int deg, int K, double g, int sr, int np, int maxLevel, int ndev, const int* devs,
+                                  aniso_t** out) {
+    API_BEGIN
+    REQUIRE(out && ndev >= 1 && ndev <= 64 && (devs || ndev == 1), "bad arguments");
+    if (ndev == 1) return aniso_create_sharded(sz, deg, K, g, sr, np, maxLevel, 1, 0, nullptr, devs ? devs[0] : -1, out);
+    for (int a = 0; a < ndev; ++a)
+        for (int b = a + 1; b < ndev; ++b) REQUIRE(devs[a] != devs[b] && devs[a] >= 0 && devs[b] >= 0, "device ordinals must be distinct and non-negative");
+    unsigned char uid[128];
+    int rc = aniso_nccl_unique_id(uid);
+    if (rc < 0) return rc;
+    aniso_handle* grp = new aniso_handle();
+    grp->multi.assign(ndev, nullptr);
+    rc = multi_all(grp, [&](int k, aniso_t*) -> int {  // the host plans (tree, lists) are built side by side
+        return aniso_create_sharded(sz, deg, K, g, sr, np, maxLevel, ndev, k, uid, devs[k], &grp->multi[k]);
+    });
+    for (aniso_handle* r : grp->multi)
+        if (r) r->in_group = true;
+    if (rc < 0) {
+        const std::string keep = aniso_last_error();
+        for (aniso_handle* r : grp->multi) delete r;  // no device state yet
+        delete grp;
+        return fail(rc, keep);
+    }
+    *out = grp;
+    return ANISO_OK;
+    API_END
+}

@@ -100,17 +100,35 @@ void peer_open(PeerComm& pc, const std::function<void(const void*, void*, size_t
     *pc.err = 0;
     PCK(cudaHostGetDevicePointer(&pc.err_dev, pc.err, 0));
     PCK(cudaDeviceSynchronize());
-    cudaIpcMemHandle_t mine;
-    PCK(cudaIpcGetMemHandle(&mine, pc.local));
-    std::vector<cudaIpcMemHandle_t> all(pc.P);
+    // what a rank publishes: an IPC handle for ranks in other processes, the raw pointer and its device for ranks that are
+    // threads of this process (CUDA IPC cannot map a buffer into the process that owns it; unified addressing plus peer
+    // access makes the pointer itself usable there)
+    struct Item {
+        cudaIpcMemHandle_t ipc;
+        void* ptr;
+        int dev;
+    };
+    Item mine;
+    std::memset(&mine, 0, sizeof(mine));
+    if (!pc.in_process) PCK(cudaIpcGetMemHandle(&mine.ipc, pc.local));
+    mine.ptr = pc.local;
+    mine.dev = pc.device;
+    std::vector<Item> all(pc.P);
     exchange(&mine, all.data(), sizeof(mine));
     for (int r = 0; r < pc.P; ++r) {
         if (r == pc.me) {
             pc.remote[r] = pc.local;
             continue;
         }
+        if (pc.in_process) {
+            const cudaError_t e = cudaDeviceEnablePeerAccess(all[r].dev, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) throw std::runtime_error(std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+            cudaGetLastError();
+            pc.remote[r] = static_cast<char*>(all[r].ptr);
+            continue;
+        }
         void* p = nullptr;
-        PCK(cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess));
+        PCK(cudaIpcOpenMemHandle(&p, all[r].ipc, cudaIpcMemLazyEnablePeerAccess));
         pc.remote[r] = static_cast<char*>(p);
     }
     pc.ready = true;
@@ -119,7 +137,7 @@ void peer_open(PeerComm& pc, const std::function<void(const void*, void*, size_t
 void peer_close(PeerComm& pc) {
     if (!pc.local) return;
     for (int r = 0; r < pc.P; ++r)
-        if (r != pc.me && pc.remote[r]) cudaIpcCloseMemHandle(pc.remote[r]);
+        if (r != pc.me && pc.remote[r] && !pc.in_process) cudaIpcCloseMemHandle(pc.remote[r]);
     cudaFree(pc.local);
     cudaFree(pc.counter);
     if (pc.err) cudaFreeHost(pc.err);

@@ -20,6 +20,8 @@ struct PeerFlags {
 struct PeerComm {
     int P = 0, me = 0;
     bool ready = false;
+    bool in_process = false;  // all ranks live in this process (aniso_create_multi): raw pointers + peer access instead of CUDA IPC
+    int device = 0;
     char* local = nullptr;
     char* remote[kMaxPeers] = {};
     size_t bytes = 0, off_flags = 0, off_red = 0, off_x = 0, off_mc = 0, nx = 0, nmc = 0;

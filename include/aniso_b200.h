@@ -59,6 +59,15 @@ int aniso_create_sharded(int geometry_size, int geometry_degree, int kernel_size
                          int np, int maxLevel, int nranks, int rank, const void* nccl_unique_id, int device,
                          aniso_t** out);
 int aniso_nccl_unique_id(void* out128);
+/* Same partition, ONE process: a group handle that drives `ndev` GPUs (device ordinals `devs`) of this node from a
+ * single-process caller such as main.cpp:7-150 or the MEX gateway AnisoWrapper.cpp:10-138 (SURVEY 8b:
+ * aniso_create_sharded(..., ndev, devs)).  Every entry point that takes HOST vectors works on the group as on a one-GPU
+ * handle - inputs are read by all ranks, outputs come back complete - and is run by one host thread per GPU inside the
+ * call.  Entry points that take device pointers or a stream (`*_dev`, aniso_stream, aniso_to_slots, ...) return
+ * ANISO_EINVAL on a group, and a preconditioner callback is not accepted (it would run on every rank's thread at once).
+ * ndev == 1 gives an ordinary handle on devs[0]. */
+int aniso_create_multi(int geometry_size, int geometry_degree, int kernel_size, double kernel_g, int kernel_degree, int np,
+                       int maxLevel, int ndev, const int* devs, aniso_t** out);
 /* MEX op 'delete' AnisoWrapper.cpp:27-31 / Aniso::~Aniso */
 int aniso_destroy(aniso_t* h);
 

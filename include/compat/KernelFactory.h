@@ -142,7 +142,19 @@ protected:
     }
     void ensure() {
         if (handle_) return;
-        ck(aniso_create(sz, deg, kernelArg_, g_, singDegree_, np, maxLevel, &handle_));
+        // ANISO_DEVICES=0,1,2,3: the single-process callers of the reference (main.cpp, the MEX gateway) drive several
+        // GPUs through one group handle (aniso_create_multi); unset: the current device
+        std::vector<int> devs;
+        if (const char* env = std::getenv("ANISO_DEVICES"))
+            for (const char* q = env; *q;) {
+                char* end = nullptr;
+                const long d = std::strtol(q, &end, 10);
+                if (end == q) break;
+                devs.push_back((int)d);
+                q = *end ? end + 1 : end;
+            }
+        if (devs.size() > 1) ck(aniso_create_multi(sz, deg, kernelArg_, g_, singDegree_, np, maxLevel, (int)devs.size(), devs.data(), &handle_));
+        else ck(aniso_create(sz, deg, kernelArg_, g_, singDegree_, np, maxLevel, &handle_));
         loadGeometry(handle_);
         if (sigma_t.row() != numberOfNodes) sigma_t = Vector(numberOfNodes);
         if (sigma_s.row() != numberOfNodes) sigma_s = Vector(numberOfNodes);

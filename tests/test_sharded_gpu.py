@@ -37,3 +37,63 @@ def test_sharded_handle_matches_one_rank(world):
     errs = [ln for ln in out.stderr.splitlines() if "Error" in ln or "assert" in ln.lower() or "aniso" in ln]
     assert out.returncode == 0, (out.stdout[-1500:], errs[-12:])
     assert out.stdout.count("SHARDED_OK") == world, out.stdout[-3000:]
+
+
+@pytest.mark.parametrize("ndev", [2, 4])
+@pytest.mark.timeout(600)
+def test_single_process_group_handle_matches_one_gpu(ndev):
+    """aniso_create_multi: ONE process drives ndev GPUs through a group handle (what the reference's single-process callers
+    main.cpp / AnisoWrapper.cpp need).  Every host-vector entry point must behave as on a one-GPU handle and return complete
+    vectors: fused matvec for even and odd kernel ids, the stage entry points, GMRES (same iteration count), the block
+    operator, the cache-free P2P option; device-pointer entry points are rejected."""
+    if _ngpus() < ndev:
+        pytest.skip("needs %d GPUs" % ndev)
+    import ctypes as C
+
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import cases
+    from aniso_b200 import Aniso, AnisoError, _lib
+
+    def rel(a, b):
+        return float(np.linalg.norm(a - b) / np.linalg.norm(b))
+
+    for name in ("c2", "nu6d5", "k3h16"):
+        sz, deg, K, g, sr, np_, ml, kind = cases.CASES.get(name) or cases.BLOCK_CASES[name]
+        grp = Aniso(sz, deg, K, g, sr, np_, ml, devices=list(range(ndev)))
+        one = Aniso(sz, deg, K, g, sr, np_, ml)
+        x, y, w = grp.nodes()
+        n = x.size
+        assert grp.owned_range() == (0, n)
+        ss, st = cases.sigma_fields(kind, x, y, sz, deg)
+        for o in (grp, one):
+            o.setCoeff(ss, st)
+        f = cases.random_source(n, 11) * cases.gaussian_source(x, y) + 0.1 * cases.tilted_source(x, y)
+        for kid in sorted({0, min(1, grp.kernelSize - 1), grp.kernelSize - 1}):
+            for o in (grp, one):
+                o.cache(kid)
+            assert rel(grp.mapping(f, kid), one.mapping(f, kid)) < 1e-12, (name, kid)
+        sg, so = grp.mapping_stages(f, 0), one.mapping_stages(f, 0)
+        for k in so:
+            assert rel(sg[k], so[k]) < 1e-12, (name, k)
+        b = one.mapping(cases.gaussian_source(x, y), 0)
+        xg, rcg, itg, hg = grp.gmres(b)
+        xo, rco, ito, ho = one.gmres(b)
+        assert rcg == rco == 0 and itg == ito and rel(xg, xo) < 1e-9, (name, itg, ito)
+        if K > 1:
+            u = cases.random_source(K * n, 5)
+            assert rel(grp.mforward(u), one.mforward(u)) < 1e-11
+            xs_g, rc_g, it_g, _ = grp.solve(u)
+            xs_o, rc_o, it_o, _ = one.solve(u)
+            assert rc_g == rc_o == 0 and it_g == it_o and rel(xs_g, xs_o) < 1e-8
+        grp.set_option("p2p", "onfly")
+        grp.cache(0)
+        assert rel(grp.mapping(f, 0), one.mapping(f, 0)) < 1e-12
+        with pytest.raises(AnisoError):  # device-pointer entry points belong to one rank
+            _lib.check(grp.L.aniso_forward_dev(grp.h, C.c_void_p(8), C.c_void_p(8)))
+        with pytest.raises(AnisoError):
+            grp.gmres(b, prec=lambda r: r)
+        assert grp.displayKernelCacheSize()[0] > 0 and "ranks=%d" % ndev in grp.config()
+        grp.delete()
+        one.delete()
