@@ -252,6 +252,8 @@ DevCSR upload_csr(aniso_handle* h, const BlockCSR& b) {
 
 void ensure_device(aniso_handle* h) {
     if (h->dev_ready) return;
+    if (h->st || !h->allocs.empty())  // an earlier attempt failed half-way (e.g. in ncclCommInitRank): do not build on its leftovers
+        throw std::logic_error("device set-up of this handle failed earlier; destroy it and create a new one");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) {
@@ -608,10 +610,11 @@ int aniso_destroy(aniso_t* h) {
         return ANISO_OK;
     }
     if (!h) return ANISO_OK;
-    if (h->dev_ready) {
-        cudaSetDevice(h->device);
-        cudaStreamSynchronize(h->st);
-        if (h->pt.on && h->pt.reps > 0) {
+    // also after a device set-up that failed half-way (dev_ready still false): whatever exists is released
+    if (h->dev_ready || h->st || !h->allocs.empty()) {
+        if (h->device >= 0) cudaSetDevice(h->device);
+        if (h->st) cudaStreamSynchronize(h->st);
+        if (h->dev_ready && h->pt.on && h->pt.reps > 0) {
             phase_mark(h, nullptr);
             fprintf(stderr, "[aniso rank %d] time line over %d matvecs (us after the start; [b] = bulk stream):", h->rank, h->pt.reps);
             for (size_t i = 1; i < h->pt.sum.size(); ++i) fprintf(stderr, " %s %.1f", h->pt.name[i], 1e3 * h->pt.sum[i] / h->pt.reps);
@@ -620,7 +623,7 @@ int aniso_destroy(aniso_t* h) {
         drop_graphs(h);
         if (h->peer.local) {
             // no rank may unmap or free its region while a peer can still store into it: a barrier first
-            if (h->comm && h->nccl && h->d_scal) {
+            if (h->comm && h->nccl && h->d_scal && h->st) {
                 h->nccl->AllReduce(h->d_scal, h->d_scal, 1, ncclDouble, ncclSum, h->comm, h->st);
                 cudaStreamSynchronize(h->st);
             }
@@ -630,7 +633,7 @@ int aniso_destroy(aniso_t* h) {
         for (void* p : h->allocs) cudaFree(p);
         if (h->pinned) cudaFreeHost(h->pinned);
         if (h->pinned_small) cudaFreeHost(h->pinned_small);
-        cudaStreamSynchronize(h->st_bulk);
+        if (h->st_bulk) cudaStreamSynchronize(h->st_bulk);
         for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join, h->ev_own})
             if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : h->copy_ev) cudaEventDestroy(e);
@@ -640,8 +643,9 @@ int aniso_destroy(aniso_t* h) {
         if (h->st_aux) cudaStreamDestroy(h->st_aux);
         for (cudaEvent_t e : h->ev_chunk)
             if (e) cudaEventDestroy(e);
-        cudaStreamDestroy(h->st_bulk);
-        cudaStreamDestroy(h->st);
+        if (h->st_bulk) cudaStreamDestroy(h->st_bulk);
+        if (h->st) cudaStreamDestroy(h->st);
+        cudaGetLastError();
     }
     delete h;
     return ANISO_OK;
@@ -1446,11 +1450,15 @@ int aniso_line_integral(aniso_t* h, int n, const double* pts4, double* out) {
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede lineIntegral");
     check_probe_points(n, pts4);
     double* d = dalloc<double>(h, (size_t)5 * n);
+    struct Guard {  // the temporary is released on the error paths too
+        aniso_handle* h;
+        void* p;
+        ~Guard() { dfree(h, p); }
+    } guard{h, d};
     CK(cudaMemcpyAsync(d, pts4, sizeof(double) * 4 * n, cudaMemcpyHostToDevice, h->st));
     LAUNCH(h, launch_probe_line_integral(h->S, n, d, d + 4 * (size_t)n, h->st));
     CK(cudaMemcpyAsync(out, d + 4 * (size_t)n, sizeof(double) * n, cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
-    dfree(h, d);
     return ANISO_OK;
     API_END
 }
@@ -1465,11 +1473,15 @@ int aniso_kernel_eval(aniso_t* h, int id, int part, int n, const double* pts4, d
     if (!h->coeff_set) throw std::logic_error("setCoeff must precede kernel evaluation");
     check_probe_points(n, pts4);
     double* d = dalloc<double>(h, (size_t)5 * n);
+    struct Guard {
+        aniso_handle* h;
+        void* p;
+        ~Guard() { dfree(h, p); }
+    } guard{h, d};
     CK(cudaMemcpyAsync(d, pts4, sizeof(double) * 4 * n, cudaMemcpyHostToDevice, h->st));
     LAUNCH(h, launch_probe_kernel(h->S, id, part, n, d, d + 4 * (size_t)n, h->st));
     CK(cudaMemcpyAsync(out, d + 4 * (size_t)n, sizeof(double) * n, cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
-    dfree(h, d);
     return ANISO_OK;
     API_END
 }
@@ -1795,6 +1807,7 @@ using DevPrec = std::function<void(double*)>;
 // also written to the input buffer), so that it can be a captured graph
 int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* x, int m, int max_iter, double tol, int* iters,
                double* hist, int hist_cap, const DevPrec* P = nullptr, const DevOp* Afix = nullptr) {
+    if (m < 1 || m > 4096) throw std::invalid_argument("restart length m out of range (1 .. 4096)");  // before any allocation
     const int ldh = m + 1;
     GmresWork g{h, n, m, nullptr, nullptr, nullptr};
     // device scalars of a solve: projections h1 / h2 (m + 2 each), then the state of the device-side Givens recurrence

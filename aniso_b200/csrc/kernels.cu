@@ -60,7 +60,38 @@ __device__ __forceinline__ double sigma_eval(const SigmaGrid& S, double x, doubl
 // then splits at the cell edges; every piece is integrated with the deg-point Gauss rule, which is exact for the
 // degree-2(deg-1) polynomial along the ray, so the value equals the sum over the cells the ray crosses.  That sum
 // is what this cell walk computes: crossing parameters are evaluated directly (not accumulated) per step.
-__device__ double line_integral(const SigmaGrid& S, double x0, double y0, double x1, double y1) {
+// DEG > 0: the degree is a compile-time constant (2 ... 5 are instantiated).  Both one-dimensional Legendre recurrences are
+// run once per point into registers and followed by the double sum, instead of re-running the y recurrence (one FP64
+// division per step) for every x order; the operations and their order are those of sigma_poly, so the values are the same.
+template <int DEG>
+__device__ __forceinline__ double sigma_poly_t(const double* __restrict__ chat, int deg, double x, double y) {
+    if (DEG == 0) return sigma_poly(chat, deg, x, y);
+    constexpr int D = DEG > 0 ? DEG : 1;
+    double px[D], py[D];
+    px[0] = 1.0;
+    py[0] = 1.0;
+    if (D > 1) {
+        px[1] = x;
+        py[1] = y;
+    }
+#pragma unroll
+    for (int n = 2; n < D; ++n) {
+        px[n] = 2.0 * x * px[n - 1] - px[n - 2] - (x * px[n - 1] - px[n - 2]) / (double)n;
+        py[n] = 2.0 * y * py[n - 1] - py[n - 2] - (y * py[n - 1] - py[n - 2]) / (double)n;
+    }
+    double acc = 0;
+#pragma unroll
+    for (int n = 0; n < D; ++n) {
+        double inner = 0;
+#pragma unroll
+        for (int k = 0; k < D; ++k) inner += py[k] * __ldg(chat + n * D + k);
+        acc += px[n] * inner;
+    }
+    return acc;
+}
+
+template <int DEG>
+__device__ double line_integral_t(const SigmaGrid& S, double x0, double y0, double x1, double y1) {
     const int sz = S.sz;
     const double ddx = x1 - x0, ddy = y1 - y0;
     const double len = sqrt(ddx * ddx + ddy * ddy);
@@ -74,7 +105,16 @@ __device__ double line_integral(const SigmaGrid& S, double x0, double y0, double
     double ty = cy != ey ? ((double)by * S.h - y0) * ivy : inf;
     const int nsteps = abs(ex - cx) + abs(ey - cy);
     double tcur = 0.0, acc = 0.0;
-    const int deg = S.deg;
+    const int deg = DEG ? DEG : S.deg;
+    constexpr int GD = DEG > 0 ? DEG : 1;
+    double gx[GD], gw[GD];  // the Gauss rule in registers when the degree is known
+    if (DEG > 0) {
+#pragma unroll
+        for (int i = 0; i < GD; ++i) {
+            gx[i] = __ldg(S.glx + i);
+            gw[i] = __ldg(S.glw + i);
+        }
+    }
     for (int step = 0; step <= nsteps; ++step) {
         const double tn = step == nsteps ? 1.0 : fmin(tx, ty);
         const double* __restrict__ chat = S.chat + (size_t)(cx * sz + cy) * S.c2;
@@ -85,9 +125,14 @@ __device__ double line_integral(const SigmaGrid& S, double x0, double y0, double
             const double xa = x0 + tcur * ddx, ya = y0 + tcur * ddy, xb = x0 + tn * ddx, yb = y0 + tn * ddy;
             const double mx = (xa + xb) / 2, my = (ya + yb) / 2, hx = (xa - xb) / 2, hy = (ya - yb) / 2;
             double s = 0;
-            for (int i = 0; i < deg; ++i) {
-                const double g = __ldg(S.glx + i);
-                s += sigma_poly(chat, deg, mx + hx * g, my + hy * g) * __ldg(S.glw + i);
+            if (DEG > 0) {
+#pragma unroll
+                for (int i = 0; i < GD; ++i) s += sigma_poly_t<DEG>(chat, deg, mx + hx * gx[i], my + hy * gx[i]) * gw[i];
+            } else {
+                for (int i = 0; i < deg; ++i) {
+                    const double g = __ldg(S.glx + i);
+                    s += sigma_poly(chat, deg, mx + hx * g, my + hy * g) * __ldg(S.glw + i);
+                }
             }
             acc += s * (tn - tcur) * 0.5;
         }
@@ -105,6 +150,16 @@ __device__ double line_integral(const SigmaGrid& S, double x0, double y0, double
         tcur = tn;
     }
     return acc * len;
+}
+
+__device__ double line_integral(const SigmaGrid& S, double x0, double y0, double x1, double y1) {
+    switch (S.deg) {
+        case 2: return line_integral_t<2>(S, x0, y0, x1, y1);
+        case 3: return line_integral_t<3>(S, x0, y0, x1, y1);  // data.cfg (BASELINE config 1)
+        case 4: return line_integral_t<4>(S, x0, y0, x1, y1);
+        case 5: return line_integral_t<5>(S, x0, y0, x1, y1);
+        default: return line_integral_t<0>(S, x0, y0, x1, y1);
+    }
 }
 
 // deg == 1 fast path.  sigma is constant per cell, so along a grid line its integral is piecewise linear:
