@@ -226,3 +226,39 @@ def test_bbfmm_point_set_tree_matches_reference(lib, golden, name):
     lib.aniso_destroy(h)
     with pytest.raises(_lib.AnisoError):
         _lib.check(lib.aniso_fmm_create(np_, 0, g[name + "_x"], g[name + "_y"], rank, ml, C.byref(h)))
+
+
+def test_group_handle_host_side(lib):
+    """aniso_create_multi (one process, several GPUs) without a GPU: creating the group is host-only; the host getters answer
+    from rank 0, the group owns every row, compute entry points fail loudly on the ranks (no CPU fallback), device-pointer
+    entry points and preconditioner callbacks are rejected, bad device lists are refused."""
+    import ctypes as C
+
+    from aniso_b200 import Aniso, AnisoError, _lib
+
+    a = Aniso(16, 1, 2, 0.5, 10, 4, 20, devices=[0, 1, 2])
+    one = Aniso(16, 1, 2, 0.5, 10, 4, 20)
+    assert a.numberOfNodes == one.numberOfNodes == 256 and a.kernelSize == 3
+    assert a.owned_range() == (0, 256)
+    assert a.tree_stats() == one.tree_stats()
+    for u, v in zip(a.nodes(), one.nodes()):
+        assert np.array_equal(u, v)
+    assert np.array_equal(a.slot_permutation(), one.slot_permutation())
+    with pytest.raises(AnisoError) as e:
+        a.setCoeff(np.ones(256), np.ones(256))
+    assert e.value.code == -2 and "rank" in str(e.value) and "no CPU fallback" in str(e.value)
+    with pytest.raises(AnisoError) as e:
+        _lib.check(lib.aniso_forward_dev(a.h, C.c_void_p(8), C.c_void_p(8)))
+    assert e.value.code == -1 and "single-process multi-GPU" in str(e.value)
+    with pytest.raises(AnisoError) as e:
+        a.gmres(np.ones(256), prec=lambda r: r)
+    assert e.value.code == -1
+    assert lib.aniso_stream(a.h) is None
+    a.delete()
+    one.delete()
+    h = C.c_void_p()
+    with pytest.raises(AnisoError):  # the same device twice
+        _lib.check(lib.aniso_create_multi(16, 1, 2, 0.5, 10, 4, 20, 2, np.array([1, 1], np.int32), C.byref(h)))
+    _lib.check(lib.aniso_create_multi(16, 1, 2, 0.5, 10, 4, 20, 1, np.array([0], np.int32), C.byref(h)))  # ndev 1: a plain handle
+    assert lib.aniso_num_nodes(h) == 256
+    lib.aniso_destroy(h)
