@@ -809,7 +809,9 @@ void free_caches(aniso_handle* h) {
 
 // The probes evaluate the kernel family between arbitrary points.  Every point the matvec itself uses (nodes, Chebyshev
 // nodes of tree boxes) lies inside the unit square, where the table line integral needs no clamp of its crossing
-// indices; points outside it are rejected here instead of being extended by the reference's getRow/getCol clamp.
+// indices.  The reference does not guard its cell look-ups at all (getRow/getCol, KernelFactory.cpp:392-401, are a bare
+// floor: a point outside the square indexes outside the coefficient grid); here such points are rejected, and a coordinate
+// of exactly 1 is counted to the last cell.
 void check_probe_points(int n, const double* pts4) {
     for (int i = 0; i < 4 * n; ++i)
         if (!(pts4[i] >= 0.0 && pts4[i] <= 1.0)) throw std::invalid_argument("probe point outside the unit square");

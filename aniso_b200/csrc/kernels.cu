@@ -16,7 +16,7 @@ namespace an {
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ int cell_index(double v, int sz) {  // getRow/getCol, KernelFactory.cpp:392-401
     int c = (int)floor(v * sz);
-    return min(max(c, 0), sz - 1);
+    return min(max(c, 0), sz - 1);  // the reference does not clamp: see magic_floor
 }
 
 // sum_{n,k} P_n(x) P_k(y) chat[n*deg+k] with the libstdc++ tr1 Legendre recurrence at GLOBAL coordinates
@@ -171,8 +171,10 @@ __device__ double line_integral(const SigmaGrid& S, double x0, double y0, double
 // one independent term per crossed line of the MINOR axis (on average 3.4x fewer terms than cells crossed, none at
 // all for axis-aligned rays), each two 16-byte table reads and a handful of FMAs.  Exact for the piecewise-constant
 // interpolant like the cell walk (the reference's bisection + one-point Gauss rule, KernelFactory.cpp:67-190).
-// CLAMP: the getRow/getCol clamp of the reference (KernelFactory.cpp:392-401), needed for caller-supplied points on or
-// beyond the edge of the unit square (the probe entry points).  Every point the matvec path itself evaluates - quadrature
+// CLAMP: the cell index is clamped to [0, sz - 1].  The reference's getRow/getCol are a bare int(floor(v * sz))
+// (KernelFactory.cpp:392-401): for a coordinate of exactly 1 they index cell sz, one past the grid (undefined behaviour there;
+// the compiled reference crashes on such probe points).  Here a caller-supplied point on the upper edge is counted to the
+// last cell instead; the probe entry points use this form.  Every point the matvec path itself evaluates - quadrature
 // nodes, Chebyshev nodes of tree boxes, which lie inside the bounding box of the nodes - is at least half a cell inside the
 // square, where round(v*sz - 0.5) is in [0, sz - 1] by itself; the evaluator instantiates CLAMP = false (the double
 // fmin / fmax pair was 15 % of its instructions, profiles/r02_ncu_raw.csv + source page).
@@ -188,9 +190,13 @@ __device__ __forceinline__ double magic_floor(double v, double szd, double top, 
 
 // crossing points lie between the two (clamped) end points: no clamp needed (the tables carry one entry of padding for the
 // one-ulp case v == 1)
-__device__ __forceinline__ double magic_floor_inner(double v, double szd, int& j) {
+// CLAMP (probe points only): a ray that ends on the upper edge v == 1 exactly AND on a grid line of its minor axis has its
+// last crossing at the end point itself, where the unclamped index would be sz
+template <bool CLAMP>
+__device__ __forceinline__ double magic_floor_inner(double v, double szd, double top, int& j) {
     const double MAGIC = 6755399441055744.0;
-    const double t = fma(v, szd, -0.5) + MAGIC;
+    double t = fma(v, szd, -0.5) + MAGIC;
+    if (CLAMP) t = fmin(t, top);
     j = __double2loint(t);
     return t - MAGIC;
 }
@@ -225,7 +231,7 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
         for (; k + 2 <= ncross; k += 2) {  // two crossings per trip: two independent table reads in flight
             const double vb0 = fma(fma(bd, h, -u0), slope, v0), vb1 = fma(fma(bd + sd, h, -u0), slope, v0);
             int ja, jb;
-            const double jda = magic_floor_inner(vb0, szd, ja), jdb = magic_floor_inner(vb1, szd, jb);
+            const double jda = magic_floor_inner<CLAMP>(vb0, szd, top, ja), jdb = magic_floor_inner<CLAMP>(vb1, szd, top, jb);
             const double2 d0 = __ldg(row + ja), d1 = __ldg(row + rstep + jb);
             cr0 += fma(d0.y, fma(-jda, h, vb0), d0.x);
             cr1 += fma(d1.y, fma(-jdb, h, vb1), d1.x);
@@ -235,7 +241,7 @@ __device__ __forceinline__ double line_integral_d1(const SigmaGrid& S, double x0
         if (k < ncross) {
             const double vb0 = fma(fma(bd, h, -u0), slope, v0);
             int ja;
-            const double jda = magic_floor_inner(vb0, szd, ja);
+            const double jda = magic_floor_inner<CLAMP>(vb0, szd, top, ja);
             const double2 d0 = __ldg(row + ja);
             cr0 += fma(d0.y, fma(-jda, h, vb0), d0.x);
         }

@@ -42,6 +42,9 @@ public:
     index_t nChebyshev = 0, rank = 0, maxLevel = 0;
     Vector chargeTree;
     size_t cacheBytes = 0;  // bytes of device-resident operator blocks (the reference's Cache, bbfmm.h:466, lives on the device)
+    // bbfmm.h:466.  Kept so that code which names or walks `Cache` compiles; it stays EMPTY here: the operator blocks are
+    // device memory (use cacheBytes / Aniso::displayKernelCacheSize for their size).
+    vector<vector<Matrix>> Cache;
 
     void initialize(index_t _nChebyshev, vector<point>& _source, vector<point>& _target, Vector& _charge, index_t _nSource,
                     index_t _nTarget, index_t _rank, index_t _maxLevel) {

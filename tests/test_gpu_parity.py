@@ -432,3 +432,39 @@ def test_set_coeff_refills_operators_in_place(golden, name):
     assert np.array_equal(a.mapping(f, 0), y_other)
     assert np.array_equal(a.mapping_stages(f, 1)["real_fmm"], stages_other["real_fmm"])
     a.delete()
+
+
+@pytest.mark.parametrize("name", ["a16", "b8d3"])
+def test_probe_points_on_and_outside_the_domain_edge(name):
+    """Caller-supplied probe points (aniso_line_integral / aniso_kernel_eval).  The reference's getRow/getCol are a bare
+    floor(v * sz) (KernelFactory.cpp:392-401): defined for coordinates in [0, 1), out of bounds at exactly 1 (the compiled
+    reference crashes there) and beyond.  Points on the lower edge and just inside the upper edge must equal the CPU oracle;
+    a coordinate of exactly 1 is counted to the last cell (finite, equal to the value just inside to rounding); points
+    outside the square are rejected with ANISO_EINVAL instead of being read out of the tables' bounds."""
+    from aniso_b200 import AnisoError
+    from oracle import oracleapi
+
+    sz, deg, K, g, sr, np_, ml, kind = cases.CASES[name]
+    a, x, y, w = make(name)
+    o = oracleapi.OracleAniso(sz, deg, K, g, sr, np_, ml)
+    o.set_coeff(*cases.sigma_fields(kind, x, y, sz, deg))
+    hi = np.nextafter(1.0, 0.0)
+    edge = np.array([[0.0, 0.3, hi, 0.8], [0.25, 0.0, 0.75, hi], [hi, hi, 0.0, 0.0], [0.0, 0.0, hi, 0.0], [0.0, 0.2, 0.0, 0.9],
+                     [0.5, 0.0, 0.1, 0.0], [0.0, hi, hi, 0.0], [0.3, 0.3, hi, hi]])
+    want = np.array([o.line_integral(*p) for p in edge])
+    np.testing.assert_allclose(a.line_integral(edge), want, rtol=1e-12)
+    np.testing.assert_allclose(a.line_integral_noalloc(edge), want, rtol=1e-12)
+    for part, opart in ((1, 0), (2, 1)):
+        got = a.kernel_eval(0, part, edge)
+        ref = np.array([o.kernel_eval(0, opart, *p) for p in edge])
+        np.testing.assert_allclose(got, ref, rtol=1e-11, atol=1e-13)
+    top = np.where(edge == hi, 1.0, edge)  # exactly on the upper edge: last cell, no out-of-bounds read
+    got_top = a.line_integral(top)
+    assert np.all(np.isfinite(got_top))
+    np.testing.assert_allclose(got_top, want, rtol=1e-9)
+    for bad in ([-0.1, 0.5, 0.5, 0.5], [0.5, 0.5, 1.0000001, 0.5], [0.5, float("nan"), 0.5, 0.5]):
+        for fn in (a.line_integral, a.line_integral_noalloc, lambda p: a.kernel_eval(0, 2, p)):
+            with pytest.raises(AnisoError) as e:
+                fn(np.array([bad]))
+            assert e.value.code == -1
+    a.delete()
