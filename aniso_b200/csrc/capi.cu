@@ -73,7 +73,8 @@ struct aniso_handle {
     // second stream of the matvec: the two big operator streams (P2P, deepest-level M2L) run here while the
     // latency-bound tree passes run on `st`; forked and joined with events inside every run_fmm
     cudaStream_t st_bulk = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr, ev_own = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_leaf = nullptr, ev_join = nullptr, ev_own = nullptr, ev_p2p = nullptr;
+    bool split_tail = false;  // ANISO_SPLIT_TAIL=1 (one rank, complete tree): second half of the P2P stream behind the deep M2L stream, leaf pass under it
     cudaEvent_t ev_chunk[kDeepChunks] = {};  // chunked tail: the deepest-level M2L rows of chunk c have been streamed
     bool overlap = true;
     // sharded upward pass (nranks > 1, complete uniform tree, equal shares): every rank runs P2M / M2M on its own sub-trees
@@ -270,11 +271,12 @@ void ensure_device(aniso_handle* h) {
         CK(cudaStreamCreateWithPriority(&h->st, cudaStreamNonBlocking, hi));
         CK(cudaStreamCreateWithPriority(&h->st_bulk, cudaStreamNonBlocking, lo));
     }
-    for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join, &h->ev_own}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    for (cudaEvent_t* e : {&h->ev_fork, &h->ev_leaf, &h->ev_join, &h->ev_own, &h->ev_p2p}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     for (auto& e : h->ev_chunk) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     h->overlap = getenv("ANISO_NO_OVERLAP") == nullptr;
     h->pt.on = getenv("ANISO_PHASE_TIMES") != nullptr;
-    h->use_graphs = getenv("ANISO_GRAPH") != nullptr && !h->pt.on;  // opt-in: measured slower than stream launches
+    h->use_graphs = getenv("ANISO_GRAPH") != nullptr && !h->pt.on;
+    h->split_tail = getenv("ANISO_SPLIT_TAIL") != nullptr;  // opt-in: measured slower than stream launches
     const HostPlan& p = h->plan;
     const int N = p.N, nn = (int)p.nodes.size(), r = p.rank;
     // geometry in slot order
@@ -634,7 +636,7 @@ int aniso_destroy(aniso_t* h) {
         if (h->pinned) cudaFreeHost(h->pinned);
         if (h->pinned_small) cudaFreeHost(h->pinned_small);
         if (h->st_bulk) cudaStreamSynchronize(h->st_bulk);
-        for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join, h->ev_own})
+        for (cudaEvent_t e : {h->ev_fork, h->ev_leaf, h->ev_join, h->ev_own, h->ev_p2p})
             if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : h->copy_ev) cudaEventDestroy(e);
         for (cudaEvent_t e : h->gm_ev)
@@ -779,7 +781,8 @@ DevCSR sub_range(const DevCSR& m, int g0, int count) {
     s.nrow += g0;
     s.ent_ptr += g0;
     if (s.srow_ptr) s.srow_ptr += g0;
-    s.nrows_total = count * m.uniform_nrow;
+    // rows per group: r for the M2L operator (uniform_nrow), the block size for a uniform P2P operator (symmetric storage)
+    s.nrows_total = count * (m.uniform_nrow ? m.uniform_nrow : m.uniform_block);
     return s;
 }
 
@@ -923,6 +926,9 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
     const int ng = h->m2l.groups, gd = h->overlap ? h->m2l_deep_g0 : ng;
     cudaStream_t sb = h->overlap ? h->st_bulk : h->st;
     double* mch = h->d_mcharge;  // multipoles (the peer-memory exchange uses its own double-buffered arrays)
+    // split tail: cached symmetric P2P tiles in at least two groups, one rank, both streams, deep M2L rows on the bulk stream
+    const bool split = h->split_tail && !src && h->nranks == 1 && h->overlap && h->subtree_ok && c.p2p && h->p2p.symmetric &&
+                       h->p2p.groups >= 2 && h->m2l_deep_g0 < h->m2l.groups && !(p.deep_chunks > 1);
     bool deep_gathered_on_bulk = false;  // peer exchange: the bulk stream itself has waited for the leaf multipoles
     const bool m2l_deep_leaf_only = h->m2l_deep_g0 < h->m2l.groups;  // the deep rows exist and read leaf multipoles only
     if (!sym_m) CK(cudaMemsetAsync(h->d_mpot, 0, (size_t)T.nnodes * T.r * sizeof(double), h->st));
@@ -1007,6 +1013,13 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
             allgather_multipoles(h);
             CK(cudaEventRecord(h->ev_leaf, h->st));
             phase_mark(h, "gather_multipoles");
+        } else if (split) {
+            // Split tail: P2P rows [0, gp/2) fill the bulk stream while the leaf multipoles are being formed; the other half
+            // follows the deepest-level M2L stream, and the latency-bound leaf pass (far field only) runs under it.
+            const int gp = h->p2p.groups;
+            LAUNCH(h, launch_bsr_apply(sub_range(h->p2p, 0, gp / 2), c.p2p, q, h->d_pot, c.sign, false, sb));
+            h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, h->ev_leaf);
+            phase_mark(h, "up");
         } else {
             h->launches += launch_up_tree(T, h->G, h->sub, q, h->d_mcharge, h->st, h->overlap ? h->ev_leaf : nullptr);
             phase_mark(h, "up");
@@ -1025,6 +1038,12 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
             }
             if (gd >= ng) CK(cudaEventRecord(h->ev_join, sb));
             phase_mark(h, "[b]m2l_deep", sb);
+            if (split) {
+                const int gp = h->p2p.groups;
+                LAUNCH(h, launch_bsr_apply(sub_range(h->p2p, gp / 2, gp - gp / 2), c.p2p, q, h->d_pot, c.sign, false, sb));
+                CK(cudaEventRecord(h->ev_p2p, sb));
+                phase_mark(h, "[b]p2p_2nd", sb);
+            }
         }
         if (gd > 0) LAUNCH(h, launch_bsr_apply(sub_range(h->m2l, 0, gd), c.m2l, mch, h->d_mpot, c.sign, false, h->st));
         phase_mark(h, "m2l_shallow");
@@ -1040,6 +1059,15 @@ void run_fmm(aniso_handle* h, const OperatorCache& c, const double* q, double* o
                                                      root0 + k * nroots, nroots);
                 if (k == nch - 2) phase_mark(h, "down_leaf_but_last");
             }
+        } else if (split) {
+            CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
+            phase_mark(h, "join_m2l");
+            h->launches += launch_down_leaf_tree(T, h->G, h->m2l, sym_m, h->p2p, sym_p, h->sub, L0, h->d_leaf_of_slot, h->slot0, h->nown,
+                                                 h->d_mpot, h->d_pot, nullptr, nullptr, nullptr, h->d_fmm, 0, h->st, nullptr, 0, -1, true);
+            phase_mark(h, "far_field");
+            CK(cudaStreamWaitEvent(h->st, h->ev_p2p, 0));
+            LAUNCH(h, launch_tail(T, h->G, h->p2p, sym_p, h->d_leaf_of_slot, h->slot0, h->nown, h->d_fmm, h->d_pot, stencil, f, x_own, out,
+                                  mode, h->st));
         } else {
             if (h->overlap) CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
             phase_mark(h, "join_bulk");
@@ -2388,7 +2416,7 @@ const char* aniso_get_config(const aniso_t* h) {
     static const char* names[] = {"ANISO_GMRES_ORTHO", "ANISO_GMRES_SYNC", "ANISO_NO_SYM", "ANISO_NO_SUBTREE", "ANISO_NO_OVERLAP",
                                   "ANISO_CELL_WALK", "ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS", "ANISO_SYMG_NO_DMMA", "ANISO_NO_DMMA",
                                   "ANISO_BLOCK_LOOP", "ANISO_BLOCK_PER_ID", "ANISO_NO_SHARED_TAU", "ANISO_SUBTREE_D",
-                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_GRAPH", "ANISO_DEEP_CHUNKS", "ANISO_NO_PEER"};
+                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_GRAPH", "ANISO_DEEP_CHUNKS", "ANISO_NO_PEER", "ANISO_SPLIT_TAIL"};
     cfg = "aniso_b200 0.2 (sm_100a)";
     if (h) {
         cfg += "; ranks=" + std::to_string(h->nranks) + " sym=" + std::to_string(h->plan.m2l.symmetric ? 1 : 0) +

@@ -183,7 +183,12 @@ int launch_down_mid_tree(const DevTree& T, const DevCSR& m2l, bool fold, const S
 int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                           const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
                           const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
-                          const FoldList* fl = nullptr, int cta0 = 0, int nctas = -1);  // [cta0, cta0 + nctas): sub-trees of one chunk
+                          const FoldList* fl = nullptr, int cta0 = 0, int nctas = -1,  // [cta0, cta0 + nctas): sub-trees of one chunk
+                          bool no_near = false);  // no_near: far field only (mode 0); launch_tail adds the rest
+// split tail: out = finalise(far + near-field fold + correction stencil), see tail_kernel (subtree.cu)
+void launch_tail(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,
+                 const double* far, const double* pot, const double* C, const double* f_ref, const double* x, double* out, int mode,
+                 cudaStream_t st);
 // L2P + tail of the matvec for slots [slot0, slot0+n):  fmm = pot[p] + L2P(p)
 //   mode 0: out = fmm;  mode 1: out = (fmm + C.f)/2pi;  mode 2: out = x - (fmm + C.f)/2pi   (C: fused stencil, f_ref: full unscaled source in reference order)
 void launch_l2p(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,

@@ -298,7 +298,8 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
         const int id = n0 ? leaf0 + (p - rb) / n0 : leaf_of_slot[p];
         P.lo = id - leaf0;
         const int tl = n0 ? (p - rb) % n0 : p - T.pt_off[id];
-        P.near = MULTI ? fold_node_multi(p2p, fl, fl.p2p_scr, id, tl) : fold_p2p ? fold_node(p2p, id, tl) : pot[p];
+        // fold_p2p == 2: the near field is added later by tail_kernel (split tail: this pass runs under the P2P stream)
+        P.near = MULTI ? fold_node_multi(p2p, fl, fl.p2p_scr, id, tl) : fold_p2p == 2 ? 0.0 : fold_p2p ? fold_node(p2p, id, tl) : pot[p];
         cheb_weights<NP>(tn, np, G.sxn[p], P.wx);
         cheb_weights<NP>(tn, np, G.syn[p], P.wy);
     };
@@ -335,6 +336,52 @@ __global__ void __launch_bounds__(256, NP == 4 ? 4 : 2) down_leaf_kernel(DevTree
         pre(p, P);
         post(p, P);
     }
+}
+
+// Split tail: what is left of the matvec per point once the leaf pass has written the far field (L2P of the finished local
+// expansions) without the near field:  v = far + near(p) + C.f;  mode 1: out = v / 2pi;  mode 2: out = x - v / 2pi.
+// near(p) = the leaf's P2P scratch rows folded in their fixed order (symmetric storage) or pot[p]; the stencil as in
+// down_leaf_kernel.  A pure streaming kernel: one point per thread, every load independent of the others.
+__global__ void __launch_bounds__(256) tail_kernel(DevTree T, DevGeom G, DevCSR p2p, int fold_p2p, const int* __restrict__ leaf_of_slot,
+                                                   int slot0, int n, const double* __restrict__ far, const double* __restrict__ pot,
+                                                   const double* __restrict__ C, const double* __restrict__ f_ref,
+                                                   const double* __restrict__ x, double* __restrict__ out, int mode) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int p = slot0 + k;
+    const int id = leaf_of_slot[p];
+    const int tl = p - T.pt_off[id];
+    const double near = fold_p2p ? fold_node(p2p, id, tl) : pot[p];
+    double corr = 0;
+    if (mode) {
+        const int c2 = G.c2, sz = G.sz;
+        const int tc = G.perm[p] / c2;
+        const int ti = tc / sz, tj = tc - ti * sz;
+        for (int qq = 0; qq < c2; ++qq) {
+            double cv[9], fv[9];
+#pragma unroll
+            for (int cs = 0; cs < 9; ++cs) {
+                const int si = ti + cs / 3 - 1, sj = tj + cs % 3 - 1;
+                const bool ok = si >= 0 && si < sz && sj >= 0 && sj < sz;
+                cv[cs] = ok ? C[(size_t)(cs * c2 + qq) * n + k] : 0.0;
+                fv[cs] = ok ? f_ref[(size_t)(si * sz + sj) * c2 + qq] : 0.0;
+            }
+#pragma unroll
+            for (int cs = 0; cs < 9; ++cs) corr = fma(cv[cs], fv[cs], corr);
+        }
+    }
+    double v = near + far[k];
+    if (mode) {
+        v = (v + corr) * (M_1_PI / 2.0);
+        if (mode == 2) v = x[k] - v;
+    }
+    out[k] = v;
+}
+
+void launch_tail(const DevTree& T, const DevGeom& G, const DevCSR& p2p, bool fold_p2p, const int* leaf_of_slot, int slot0, int n,
+                 const double* far, const double* pot, const double* C, const double* f_ref, const double* x, double* out, int mode,
+                 cudaStream_t st) {
+    if (n > 0) tail_kernel<<<(n + 255) / 256, 256, 0, st>>>(T, G, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, far, pot, C, f_ref, x, out, mode);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -454,7 +501,7 @@ template <int NP>
 static void down_leaf_launch(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                              const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
                              const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
-                             const FoldList* flp, int cta0, int nctas) {
+                             const FoldList* flp, int cta0, int nctas, bool no_near) {
     static const FoldList none = FoldList();
     const FoldList& fl = flp ? *flp : none;
     const int r = T.r, D = sp.leaf_D, Ls = sp.leaf_Ls, ctas = nctas >= 0 ? nctas : 1 << (2 * Ls), top = Ls == L0;
@@ -464,7 +511,7 @@ static void down_leaf_launch(const DevTree& T, const DevGeom& G, const DevCSR& m
 #define DOWN_LEAF(SR, FO, MU)                                                                                                   \
     do {                                                                                                                        \
         want_smem(down_leaf_kernel<NP, SR, FO, MU>, bytes);                                                                     \
-        down_leaf_kernel<NP, SR, FO, MU><<<ctas, 256, bytes, st>>>(T, G, m2l, p2p, fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, \
+        down_leaf_kernel<NP, SR, FO, MU><<<ctas, 256, bytes, st>>>(T, G, m2l, p2p, no_near ? 2 : fold_p2p ? 1 : 0, leaf_of_slot, slot0, n, mpot, pot, \
                                                                    C, f_ref, x, out, mode, Ls, D, top, cta0, fl);               \
     } while (0)
     if (flp && sr) DOWN_LEAF(true, true, true);
@@ -479,13 +526,13 @@ static void down_leaf_launch(const DevTree& T, const DevGeom& G, const DevCSR& m
 int launch_down_leaf_tree(const DevTree& T, const DevGeom& G, const DevCSR& m2l, bool fold, const DevCSR& p2p, bool fold_p2p,
                           const SubtreePlan& sp, int L0, const int* leaf_of_slot, int slot0, int n, double* mpot, const double* pot,
                           const double* C, const double* f_ref, const double* x, double* out, int mode, cudaStream_t st,
-                          const FoldList* fl, int cta0, int nctas) {
+                          const FoldList* fl, int cta0, int nctas, bool no_near) {
     if (n == 0) return 0;
     switch (T.np) {
-        case 4: down_leaf_launch<4>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas); break;
-        case 6: down_leaf_launch<6>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas); break;
-        case 8: down_leaf_launch<8>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas); break;
-        default: down_leaf_launch<0>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas);
+        case 4: down_leaf_launch<4>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas, no_near); break;
+        case 6: down_leaf_launch<6>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas, no_near); break;
+        case 8: down_leaf_launch<8>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas, no_near); break;
+        default: down_leaf_launch<0>(T, G, m2l, fold, p2p, fold_p2p, sp, L0, leaf_of_slot, slot0, n, mpot, pot, C, f_ref, x, out, mode, st, fl, cta0, nctas, no_near);
     }
     return 1;
 }
