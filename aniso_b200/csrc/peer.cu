@@ -11,7 +11,7 @@
 //                   rank order, so all ranks hold bit-identical results (GMRES stays in lock-step, as with ncclAllReduce)
 // Buffers are double-buffered by the parity of an epoch counter every rank advances alike (the entry points are SPMD): a rank
 // can be at most one exchange ahead of the slowest rank, because finishing exchange e needs every rank's push of e.
-// Every wait carries a time-out (error flag in pinned host memory) instead of spinning for ever on a lost peer.
+// Every wait carries a time-out (~20 s; error flag in pinned host memory) instead of spinning for ever on a lost peer.
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>

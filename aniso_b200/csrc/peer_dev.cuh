@@ -12,12 +12,14 @@ __device__ __forceinline__ unsigned long long peer_ld_flag(const unsigned long l
 __device__ __forceinline__ void peer_st_flag(unsigned long long* p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-// waits until flags[0..P) >= epoch; ~2 s time-out at 1.9 GHz
+// waits until flags[0..P) >= epoch.  Time-out ~20 s at 1.9 GHz: ranks of a solver loop are microseconds apart, but callers
+// may let ranks drift by seconds between collective calls (NCCL would simply wait); a peer that never arrives must still
+// not hold the GPU for ever
 __device__ __forceinline__ bool peer_wait_all(const unsigned long long* flags, int P, unsigned long long epoch, int* err) {
     const long long t0 = clock64();
     for (int r = 0; r < P; ++r) {
         while (peer_ld_flag(flags + r) < epoch) {
-            if (clock64() - t0 > 4000000000ll) {
+            if (clock64() - t0 > 40000000000ll) {
                 *err = 1;
                 return false;
             }
