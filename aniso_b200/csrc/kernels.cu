@@ -6,6 +6,7 @@
 //   stencil_apply    the per-matvec correction
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 
 #include "device.cuh"
 
@@ -460,10 +461,77 @@ __global__ void __launch_bounds__(256) fill_from_base_kernel(DevCSR m, DevTree T
         }
     }
 }
+// The same for uniform 16 x 16 blocks (every BASELINE configuration at np 4: M2L blocks between 4 x 4 Chebyshev grids, P2P
+// tiles between 16-point leaves).  256 threads = one block entry each, so a thread's (source, target) position - and for
+// the Chebyshev case its four node offsets - are the same in every block and leave the loop; the EPC id-0 values a thread
+// needs are requested before any arithmetic (EPC loads in flight per thread instead of one).  The generic kernel ran at
+// 2.3 TB/s, bound by its index arithmetic (idx / nrow, % np per entry).  Same expressions, same values.
+template <bool CHEB>
+__global__ void __launch_bounds__(256) fill_from_base16_kernel(DevCSR m, DevTree T, DevGeom G, int id, const double* __restrict__ A0,
+                                                               double* __restrict__ A) {
+    __shared__ double s_geo[EPC][8];
+    __shared__ int s_off[EPC][2];
+    __shared__ int64_t s_blk[EPC];
+    __shared__ double s_cheb[4];
+    const int e_base = blockIdx.x * EPC, cnt = min(EPC, m.entries - e_base);
+    if (threadIdx.x < cnt) {
+        const int e = e_base + threadIdx.x;
+        const int tn = m.tgt_node[e], sn = m.src_node[e];
+        s_blk[threadIdx.x] = m.blk_off[e];
+        if (CHEB) {
+            double* __restrict__ gg = s_geo[threadIdx.x];
+            gg[0] = T.cx[tn]; gg[1] = T.cy[tn]; gg[2] = T.rx[tn]; gg[3] = T.ry[tn];
+            gg[4] = T.cx[sn]; gg[5] = T.cy[sn]; gg[6] = T.rx[sn]; gg[7] = T.ry[sn];
+        } else {
+            s_off[threadIdx.x][0] = T.pt_off[tn];
+            s_off[threadIdx.x][1] = T.pt_off[sn];
+        }
+    } else if (CHEB && threadIdx.x >= 32 && threadIdx.x < 36)
+        s_cheb[threadIdx.x - 32] = T.cheb[threadIdx.x - 32];
+    __syncthreads();
+    const int idx = threadIdx.x, sI = idx >> 4, tI = (idx & 15) ^ (m.swz ? (sI & 3) << 2 : 0);
+    double base[EPC];
+#pragma unroll
+    for (int j = 0; j < EPC; ++j) base[j] = j < cnt ? A0[s_blk[j] + idx] : 0.0;
+    const double csx = CHEB ? s_cheb[sI & 3] : 0.0, csy = CHEB ? s_cheb[sI >> 2] : 0.0;
+    const double ctx = CHEB ? s_cheb[tI & 3] : 0.0, cty = CHEB ? s_cheb[tI >> 2] : 0.0;
+#pragma unroll
+    for (int j = 0; j < EPC; ++j) {
+        if (j >= cnt) break;
+        double ax, ay, bx, by;
+        if (CHEB) {
+            const double* __restrict__ gg = s_geo[j];
+            ax = gg[4] + gg[6] * csx;
+            ay = gg[5] + gg[7] * csy;
+            bx = gg[0] + gg[2] * ctx;
+            by = gg[1] + gg[3] * cty;
+        } else {
+            const int toff = s_off[j][0], soff = s_off[j][1];
+            ax = G.px[soff + sI]; ay = G.py[soff + sI];
+            bx = G.px[toff + tI]; by = G.py[toff + tI];
+        }
+        const double ddx = ax - bx, ddy = ay - by, d2 = ddx * ddx + ddy * ddy;
+        double v = 0.0;
+        if (d2 != 0.0) {
+            double inv = rsqrt(d2);
+            inv = fma(fma(-d2 * inv, inv, 1.0), 0.5 * inv, inv);
+            v = base[j] * cos_k_theta(id, ddx * inv, ddy * inv);
+        }
+        A[s_blk[j] + idx] = v;
+    }
+}
+
 void launch_fill_from_base(const DevCSR& m, const DevTree& T, const DevGeom& G, int id, int cheb, const double* A0, double* A,
                            cudaStream_t st) {
     if (m.entries == 0) return;
-    fill_from_base_kernel<<<(m.entries + EPC - 1) / EPC, 256, 0, st>>>(m, T, G, id, cheb, A0, A);
+    const unsigned ctas = (m.entries + EPC - 1) / EPC;
+    static const bool generic = getenv("ANISO_FROM_BASE_GENERIC") != nullptr;  // A/B switch
+    if (m.uniform_block == 16 && !generic && (!cheb || T.np == 4)) {
+        if (cheb) fill_from_base16_kernel<true><<<ctas, 256, 0, st>>>(m, T, G, id, A0, A);
+        else fill_from_base16_kernel<false><<<ctas, 256, 0, st>>>(m, T, G, id, A0, A);
+        return;
+    }
+    fill_from_base_kernel<<<ctas, 256, 0, st>>>(m, T, G, id, cheb, A0, A);
 }
 
 void launch_fill(const DevCSR& m, const DevTree& T, const DevGeom& G, const SigmaGrid& S, int id, int part, int cheb,
