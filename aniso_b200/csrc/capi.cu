@@ -2416,7 +2416,7 @@ const char* aniso_get_config(const aniso_t* h) {
     static const char* names[] = {"ANISO_GMRES_ORTHO", "ANISO_GMRES_SYNC", "ANISO_NO_SYM", "ANISO_NO_SUBTREE", "ANISO_NO_OVERLAP",
                                   "ANISO_CELL_WALK", "ANISO_NO_SWIZZLE", "ANISO_STREAM_REGS", "ANISO_SYMG_NO_DMMA", "ANISO_NO_DMMA",
                                   "ANISO_BLOCK_LOOP", "ANISO_BLOCK_PER_ID", "ANISO_NO_SHARED_TAU", "ANISO_SUBTREE_D",
-                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_GRAPH", "ANISO_DEEP_CHUNKS", "ANISO_NO_PEER", "ANISO_SPLIT_TAIL"};
+                                  "ANISO_HOST_FULL_COPY", "ANISO_UP_REPLICATED", "ANISO_GRAPH", "ANISO_DEEP_CHUNKS", "ANISO_NO_PEER", "ANISO_SPLIT_TAIL", "ANISO_FROM_BASE_GENERIC"};
     cfg = "aniso_b200 0.2 (sm_100a)";
     if (h) {
         cfg += "; ranks=" + std::to_string(h->nranks) + " sym=" + std::to_string(h->plan.m2l.symmetric ? 1 : 0) +
