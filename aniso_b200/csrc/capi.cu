@@ -2093,6 +2093,9 @@ int gmres_core(aniso_handle* h, const DevOp& A, int n, const double* b, double* 
     }
     if (hist && *iters < hist_cap) hist[*iters] = resid;
     CK(cudaStreamSynchronize(h->st));
+    // a step queued ahead of a converging one leaves its scalar recurrence and its report copy on the side stream: nothing of
+    // this solve may still write to the pinned report buffer when the next solve starts reading it
+    if (h->st_aux) CK(cudaStreamSynchronize(h->st_aux));
     check_peer(h);
     if (gt_on) {
         const double wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - gt_t0).count();
