@@ -262,3 +262,21 @@ def test_group_handle_host_side(lib):
     _lib.check(lib.aniso_create_multi(16, 1, 2, 0.5, 10, 4, 20, 1, np.array([0], np.int32), C.byref(h)))  # ndev 1: a plain handle
     assert lib.aniso_num_nodes(h) == 256
     lib.aniso_destroy(h)
+
+
+def test_rank_major_multipole_layout_properties(tmp_path):
+    """The rank-major packing of the sharded upward pass (mc_node / DevTree::pack_* in aniso_b200/csrc/device.cuh; the
+    reference's upPass, bbfmm.h:817-861, has one address space and no such layout): a bijection, one contiguous block per rank
+    (so one all-gather moves every level), Morton order kept inside a block.  tests/data/mc_node_check.cu includes the
+    product header and runs the mapping on the host."""
+    import shutil
+
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not found")
+    exe = str(tmp_path / "mc_node_check")
+    c = subprocess.run([nvcc, "-std=c++17", "-I", os.path.join(ROOT, "aniso_b200", "csrc"), "-o", exe,
+                        os.path.join(ROOT, "tests", "data", "mc_node_check.cu")], capture_output=True, text=True, timeout=600)
+    assert c.returncode == 0, c.stderr[-2000:]
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "mc_node ok" in out.stdout, out.stdout[-2000:]
