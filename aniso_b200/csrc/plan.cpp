@@ -7,8 +7,8 @@
 #include <cmath>
 #include <cstring>
 #include <functional>
+#include <numeric>
 #include <stdexcept>
-#include <unordered_map>
 
 namespace an {
 
@@ -506,10 +506,29 @@ static void finish_csr(BlockCSR& b) {
 static void symmetrize(BlockCSR& b, const std::vector<int>* chunk = nullptr) {
     const int groups = (int)b.nrow.size(), R = b.uniform_block;
     if (!groups || R < 4 || R > 64 || getenv("ANISO_NO_SYM")) return;  // R = 16, 64: stream.cu bsr_apply_sym_kernel; else symg
-    auto key = [](int t, int s) { return ((int64_t)t << 32) | (uint32_t)s; };
-    std::unordered_map<int64_t, int> entry_of;  // (tgt, src) -> entry
-    entry_of.reserve(b.col_off.size() * 2);
-    for (size_t e = 0; e < b.col_off.size(); ++e) entry_of[key(b.tgt_node[e], b.src_node[e])] = (int)e;
+    // partner[e]: the entry (tgt s <- src t) of the same pair as entry e = (tgt t <- src s), or -1.  Found by a binary search
+    // in the entries of s's group sorted by source node (a hash map of all entries took 1 s of the 1.9 s plan build at C5).
+    const int ne = (int)b.col_off.size();
+    int max_node = 0;
+    for (int e = 0; e < ne; ++e) max_node = std::max(max_node, std::max(b.tgt_node[e], b.src_node[e]));
+    std::vector<int> group_of(max_node + 1, -1), by_src(ne), partner(ne, -1);
+    for (int g = 0; g < groups; ++g) group_of[b.group_node[g]] = g;
+#pragma omp parallel for schedule(static)
+    for (int g = 0; g < groups; ++g) {
+        int* lo = by_src.data() + b.ent_ptr[g];
+        int* hi = by_src.data() + b.ent_ptr[g + 1];
+        std::iota(lo, hi, b.ent_ptr[g]);
+        std::sort(lo, hi, [&b](int x, int y) { return b.src_node[x] < b.src_node[y]; });
+    }
+#pragma omp parallel for schedule(static)
+    for (int e = 0; e < ne; ++e) {
+        const int t = b.tgt_node[e], s = b.src_node[e], g = group_of[s];
+        if (t == s || g < 0) continue;
+        const int* lo = by_src.data() + b.ent_ptr[g];
+        const int* hi = by_src.data() + b.ent_ptr[g + 1];
+        const int* it = std::lower_bound(lo, hi, t, [&b](int x, int node) { return b.src_node[x] < node; });
+        if (it != hi && b.src_node[*it] == t) partner[e] = *it;
+    }
     // Of a pair (A,B) the block is kept by A when A+B is even and A < B, or A+B is odd and A > B: every target keeps
     // about half of its pairs, so the warps of the streaming kernel stay balanced.  An entry is a mirror (dropped)
     // when its partner exists and the partner owns the pair.
@@ -524,7 +543,7 @@ static void symmetrize(BlockCSR& b, const std::vector<int>* chunk = nullptr) {
         int rows = 1;
         for (int e = b.ent_ptr[g]; e < b.ent_ptr[g + 1]; ++e) {
             const int t = b.tgt_node[e], s = b.src_node[e];
-            if (t != s && !owns(t, s) && entry_of.count(key(s, t))) {
+            if (partner[e] >= 0 && !owns(t, s)) {
                 is_mirror[e] = 1;
                 row_of_entry[e] = b.srow_ptr[g] + rows++;
             }
@@ -533,16 +552,16 @@ static void symmetrize(BlockCSR& b, const std::vector<int>* chunk = nullptr) {
     }
     b.scratch_rows = b.srow_ptr[groups];
     BlockCSR n;
+    const size_t kept = (size_t)ne - (size_t)(b.scratch_rows - groups);
+    for (auto* v : {&n.col_off, &n.ncol, &n.tgt_node, &n.src_node, &n.mirror_row}) v->reserve(kept);
+    n.blk_off.reserve(kept);
+    n.ent_ptr.reserve(groups + 1);
     n.ent_ptr.push_back(0);
     for (int g = 0; g < groups; ++g) {
         for (int e = b.ent_ptr[g]; e < b.ent_ptr[g + 1]; ++e) {
             if (is_mirror[e]) continue;
             const int t = b.tgt_node[e], s = b.src_node[e];
-            int mrow = -1;
-            if (t != s && owns(t, s)) {
-                auto it = entry_of.find(key(s, t));
-                if (it != entry_of.end()) mrow = row_of_entry[it->second];
-            }
+            const int mrow = partner[e] >= 0 && owns(t, s) ? row_of_entry[partner[e]] : -1;
             n.col_off.push_back(b.col_off[e]);
             n.ncol.push_back(b.ncol[e]);
             n.blk_off.push_back(n.nnz);
@@ -571,6 +590,16 @@ void flatten_lists(HostPlan& p, int leaf_begin, int leaf_end) {
         for (int id = p.leaves[k]; id >= 0 && !need[id]; id = p.nodes[id].parent) need[id] = 1;
     BlockCSR m, q;
     m.uniform_nrow = r;
+    {
+        size_t nm = 0, nq = 0;
+        for (int id = 0; id < nn; ++id)
+            if (need[id]) nm += p.nodes[id].V.size() + p.nodes[id].X.size();
+        for (int k = leaf_begin; k < leaf_end; ++k) nq += p.nodes[p.leaves[k]].U.size() + p.nodes[p.leaves[k]].W.size();
+        for (auto* v : {&m.col_off, &m.ncol, &m.tgt_node, &m.src_node}) v->reserve(nm);
+        m.blk_off.reserve(nm);
+        for (auto* v : {&q.col_off, &q.ncol, &q.tgt_node, &q.src_node}) v->reserve(nq);
+        q.blk_off.reserve(nq);
+    }
     m.ent_ptr.push_back(0);
     q.ent_ptr.push_back(0);
     for (int id = 0; id < nn; ++id) {  // level-major order: M2L blocks of one level are contiguous

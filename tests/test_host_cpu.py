@@ -280,3 +280,18 @@ def test_rank_major_multipole_layout_properties(tmp_path):
     assert c.returncode == 0, c.stderr[-2000:]
     out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0 and "mc_node ok" in out.stdout, out.stdout[-2000:]
+
+
+def test_symmetric_block_storage_invariants(tmp_path):
+    """The one-block-per-pair storage of the V/X and U/W lists (symmetrize in aniso_b200/csrc/plan.cpp; the reference applies
+    both blocks of a pair, bbfmm.h:863-946): every list entry is covered exactly once, as a stored block or as the transposed
+    product of its partner's block; mirror rows lie in the partner's scratch range and no scratch row has two writers; for
+    complete, ragged, depth-capped and sharded plans.  tests/data/plan_sym_check.cpp is compiled with the product's plan.cpp."""
+    exe = str(tmp_path / "plan_sym_check")
+    src = os.path.join(ROOT, "aniso_b200", "csrc")
+    c = subprocess.run(["g++", "-O2", "-std=c++17", "-fopenmp", "-I", src, "-o", exe,
+                        os.path.join(ROOT, "tests", "data", "plan_sym_check.cpp"), os.path.join(src, "plan.cpp")],
+                       capture_output=True, text=True, timeout=600)
+    assert c.returncode == 0, c.stderr[-2000:]
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "plan symmetric storage ok" in out.stdout, out.stdout[-3000:]
