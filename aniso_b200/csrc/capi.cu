@@ -572,7 +572,7 @@ int aniso_create_sharded(int sz, int deg, int K, double g, int sr, int np, int m
     REQUIRE(nranks == 1 || uid, "nccl_unique_id required for nranks > 1");
     aniso_handle* h = new aniso_handle();
     try {
-        build_plan(h->plan, sz, deg, K, g, sr, np, maxLevel);
+        build_plan(h->plan, sz, deg, K, g, sr, np, maxLevel, nranks == 1);
     } catch (const std::exception& e) {
         delete h;
         throw std::invalid_argument(e.what());

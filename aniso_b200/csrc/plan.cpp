@@ -761,7 +761,7 @@ void tabulate_operator(const HostPlan& p, const BlockCSR& b, bool cheb, plan_eva
     }
 }
 
-void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, int maxLevel) {
+void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, int maxLevel, bool flatten) {
     if (sz < 1) throw std::runtime_error("geometry_size must be >= 1");
     if (deg < 1 || deg > 128) throw std::runtime_error("The degree is not implemented.");  // Quadrature.cpp:22189-22191
     if (sr < 1 || sr > 128) throw std::runtime_error("The degree is not implemented.");
@@ -781,7 +781,7 @@ void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, i
     build_geometry(p);
     build_tree(p);
     build_chebyshev(p);
-    flatten_lists(p, 0, (int)p.leaves.size());
+    if (flatten) flatten_lists(p, 0, (int)p.leaves.size());
     for (TreeNode& n : p.nodes) std::vector<int>().swap(n.pts);  // build-time only
 }
 

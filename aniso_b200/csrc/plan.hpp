@@ -98,8 +98,9 @@ struct HostPlan {
 // (the reference prints "The degree is not implemented." and leaves the table empty).
 bool gl_table(int n, double* x, double* w);
 
-// Builds everything above.  Throws std::runtime_error on invalid arguments.
-void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, int maxLevel);
+// Builds everything above.  Throws std::runtime_error on invalid arguments.  flatten = false leaves m2l / p2p empty for a
+// caller that flattens a leaf range itself (sharded handles).
+void build_plan(HostPlan& p, int sz, int deg, int K, double g, int sr, int np, int maxLevel, bool flatten = true);
 
 // kernel::initialize for an arbitrary point set with sources == targets (bbfmm.h:476-505 -> tree::populate 176-209): tree,
 // lists, Chebyshev operators and the flattened (unsymmetric) block-CSR operators; no quadrature geometry.
