@@ -2603,9 +2603,10 @@ int aniso_fmm_apply(aniso_t* h, const double* charge, double* potential) {
 // Single-process multi-GPU (SURVEY 5 / 8b "one process, 8 streams"; aniso_create_sharded(..., ndev, devs) of the required
 // export list): main.cpp:7-150 and AnisoWrapper.cpp:10-138 are single-process callers, so a handle that needs one process
 // per GPU leaves them on one device.  A group handle owns one sharded rank handle per device; each collective call is run
-// by one host thread per rank (CUDA device bound per thread), and the ranks exchange over NCCL exactly as in the
-// process-per-GPU form (CUDA IPC cannot map a buffer into the process that owns it, so the peer-memory collectives fall
-// back to NCCL here).  Host vectors are shared: inputs are read by every rank, each rank writes its own rows of an output.
+// by one host thread per rank (CUDA device bound per thread), and the ranks exchange exactly as in the process-per-GPU
+// form: NCCL for the set-up, the peer-memory collectives per matvec (CUDA IPC cannot map a buffer into the process that
+// owns it, so ranks that are threads of one process publish the raw device pointer and enable peer access instead,
+// peer.cu peer_open).  Host vectors are shared: inputs are read by every rank, each rank writes its own rows of an output.
 // ---------------------------------------------------------------------------------------------------
 template <class F>
 static int multi_all(aniso_handle* h, F&& fn) {
